@@ -1,0 +1,175 @@
+/* relp_b200.h -- C ABI of the B200-native exact revised-simplex hot path.
+ *
+ * The reference (RELP, crate `relp` 0.0.5) has no FFI: its boundary for this path is four generic
+ * Rust traits.  Each entry point below names the trait method(s) it replaces, with file:line under
+ * /root/reference/src/algorithm/two_phase/.  A Rust shim implements
+ * `InverseMaintener` / `BasisInverse` / `PivotRule` on top of exactly these symbols.
+ *
+ * Conventions
+ *   - All functions return a `relp_status` value (>= 0 ok / solver outcome, < 0 error).  No CPU fallback:
+ *     without a CUDA device `relp_create` returns NULL and sets relp_last_error().
+ *   - Rationals cross the boundary as "rat arrays": parallel arrays num[count], den[count] of
+ *     int64 plus one limb buffer.  den[i] >= 1: the value is num[i]/den[i] (canonical: reduced,
+ *     zero = 0/1).  den[i] == 0: the value does not fit int64/int64 and num[i] is a word offset
+ *     into the limb buffer where [header, numerator limbs, denominator limbs] are stored
+ *     (uint32 limbs, little endian; header = nn | nd << 14 | sign << 31).  Always canonical, i.e.
+ *     bit-identical to what `RationalBig` (rational/big/mod.rs:17-29) would hold.
+ *   - Column indices are tableau indices of the current phase: in phase 1 the `nr_artificial`
+ *     artificial columns come first (tableau/kind/artificial/partially.rs:72-88), in phase 2 they
+ *     are provider indices.
+ *   - Rows: the Carry matrix has m+1 rows and m+1 columns.  Row i < m is [b_i | B^-1 row i];
+ *     row m is the cost row [-objective | -pi]  (inverse_maintenance/carry/mod.rs:45-65).
+ */
+#ifndef RELP_B200_H
+#define RELP_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct relp_ctx relp_ctx;
+
+enum relp_status {
+    RELP_OK = 0,              /* call succeeded / loop still running (iteration budget reached)     */
+    RELP_OPTIMAL = 1,         /* pricing found no column: OptimumResult::FiniteOptimum / phase-1 end */
+    RELP_UNBOUNDED = 2,       /* ratio test found no row (phase_two.rs:44-46)                       */
+    RELP_INFEASIBLE = 3,      /* phase 1 ended with objective != 0 (phase_one.rs:146-148)           */
+    RELP_ERR_CUDA = -1,
+    RELP_ERR_ZERO_PIVOT = -2, /* "Pivot value can't be zero" (carry/mod.rs:291-292)                 */
+    RELP_ERR_LIMB_CAPACITY = -3,  /* a numerator/denominator exceeded RELP_OPL 32-bit limbs         */
+    RELP_ERR_HEAP_EXHAUSTED = -4, /* limb heap full: recreate the context with a larger heap        */
+    RELP_ERR_ARGUMENT = -5,
+    RELP_ERR_PHASE1_UNBOUNDED = -6, /* "Artificial cost can not be unbounded" (phase_one.rs:143)     */
+    RELP_ERR_COMM = -7
+};
+
+enum relp_rule {              /* strategy/pivot_rule.rs */
+    RELP_FIRST_PROFITABLE = 0,             /* :38-58  */
+    RELP_FIRST_PROFITABLE_WITH_MEMORY = 1, /* :62-94  (phase-1 default, phase_one.rs:97)   */
+    RELP_STEEPEST_DESCENT = 2              /* :97-127 (phase-2 default, two_phase/mod.rs:44) */
+};
+
+/* One entry of the pivot log written by relp_iterate / relp_solve_relaxation. */
+typedef struct relp_iter_log {
+    int32_t tag;      /* '1' phase-1 pivot, '2' phase-2 pivot, 'z' zero-cost artificial clean-up pivot */
+    int32_t j;        /* entering column (tableau index of that phase) */
+    int32_t r;        /* pivot row */
+    int32_t leaving;  /* leaving column */
+    int32_t T;        /* nnz(generated column) - 1 : rows eliminated            */
+    int32_t S;        /* nnz(B^-1 row r) + 1       : entries per eliminated row */
+} relp_iter_log;
+
+typedef struct relp_stats {
+    uint64_t pivots;            /* pivots taken since relp_load_matrix                       */
+    uint64_t escalated;         /* Carry elements that took the multi-limb path              */
+    uint64_t sum_T, sum_S, sum_TS; /* algorithmic work: bytes(K1) = w * (2*sum_TS + sum_S + sum_T) */
+    uint64_t heap_peak_words;   /* high-water mark of the persistent limb pool               */
+    uint64_t compactions;       /* limb-pool compactions                                     */
+    uint64_t kernel_launches;   /* CUDA kernels launched by this context                     */
+    int32_t  max_limbs;         /* longest stored numerator/denominator seen at read-back    */
+    int32_t  m, n, nr_artificial, phase;
+    double   loop_ms;           /* device time (CUDA events) spent inside relp_iterate loops */
+} relp_stats;
+
+/* ---- life cycle ------------------------------------------------------------------------- */
+/* One context = one GPU.  rank/world describe the row shard of a multi-GPU solve;
+ * world == 1 for a single-GPU solve.  heap_words = size of the limb heap in uint32 words
+ * (0 = default).  Returns NULL on failure (see relp_last_error). */
+relp_ctx* relp_create(int device, int rank, int world, uint64_t heap_words);
+void relp_destroy(relp_ctx*);
+const char* relp_last_error(void);
+int relp_abi_version(void);
+
+/* Multi-GPU only: attach an NCCL communicator (ncclComm_t, created by the caller from
+ * torch.distributed's rendezvous) used for the per-pivot pivot-row broadcast and the two
+ * candidate all-gathers.  `nccl_lib` is the dlopen path of libnccl (NULL = "libnccl.so.2"). */
+int relp_comm_unique_id(void* id128, const char* nccl_lib);
+int relp_attach_comm(relp_ctx*, const void* id128, const char* nccl_lib);
+
+/* ---- input: MatrixProvider (matrix_provider/mod.rs:37-136) ---------------------------------- */
+/* CSC of ALL provider columns, virtual slack columns materialised (matrix_data.rs:308-348),
+ * cost_value(j) with None == 0 (matrix_data.rs:350-357), right_hand_side() >= 0 (:359-371).
+ * Host pointers; copied to the device (the e2e timed region of bench.py includes this copy). */
+int relp_load_matrix(relp_ctx*, int32_t m, int32_t n,
+                     const int64_t* col_ptr, const int32_t* row_idx,
+                     const int64_t* val_num, const int64_t* val_den,
+                     const int64_t* cost_num, const int64_t* cost_den,
+                     const int64_t* rhs_num, const int64_t* rhs_den);
+
+/* ---- InverseMaintener constructors (inverse_maintenance/mod.rs:29-267) --------------------- */
+/* Partially::new + Carry::create_for_partially_artificial
+ * (tableau/kind/artificial/partially.rs:125-205, carry/mod.rs:381-426).  (piv_rows[k], piv_cols[k])
+ * = PartialInitialBasis::pivot_element_indices() (matrix_data.rs:432-452).  n_piv == 0 gives the
+ * fully artificial tableau (carry/mod.rs:358-379). */
+int relp_carry_create_partially_artificial(relp_ctx*, int32_t n_piv,
+                                           const int32_t* piv_rows, const int32_t* piv_cols);
+/* NonArtificial::from_artificial + Carry::from_artificial (non_artificial.rs:151-172,
+ * carry/mod.rs:484-510, :214-271): drop the artificial columns, recompute -pi and -obj (K5). */
+int relp_carry_from_artificial(relp_ctx*);
+/* from_artificial_removing_rows (non_artificial.rs:191-220, carry/mod.rs:650-689,
+ * filter/generic_wrapper.rs:224-300): additionally remove `rows` (sorted) from the Carry, from
+ * every column of A and from b. */
+int relp_carry_from_artificial_remove_rows(relp_ctx*, int32_t n_rows, const int32_t* sorted_rows);
+
+/* ---- per-iteration trait methods (one call per step; results stay on the device) ------------- */
+/* PivotRule::select_primal_pivot_column (pivot_rule.rs:21-33) over Tableau::relative_cost
+ * (tableau/mod.rs:102-108) = Carry::cost_difference (carry/mod.rs:572-577) + initial cost.  K3.
+ * Returns RELP_OK and *j_out, or RELP_OPTIMAL if no column is profitable.  rc (one rat, may be
+ * NULL) receives the reduced cost. */
+int relp_price(relp_ctx*, int rule, int32_t* j_out,
+               int64_t* rc_num, int64_t* rc_den, uint32_t* limbs, size_t limb_cap);
+/* Tableau::generate_column (tableau/mod.rs:122-126) -> BasisInverseRows::generate_column
+ * (basis_inverse_rows.rs:144-155).  K2.  `rc` of column j is recomputed on the device. */
+int relp_generate_column(relp_ctx*, int32_t j);
+/* Tableau::select_primal_pivot_row (tableau/mod.rs:221-247) on the generated column.  K4.
+ * RELP_OK and *r_out, or RELP_UNBOUNDED. */
+int relp_ratio_test(relp_ctx*, int32_t* r_out);
+/* Tableau::bring_into_basis (tableau/mod.rs:47-60) -> Carry::change_basis (carry/mod.rs:549-570)
+ * with the column generated last.  K1. */
+int relp_change_basis(relp_ctx*, int32_t r, int32_t* leaving_out);
+/* BasisInverseRows::generate_element (basis_inverse_rows.rs:157-173): one rat. */
+int relp_generate_element(relp_ctx*, int32_t i, int32_t j,
+                          int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap);
+
+/* ---- fused drivers ---------------------------------------------------------------------------- */
+/* phase_one::primal / phase_two::primal loop (phase_one.rs:135-169, phase_two.rs:32-50), device
+ * resident: price -> generate column -> ratio test -> change basis, up to max_iters pivots
+ * (< 0: until termination).  Appends to the context's pivot log.  Returns RELP_OK (budget
+ * reached), RELP_OPTIMAL (pricing found nothing), RELP_UNBOUNDED, or an error. */
+int relp_iterate(relp_ctx*, int rule, int64_t max_iters);
+/* SolveRelaxation::solve_relaxation (two_phase/mod.rs:30-75): artificial tableau, phase 1, the
+ * artificial clean-up (phase_one.rs:223-260), hand-over (with row removal when rank deficient) and
+ * phase 2.  max_pivots < 0: run to the end.  Resumable: call again to continue. */
+int relp_solve_relaxation(relp_ctx*, int rule_phase1, int rule_phase2,
+                          int32_t n_piv, const int32_t* piv_rows, const int32_t* piv_cols,
+                          int64_t max_pivots);
+int relp_solve_continue(relp_ctx*, int64_t max_pivots);
+/* Stop the resumable solve right after the phase hand-over (parity tests of the pinned fixtures). */
+int relp_solve_to_handover(relp_ctx*, int rule_phase1, int32_t n_piv,
+                           const int32_t* piv_rows, const int32_t* piv_cols);
+
+/* ---- readers (InverseMaintener::current_bfs/b/get_objective_function_value, carry/mod.rs:616-642) */
+int relp_dims(relp_ctx*, int32_t* m, int32_t* n, int32_t* nr_artificial, int32_t* phase);
+int relp_read_basis(relp_ctx*, int32_t* basis_indices /* m */);
+/* Rat array of a rectangular block of the (m+1) x (m+1) Carry, row-major. */
+int relp_read_block(relp_ctx*, int32_t row0, int32_t nrows, int32_t col0, int32_t ncols,
+                    int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used);
+int relp_read_carry(relp_ctx*, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used);
+int relp_read_b(relp_ctx*, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used);
+int relp_read_minus_pi(relp_ctx*, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used);
+int relp_read_minus_objective(relp_ctx*, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used);
+/* The column generated last (dense, m entries; zeros are the entries the reference drops). */
+int relp_read_column(relp_ctx*, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used);
+/* Pivot log: number of entries, then a copy of [first, first+count). */
+int64_t relp_log_size(relp_ctx*);
+int relp_read_log(relp_ctx*, int64_t first, int64_t count, relp_iter_log* out);
+int relp_stats_get(relp_ctx*, relp_stats* out);
+/* Redundant rows found by the artificial clean-up of the last solve (phase_one.rs:223-260). */
+int relp_rows_removed(relp_ctx*, int32_t* out, int32_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

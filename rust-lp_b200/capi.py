@@ -1,0 +1,311 @@
+"""ctypes binding of librelp_b200.so (include/relp_b200.h) and a thin host mirror of the reference's
+interface for the hot path: `Carry` (InverseMaintener, inverse_maintenance/mod.rs:29-267),
+`PivotRule` constants (strategy/pivot_rule.rs), `solve_relaxation` (two_phase/mod.rs:30-75).
+
+The library is CUDA-only.  Importing this module never falls back to a CPU implementation:
+`Carry(...)` raises `RelpError` when the shared library is missing or no GPU is present.
+"""
+import ctypes as C
+import os
+from fractions import Fraction as Fr
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librelp_b200.so")
+
+OK, OPTIMAL, UNBOUNDED, INFEASIBLE = 0, 1, 2, 3
+ERR_CUDA, ERR_ZERO_PIVOT, ERR_LIMB_CAPACITY, ERR_HEAP_EXHAUSTED, ERR_ARGUMENT, ERR_PHASE1_UNBOUNDED, ERR_COMM = \
+    -1, -2, -3, -4, -5, -6, -7
+FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
+
+# every symbol include/relp_b200.h declares (tests check the library exports all of them)
+SYMBOLS = [
+    "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_comm_unique_id",
+    "relp_attach_comm", "relp_load_matrix", "relp_carry_create_partially_artificial",
+    "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_price",
+    "relp_generate_column", "relp_ratio_test", "relp_change_basis", "relp_generate_element",
+    "relp_iterate", "relp_solve_relaxation", "relp_solve_continue", "relp_solve_to_handover",
+    "relp_dims", "relp_read_basis", "relp_read_block", "relp_read_carry", "relp_read_b",
+    "relp_read_minus_pi", "relp_read_minus_objective", "relp_read_column", "relp_log_size",
+    "relp_read_log", "relp_stats_get", "relp_rows_removed",
+]
+
+
+class RelpError(RuntimeError):
+    def __init__(self, status, msg=""):
+        super().__init__(f"relp status {status}: {msg}")
+        self.status = status
+
+
+class IterLog(C.Structure):
+    _fields_ = [("tag", C.c_int32), ("j", C.c_int32), ("r", C.c_int32), ("leaving", C.c_int32),
+                ("T", C.c_int32), ("S", C.c_int32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("pivots", C.c_uint64), ("escalated", C.c_uint64), ("sum_T", C.c_uint64),
+                ("sum_S", C.c_uint64), ("sum_TS", C.c_uint64), ("heap_peak_words", C.c_uint64),
+                ("compactions", C.c_uint64), ("kernel_launches", C.c_uint64), ("max_limbs", C.c_int32),
+                ("m", C.c_int32), ("n", C.c_int32), ("nr_artificial", C.c_int32), ("phase", C.c_int32),
+                ("loop_ms", C.c_double)]
+
+
+_libs = {}
+
+
+def load_library(path=None):
+    """dlopen the C-ABI library and declare its prototypes.  No fallback of any kind."""
+    path = path or LIB_PATH
+    if path in _libs:
+        return _libs[path]
+    if not os.path.exists(path):
+        raise RelpError(ERR_CUDA, f"{path} not built: run `python -c 'import __graft_entry__ as g; g.build()'`")
+    L = C.CDLL(path)
+    vp, i32, i64, sz = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t
+    L.relp_create.restype = vp
+    L.relp_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint64]
+    L.relp_destroy.argtypes = [vp]
+    L.relp_destroy.restype = None
+    L.relp_last_error.restype = C.c_char_p
+    L.relp_comm_unique_id.argtypes = [vp, C.c_char_p]
+    L.relp_attach_comm.argtypes = [vp, vp, C.c_char_p]
+    L.relp_load_matrix.argtypes = [vp, i32, i32] + [vp] * 8
+    L.relp_carry_create_partially_artificial.argtypes = [vp, i32, vp, vp]
+    L.relp_carry_from_artificial.argtypes = [vp]
+    L.relp_carry_from_artificial_remove_rows.argtypes = [vp, i32, vp]
+    L.relp_price.argtypes = [vp, C.c_int, vp, vp, vp, vp, sz]
+    L.relp_generate_column.argtypes = [vp, i32]
+    L.relp_ratio_test.argtypes = [vp, vp]
+    L.relp_change_basis.argtypes = [vp, i32, vp]
+    L.relp_generate_element.argtypes = [vp, i32, i32, vp, vp, vp, sz]
+    L.relp_iterate.argtypes = [vp, C.c_int, i64]
+    L.relp_solve_relaxation.argtypes = [vp, C.c_int, C.c_int, i32, vp, vp, i64]
+    L.relp_solve_continue.argtypes = [vp, i64]
+    L.relp_solve_to_handover.argtypes = [vp, C.c_int, i32, vp, vp]
+    L.relp_dims.argtypes = [vp, vp, vp, vp, vp]
+    L.relp_read_basis.argtypes = [vp, vp]
+    L.relp_read_block.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp, sz, vp]
+    for f in ("relp_read_carry", "relp_read_b", "relp_read_minus_pi", "relp_read_minus_objective", "relp_read_column"):
+        getattr(L, f).argtypes = [vp, vp, vp, vp, sz, vp]
+    L.relp_log_size.argtypes = [vp]
+    L.relp_log_size.restype = i64
+    L.relp_read_log.argtypes = [vp, i64, i64, vp]
+    L.relp_stats_get.argtypes = [vp, vp]
+    L.relp_rows_removed.argtypes = [vp, vp, i32]
+    _libs[path] = L
+    return L
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def decode_rats(num, den, limbs):
+    """Rat array (see relp_b200.h) -> list of Fraction.  Asserts canonical form."""
+    out = []
+    for n, d in zip(num.tolist(), den.tolist()):
+        if d > 0:
+            out.append(Fr(n, d))
+            continue
+        assert d == 0, "absent value crossed the boundary"
+        h = int(limbs[n]); nn = h & 0x3fff; nd = (h >> 14) & 0x3fff
+        a = 0
+        for i in range(nn):
+            a |= int(limbs[n + 1 + i]) << (32 * i)
+        b = 0
+        for i in range(nd):
+            b |= int(limbs[n + 1 + nn + i]) << (32 * i)
+        f = Fr(a, b)
+        assert f.numerator == a and f.denominator == b, "device returned a non-canonical rational"
+        out.append(-f if h >> 31 else f)
+    return out
+
+
+class Carry:
+    """Device-resident `Carry<RationalBig, BasisInverseRows>` (carry/mod.rs:45-65) + the tableau
+    bookkeeping the fused loop needs.  Method names follow the reference's trait methods."""
+
+    def __init__(self, provider, device=0, rank=0, world=1, heap_words=0, lib_path=None):
+        self.L = load_library(lib_path)
+        self.pa = provider
+        self.h = self.L.relp_create(device, rank, world, heap_words)
+        if not self.h:
+            raise RelpError(ERR_CUDA, self.L.relp_last_error().decode())
+        self.rank, self.world = rank, world
+        self._limb_cap = 1 << 16
+        self.load_matrix(provider)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.relp_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _chk(self, st):
+        if st < 0:
+            raise RelpError(st, self.L.relp_last_error().decode())
+        return st
+
+    # ---- MatrixProvider side -----------------------------------------------------------------
+    def load_matrix(self, pa):
+        self.pa = pa
+        self._chk(self.L.relp_load_matrix(self.h, pa.m, pa.n, _p(pa.col_ptr), _p(pa.row_idx), _p(pa.val_num),
+                                          _p(pa.val_den), _p(pa.cost_num), _p(pa.cost_den), _p(pa.rhs_num),
+                                          _p(pa.rhs_den)))
+
+    # ---- InverseMaintener constructors ---------------------------------------------------------
+    def create_for_partially_artificial(self, piv_rows=None, piv_cols=None):
+        pr = self.pa.piv_rows if piv_rows is None else np.ascontiguousarray(piv_rows, dtype=np.int32)
+        pc = self.pa.piv_cols if piv_cols is None else np.ascontiguousarray(piv_cols, dtype=np.int32)
+        self._chk(self.L.relp_carry_create_partially_artificial(self.h, len(pr), _p(pr), _p(pc)))
+
+    def from_artificial(self):
+        self._chk(self.L.relp_carry_from_artificial(self.h))
+
+    def from_artificial_remove_rows(self, rows):
+        r = np.ascontiguousarray(rows, dtype=np.int32)
+        self._chk(self.L.relp_carry_from_artificial_remove_rows(self.h, len(r), _p(r)))
+
+    # ---- per-iteration trait methods -------------------------------------------------------------
+    def select_primal_pivot_column(self, rule):
+        """PivotRule::select_primal_pivot_column -> (j, rc) or None."""
+        j = C.c_int32(-1)
+        n = np.zeros(1, np.int64); d = np.zeros(1, np.int64); limbs = np.zeros(self._limb_cap, np.uint32)
+        st = self._chk(self.L.relp_price(self.h, rule, C.byref(j), _p(n), _p(d), _p(limbs), limbs.size))
+        if st == OPTIMAL:
+            return None
+        return j.value, decode_rats(n, d, limbs)[0]
+
+    def generate_column(self, j):
+        self._chk(self.L.relp_generate_column(self.h, j))
+        vals = self._read(self.L.relp_read_column, self.mloc)
+        return [(self.row_lo + i, v) for i, v in enumerate(vals) if v != 0]
+
+    def select_primal_pivot_row(self):
+        r = C.c_int32(-1)
+        st = self._chk(self.L.relp_ratio_test(self.h, C.byref(r)))
+        return None if st == UNBOUNDED else r.value
+
+    def change_basis(self, r):
+        leaving = C.c_int32(-1)
+        self._chk(self.L.relp_change_basis(self.h, r, C.byref(leaving)))
+        return leaving.value
+
+    def generate_element(self, i, j):
+        n = np.zeros(1, np.int64); d = np.zeros(1, np.int64); limbs = np.zeros(self._limb_cap, np.uint32)
+        self._chk(self.L.relp_generate_element(self.h, i, j, _p(n), _p(d), _p(limbs), limbs.size))
+        v = decode_rats(n, d, limbs)[0]
+        return None if v == 0 else v
+
+    # ---- fused drivers ------------------------------------------------------------------------
+    def iterate(self, rule, max_iters=-1):
+        return self._chk(self.L.relp_iterate(self.h, rule, max_iters))
+
+    def solve_relaxation(self, rule1=FIRST_PROFITABLE_WITH_MEMORY, rule2=STEEPEST_DESCENT, max_pivots=-1):
+        pa = self.pa
+        return self._chk(self.L.relp_solve_relaxation(self.h, rule1, rule2, len(pa.piv_rows), _p(pa.piv_rows),
+                                                      _p(pa.piv_cols), max_pivots))
+
+    def solve_continue(self, max_pivots=-1):
+        return self._chk(self.L.relp_solve_continue(self.h, max_pivots))
+
+    def solve_to_handover(self, rule1=FIRST_PROFITABLE_WITH_MEMORY):
+        pa = self.pa
+        return self._chk(self.L.relp_solve_to_handover(self.h, rule1, len(pa.piv_rows), _p(pa.piv_rows), _p(pa.piv_cols)))
+
+    # ---- readers ------------------------------------------------------------------------------
+    def dims(self):
+        v = [C.c_int32() for _ in range(4)]
+        self._chk(self.L.relp_dims(self.h, *[C.byref(x) for x in v]))
+        return tuple(x.value for x in v)     # m, n, nr_artificial, phase
+
+    @property
+    def m(self):
+        return self.dims()[0]
+
+    @property
+    def nr_artificial(self):
+        return self.dims()[2]
+
+    @property
+    def mloc(self):
+        m = self.m
+        per = (m + self.world - 1) // self.world
+        lo = min(m, self.rank * per)
+        return max(0, min(m, lo + per) - lo)
+
+    @property
+    def row_lo(self):
+        m = self.m
+        per = (m + self.world - 1) // self.world
+        return min(m, self.rank * per)
+
+    def _read(self, fn, count, *args):
+        n = np.zeros(max(count, 1), np.int64); d = np.zeros(max(count, 1), np.int64)
+        while True:
+            limbs = np.zeros(self._limb_cap, np.uint32)
+            used = C.c_size_t(0)
+            st = fn(self.h, *args, _p(n), _p(d), _p(limbs), limbs.size, C.byref(used))
+            if st == ERR_ARGUMENT and used.value > limbs.size:
+                self._limb_cap = int(used.value) * 2
+                continue
+            self._chk(st)
+            return decode_rats(n[:count], d[:count], limbs)
+
+    def basis_indices(self):
+        out = np.zeros(self.m, np.int32)
+        self._chk(self.L.relp_read_basis(self.h, _p(out)))
+        return out
+
+    def b(self):
+        return self._read(self.L.relp_read_b, self.mloc)
+
+    def minus_pi(self):
+        return self._read(self.L.relp_read_minus_pi, self.m)
+
+    def minus_objective(self):
+        return self._read(self.L.relp_read_minus_objective, 1)[0]
+
+    def get_objective_function_value(self):
+        return -self.minus_objective()
+
+    def carry(self):
+        """(minus_obj, minus_pi[], b[], basis[], rows[] as dict col->Fraction) -- the oracle's layout."""
+        m, mloc = self.m, self.mloc
+        flat = self._read(self.L.relp_read_carry, (mloc + 1) * (m + 1))
+        rows = [flat[i * (m + 1):(i + 1) * (m + 1)] for i in range(mloc + 1)]
+        z = rows[mloc]
+        return (z[0], z[1:], [r[0] for r in rows[:mloc]], [int(x) for x in self.basis_indices()],
+                [{k: v for k, v in enumerate(r[1:]) if v != 0} for r in rows[:mloc]])
+
+    def current_bfs(self):
+        """carry/mod.rs:616-625: (basis column, value) for b_i != 0, sorted by column."""
+        b = self.b(); basis = self.basis_indices()
+        t = [(int(basis[self.row_lo + i]), v) for i, v in enumerate(b) if v != 0]
+        t.sort(key=lambda x: x[0])
+        return t
+
+    def log(self):
+        n = self.L.relp_log_size(self.h)
+        arr = (IterLog * max(n, 1))()
+        self._chk(self.L.relp_read_log(self.h, 0, n, arr))
+        return [(chr(arr[k].tag), arr[k].j, arr[k].r, arr[k].leaving, arr[k].T, arr[k].S) for k in range(n)]
+
+    def stats(self):
+        s = Stats()
+        self._chk(self.L.relp_stats_get(self.h, C.byref(s)))
+        return s
+
+    def rows_removed(self):
+        out = np.zeros(max(self.pa.m, 1), np.int32)
+        n = self.L.relp_rows_removed(self.h, _p(out), out.size)
+        return [int(x) for x in out[:n]]
+
+
+def solve_relaxation(provider, rule1=FIRST_PROFITABLE_WITH_MEMORY, rule2=STEEPEST_DESCENT, **kw):
+    """`provider.solve_relaxation::<Carry<RationalBig, BasisInverseRows<_>>>()` (two_phase/mod.rs:30-75).
+    Returns (status, carry)."""
+    c = Carry(provider, **kw)
+    return c.solve_relaxation(rule1, rule2), c

@@ -1,0 +1,483 @@
+// Exact rational arithmetic for the device-resident Carry matrix.
+//
+// Replaces, value for value, the reference's `RationalBig` = newtype over `num::BigRational`
+// (/root/reference/src/data/number_types/rational/big/mod.rs:17-29; operators forwarded in
+// big/wrapping.rs:47-311): every stored value is canonical -- gcd-reduced, denominator > 0,
+// zero = 0/1 -- so results are bit-identical to the reference's by uniqueness of that form,
+// whatever algorithm computes them.
+//
+// Two tiers, chosen per element:
+//   small  : Val{n, d} with int64 numerator and int64 denominator d >= 1; all intermediates in
+//            128 bits with explicit overflow detection ("does the reduced result fit?").
+//   big    : Val{handle, 0}; `handle` is a word offset into the limb heap where
+//            [header | numerator limbs | denominator limbs] live (32-bit limbs, little endian).
+//            header = nn | nd << 14 | sign << 31.   A value is stored big only if it does NOT fit
+//            small, so equal values have equal representations up to the handle.
+//   absent : Val{*, -1} marks "no candidate" in reductions.
+//
+// Everything here is __host__ __device__ so that the same code is unit-tested on the CPU
+// (tests/test_arith_host.py builds csrc/arith_host_test.cpp with g++) before it runs in kernels.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define RELP_HD __host__ __device__ __forceinline__
+#define RELP_HDN __host__ __device__ __noinline__
+#else
+#define RELP_HD inline
+#define RELP_HDN
+#endif
+
+#ifndef RELP_OPL
+#define RELP_OPL 64              // max 32-bit limbs of a stored numerator or denominator (2048 bits)
+#endif
+#define RELP_TL (3 * RELP_OPL + 2)   // max limbs of an intermediate
+
+namespace relp {
+
+typedef unsigned __int128 u128;
+typedef __int128 i128;
+
+struct Val { int64_t n; int64_t d; };
+
+enum { ERR_NONE = 0, ERR_LIMB_CAPACITY = 1, ERR_HEAP_EXHAUSTED = 2, ERR_ZERO_PIVOT = 4 };
+
+// Bump allocator over a region [*top, limit) of the limb heap.
+struct Arena {
+    unsigned long long* top;
+    unsigned long long limit;
+    int* err;                    // sticky error bits (ERR_*)
+};
+
+RELP_HD void set_err(int* err, int bit) {
+#if defined(__CUDA_ARCH__)
+    atomicOr(err, bit);
+#else
+    *err |= bit;
+#endif
+}
+
+RELP_HD long long arena_alloc(const Arena& a, unsigned words) {
+#if defined(__CUDA_ARCH__)
+    unsigned long long off = atomicAdd(a.top, (unsigned long long)words);
+#else
+    unsigned long long off = *a.top; *a.top += words;
+#endif
+    if (off + words > a.limit) { set_err(a.err, ERR_HEAP_EXHAUSTED); return -1; }
+    return (long long)off;
+}
+
+RELP_HD bool is_small(const Val& v) { return v.d > 0; }
+RELP_HD bool is_big(const Val& v) { return v.d == 0; }
+RELP_HD bool is_absent(const Val& v) { return v.d < 0; }
+RELP_HD Val make_small(int64_t n, int64_t d) { Val v; v.n = n; v.d = d; return v; }
+RELP_HD Val val_zero() { return make_small(0, 1); }
+RELP_HD Val val_absent() { return make_small(0, -1); }
+RELP_HD bool val_is_zero(const Val& v) { return v.d == 1 && v.n == 0; }
+
+RELP_HD int ctz64(uint64_t x) {
+#if defined(__CUDA_ARCH__)
+    return __ffsll((long long)x) - 1;
+#else
+    return __builtin_ctzll(x);
+#endif
+}
+RELP_HD int ctz32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)x) - 1;
+#else
+    return __builtin_ctz(x);
+#endif
+}
+
+// Binary GCD on 64-bit magnitudes (Stein, with count-trailing-zero shifts).
+RELP_HD uint64_t gcd64(uint64_t a, uint64_t b) {
+    if (a == 0) return b;
+    if (b == 0) return a;
+    int sh = ctz64(a | b);
+    a >>= ctz64(a);
+    do {
+        b >>= ctz64(b);
+        if (a > b) { uint64_t t = a; a = b; b = t; }
+        b -= a;
+    } while (b);
+    return a << sh;
+}
+
+RELP_HD uint64_t abs64(int64_t x) { return x < 0 ? (uint64_t)0 - (uint64_t)x : (uint64_t)x; }
+
+// ------------------------------------------------------------------------------------------
+// small tier: int64/int64 with 128-bit intermediates.  Each returns false when the canonical
+// result (or an intermediate product) does not fit, in which case the caller escalates.
+// ------------------------------------------------------------------------------------------
+
+#define RELP_I64_MAX ((i128)0x7fffffffffffffffLL)
+
+// out = x + s * a * b, s = +1 or -1      (sparse.rs:213-248 add_multiple_of_row element,
+//                                          carry/mod.rs:283-313 update_b, :326-333 cost row,
+//                                          dense.rs:81-92 / sparse.rs:82-106 inner products)
+RELP_HD bool small_fma(const Val& x, const Val& a, const Val& b, int s, Val* out) {
+    if (a.n == 0 || b.n == 0) { *out = x; return true; }
+    if (x.d == 1 && a.d == 1 && b.d == 1) {                 // integer fast path
+        i128 t = (i128)a.n * b.n;
+        i128 r = s > 0 ? (i128)x.n + t : (i128)x.n - t;
+        if (r > RELP_I64_MAX || r < -RELP_I64_MAX) return false;
+        *out = make_small((int64_t)r, 1);
+        return true;
+    }
+    // canonical product tn/td of a*b (cross-reduce, then multiply)
+    uint64_t an = abs64(a.n), bn = abs64(b.n);
+    uint64_t g1 = b.d == 1 ? 1 : gcd64(an, (uint64_t)b.d);
+    uint64_t g2 = a.d == 1 ? 1 : gcd64(bn, (uint64_t)a.d);
+    u128 tn = (u128)(an / g1) * (bn / g2);
+    u128 td = (u128)((uint64_t)a.d / g2) * ((uint64_t)b.d / g1);
+    if (tn > (u128)RELP_I64_MAX || td > (u128)RELP_I64_MAX) return false;
+    bool tneg = ((a.n < 0) != (b.n < 0)) != (s < 0);
+    uint64_t tnn = (uint64_t)tn, tdd = (uint64_t)td;
+    if (x.n == 0) { *out = make_small(tneg ? -(int64_t)tnn : (int64_t)tnn, (int64_t)tdd); return true; }
+    // x.n/x.d + (+-tn)/td
+    uint64_t xd = (uint64_t)x.d;
+    uint64_t g = (xd == 1 || tdd == 1) ? 1 : gcd64(xd, tdd);
+    uint64_t xdg = xd / g, tdg = tdd / g;
+    i128 p = (i128)x.n * (i128)tdg;                // |.| < 2^126
+    i128 q = (i128)tnn * (i128)xdg;                // < 2^126
+    i128 num = tneg ? p - q : p + q;               // |.| < 2^127
+    if (num == 0) { *out = val_zero(); return true; }
+    u128 den = (u128)xdg * tdd;                    // < 2^126
+    if (g > 1) {                                   // gcd(num, den) = gcd(num, g)  (Knuth 4.5.1)
+        u128 na = num < 0 ? (u128)0 - (u128)num : (u128)num;
+        uint64_t g3 = gcd64((uint64_t)(na % g), g);
+        if (g3 > 1) { num /= (i128)g3; den /= g3; }
+    }
+    if (num > RELP_I64_MAX || num < -RELP_I64_MAX || den > (u128)RELP_I64_MAX) return false;
+    *out = make_small((int64_t)num, (int64_t)den);
+    return true;
+}
+
+// out = x / y  (y != 0)      (sparse.rs:291-301 element_wise_divide, tableau/mod.rs:229 ratio)
+RELP_HD bool small_div(const Val& x, const Val& y, Val* out) {
+    if (x.n == 0) { *out = val_zero(); return true; }
+    uint64_t xn = abs64(x.n), yn = abs64(y.n);
+    uint64_t g1 = gcd64(xn, yn);
+    uint64_t g2 = (x.d == 1 || y.d == 1) ? 1 : gcd64((uint64_t)x.d, (uint64_t)y.d);
+    u128 n = (u128)(xn / g1) * ((uint64_t)y.d / g2);
+    u128 d = (u128)((uint64_t)x.d / g2) * (yn / g1);
+    if (n > (u128)RELP_I64_MAX || d > (u128)RELP_I64_MAX) return false;
+    bool neg = (x.n < 0) != (y.n < 0);
+    *out = make_small(neg ? -(int64_t)(uint64_t)n : (int64_t)(uint64_t)n, (int64_t)(uint64_t)d);
+    return true;
+}
+
+RELP_HD int small_cmp(const Val& x, const Val& y) {
+    if (x.d == y.d) return x.n < y.n ? -1 : (x.n > y.n ? 1 : 0);
+    i128 l = (i128)x.n * y.d, r = (i128)y.n * x.d;
+    return l < r ? -1 : (l > r ? 1 : 0);
+}
+
+// ------------------------------------------------------------------------------------------
+// big tier: magnitudes as little-endian uint32 arrays (n limbs, no leading zero limb; 0 <=> n=0)
+// ------------------------------------------------------------------------------------------
+
+RELP_HD int mag_trim(const uint32_t* a, int n) { while (n > 0 && a[n - 1] == 0) n--; return n; }
+
+RELP_HD int mag_cmp(const uint32_t* a, int na, const uint32_t* b, int nb) {
+    if (na != nb) return na < nb ? -1 : 1;
+    for (int i = na - 1; i >= 0; i--) if (a[i] != b[i]) return a[i] < b[i] ? -1 : 1;
+    return 0;
+}
+
+// r = a + b (r may alias a or b); returns limbs of r (capacity max(na,nb)+1)
+RELP_HD int mag_add(uint32_t* r, const uint32_t* a, int na, const uint32_t* b, int nb) {
+    if (na < nb) { const uint32_t* t = a; a = b; b = t; int ti = na; na = nb; nb = ti; }
+    uint64_t c = 0;
+    int i = 0;
+    for (; i < nb; i++) { c += (uint64_t)a[i] + b[i]; r[i] = (uint32_t)c; c >>= 32; }
+    for (; i < na; i++) { c += a[i]; r[i] = (uint32_t)c; c >>= 32; }
+    if (c) { r[i++] = (uint32_t)c; }
+    return i;
+}
+
+// r = a - b, requires a >= b (r may alias a); returns trimmed limbs
+RELP_HD int mag_sub(uint32_t* r, const uint32_t* a, int na, const uint32_t* b, int nb) {
+    int64_t c = 0;
+    int i = 0;
+    for (; i < nb; i++) { c += (int64_t)a[i] - (int64_t)b[i]; r[i] = (uint32_t)c; c >>= 32; }
+    for (; i < na; i++) { c += (int64_t)a[i]; r[i] = (uint32_t)c; c >>= 32; }
+    return mag_trim(r, na);
+}
+
+// r = a * b (r must not alias); returns limbs (capacity na+nb)
+RELP_HD int mag_mul(uint32_t* r, const uint32_t* a, int na, const uint32_t* b, int nb) {
+    if (na == 0 || nb == 0) return 0;
+    for (int i = 0; i < na + nb; i++) r[i] = 0;
+    for (int i = 0; i < na; i++) {
+        uint64_t c = 0, ai = a[i];
+        for (int j = 0; j < nb; j++) {
+            c += ai * b[j] + r[i + j];
+            r[i + j] = (uint32_t)c; c >>= 32;
+        }
+        r[i + nb] = (uint32_t)c;
+    }
+    return mag_trim(r, na + nb);
+}
+
+RELP_HD int mag_ctz(const uint32_t* a, int n) {     // n > 0
+    int i = 0;
+    while (a[i] == 0) i++;
+    return 32 * i + ctz32(a[i]);
+}
+
+// a >>= s in place; returns limbs
+RELP_HD int mag_shr(uint32_t* a, int n, int s) {
+    int w = s >> 5, b = s & 31;
+    if (w >= n) return 0;
+    int m = n - w;
+    if (b == 0) { for (int i = 0; i < m; i++) a[i] = a[i + w]; }
+    else {
+        for (int i = 0; i < m - 1; i++) a[i] = (a[i + w] >> b) | (a[i + w + 1] << (32 - b));
+        a[m - 1] = a[n - 1] >> b;
+    }
+    return mag_trim(a, m);
+}
+
+// a <<= s in place (capacity n + s/32 + 1); returns limbs
+RELP_HD int mag_shl(uint32_t* a, int n, int s) {
+    if (n == 0) return 0;
+    int w = s >> 5, b = s & 31;
+    if (b == 0) { for (int i = n - 1; i >= 0; i--) a[i + w] = a[i]; n += w; }
+    else {
+        a[n + w] = a[n - 1] >> (32 - b);
+        for (int i = n - 1; i > 0; i--) a[i + w] = (a[i] << b) | (a[i - 1] >> (32 - b));
+        a[w] = a[0] << b;
+        n += w + 1;
+    }
+    for (int i = 0; i < w; i++) a[i] = 0;
+    return mag_trim(a, n);
+}
+
+// Binary GCD of two nonzero magnitudes; destroys both buffers; *res points at the buffer (u or
+// v) holding the result; returns its limb count.  Buffers need one spare limb for the final shift
+// beyond max(nu, nv).
+RELP_HD int mag_gcd(uint32_t* u, int nu, uint32_t* v, int nv, uint32_t** res) {
+    int zu = mag_ctz(u, nu), zv = mag_ctz(v, nv);
+    int sh = zu < zv ? zu : zv;
+    nu = mag_shr(u, nu, zu);
+    nv = mag_shr(v, nv, zv);
+    for (;;) {                                   // invariant: u, v odd and nonzero
+        int c = mag_cmp(u, nu, v, nv);
+        if (c == 0) break;
+        if (c < 0) { uint32_t* t = u; u = v; v = t; int ti = nu; nu = nv; nv = ti; }
+        nu = mag_sub(u, u, nu, v, nv);           // u > v, both odd => u even and nonzero
+        nu = mag_shr(u, nu, mag_ctz(u, nu));
+    }
+    if (sh) nu = mag_shl(u, nu, sh);
+    *res = u;
+    return nu;
+}
+
+// inverse of an odd 32-bit number modulo 2^32 (Newton)
+RELP_HD uint32_t inv32(uint32_t d) {
+    uint32_t x = d;                 // correct to 3 bits
+    x *= 2u - d * x; x *= 2u - d * x; x *= 2u - d * x; x *= 2u - d * x;
+    return x;
+}
+
+// q = a / d where d divides a exactly (Jebelean: multiply by d^-1 modulo 2^(32 nq)).
+// `a` is destroyed (used as the running remainder).  q must not alias a.  Returns limbs of q.
+RELP_HD int mag_divexact(uint32_t* q, uint32_t* a, int na, const uint32_t* d, int nd, uint32_t* dtmp) {
+    if (na == 0) return 0;
+    if (nd == 1 && d[0] == 1) { for (int i = 0; i < na; i++) q[i] = a[i]; return na; }
+    int z = mag_ctz(d, nd);
+    const uint32_t* dd = d;
+    if (z) {                                     // strip the common power of two
+        for (int i = 0; i < nd; i++) dtmp[i] = d[i];
+        nd = mag_shr(dtmp, nd, z);
+        na = mag_shr(a, na, z);
+        dd = dtmp;
+    }
+    int nq = na - nd + 1;                        // quotient has nq or nq-1 limbs
+    uint32_t inv = inv32(dd[0]);
+    for (int i = 0; i < nq; i++) {
+        uint32_t qi = a[i] * inv;
+        q[i] = qi;
+        if (qi) {                                // a[i..nq) -= qi * dd   (truncated at limb nq)
+            uint64_t borrow = 0;
+            int lim = nq - i < nd ? nq - i : nd;
+            int j = 0;
+            for (; j < lim; j++) {
+                uint64_t p = (uint64_t)qi * dd[j] + borrow;
+                uint32_t lo = (uint32_t)p;
+                borrow = (p >> 32) + (a[i + j] < lo);
+                a[i + j] -= lo;
+            }
+            for (int k = i + j; borrow && k < nq; k++) {
+                uint32_t lo = (uint32_t)borrow;
+                borrow = (borrow >> 32) + (a[k] < lo);
+                a[k] -= lo;
+            }
+        }
+    }
+    return mag_trim(q, nq);
+}
+
+// ------------------------------------------------------------------------------------------
+// Views of stored values
+// ------------------------------------------------------------------------------------------
+struct Ref {
+    const uint32_t* num; int nn;
+    const uint32_t* den; int nd;
+    int sign;                    // -1, 0, +1
+    uint32_t tmp[4];             // backing store for small values
+};
+
+RELP_HD void ref_load(Ref& r, const Val& v, const uint32_t* heap) {
+    if (v.d > 0) {
+        uint64_t a = abs64(v.n);
+        r.tmp[0] = (uint32_t)a; r.tmp[1] = (uint32_t)(a >> 32);
+        r.tmp[2] = (uint32_t)v.d; r.tmp[3] = (uint32_t)((uint64_t)v.d >> 32);
+        r.num = r.tmp; r.nn = r.tmp[1] ? 2 : (r.tmp[0] ? 1 : 0);
+        r.den = r.tmp + 2; r.nd = r.tmp[3] ? 2 : 1;
+        r.sign = v.n > 0 ? 1 : (v.n < 0 ? -1 : 0);
+    } else {
+        const uint32_t* p = heap + v.n;
+        uint32_t h = p[0];
+        r.nn = (int)(h & 0x3fff); r.nd = (int)((h >> 14) & 0x3fff);
+        r.sign = (h >> 31) ? -1 : 1;
+        r.num = p + 1; r.den = p + 1 + r.nn;
+    }
+}
+
+RELP_HD unsigned big_words(const uint32_t* heap, const Val& v) {
+    uint32_t h = heap[v.n];
+    return 1u + (h & 0x3fff) + ((h >> 14) & 0x3fff);
+}
+
+RELP_HD int val_sign(const Val& v, const uint32_t* heap) {
+    if (v.d > 0) return v.n > 0 ? 1 : (v.n < 0 ? -1 : 0);
+    return (heap[v.n] >> 31) ? -1 : 1;
+}
+
+// Store a canonical (already reduced, den > 0) value: small if it fits, else in the arena.
+RELP_HD Val store_val(int sign, const uint32_t* num, int nn, const uint32_t* den, int nd,
+                      uint32_t* heap, const Arena& ar) {
+    if (nn == 0) return val_zero();
+    if (nn <= 2 && nd <= 2) {
+        uint64_t a = num[0] | (nn > 1 ? (uint64_t)num[1] << 32 : 0);
+        uint64_t b = den[0] | (nd > 1 ? (uint64_t)den[1] << 32 : 0);
+        if (a <= 0x7fffffffffffffffULL && b <= 0x7fffffffffffffffULL)
+            return make_small(sign < 0 ? -(int64_t)a : (int64_t)a, (int64_t)b);
+    }
+    if (nn > RELP_OPL || nd > RELP_OPL) { set_err(ar.err, ERR_LIMB_CAPACITY); return val_zero(); }
+    long long off = arena_alloc(ar, 1u + nn + nd);
+    if (off < 0) return val_zero();
+    uint32_t* p = heap + off;
+    p[0] = (uint32_t)nn | ((uint32_t)nd << 14) | (sign < 0 ? 0x80000000u : 0u);
+    for (int i = 0; i < nn; i++) p[1 + i] = num[i];
+    for (int i = 0; i < nd; i++) p[1 + nn + i] = den[i];
+    Val v; v.n = off; v.d = 0;
+    return v;
+}
+
+// Copy a value into another arena (persistent <-> transient, compaction).
+RELP_HD Val copy_val(const Val& v, uint32_t* heap, const Arena& ar) {
+    if (v.d != 0) return v;
+    unsigned w = big_words(heap, v);
+    long long off = arena_alloc(ar, w);
+    if (off < 0) return val_zero();
+    for (unsigned i = 0; i < w; i++) heap[off + i] = heap[v.n + i];
+    Val o; o.n = off; o.d = 0;
+    return o;
+}
+
+// Reduce sign * num / den (den > 0, both in scratch buffers that may be destroyed) and store.
+// g1, g2: scratch of RELP_TL limbs each; q: scratch of RELP_TL limbs.
+RELP_HD Val reduce_store(int sign, uint32_t* num, int nn, uint32_t* den, int nd,
+                         uint32_t* g1, uint32_t* g2, uint32_t* q,
+                         uint32_t* heap, const Arena& ar) {
+    if (nn == 0) return val_zero();
+    if (nd == 1 && den[0] == 1) return store_val(sign, num, nn, den, nd, heap, ar);
+    for (int i = 0; i < nn; i++) g1[i] = num[i];
+    for (int i = 0; i < nd; i++) g2[i] = den[i];
+    uint32_t* g;
+    int ng = mag_gcd(g1, nn, g2, nd, &g);
+    if (ng == 1 && g[0] == 1) return store_val(sign, num, nn, den, nd, heap, ar);
+    uint32_t* other = (g == g1) ? g2 : g1;       // free scratch: reused as the stripped divisor
+    int nq = mag_divexact(q, num, nn, g, ng, other);
+    // num buffer is now free: use it for the reduced denominator
+    int ndq = mag_divexact(num, den, nd, g, ng, other);
+    return store_val(sign, q, nq, num, ndq, heap, ar);
+}
+
+// out = x + s * a * b for arbitrary tiers.                      (slow path of K1/K2/K3/K5)
+RELP_HDN Val big_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) {
+    Ref rx, ra, rb;
+    ref_load(rx, x, heap); ref_load(ra, a, heap); ref_load(rb, b, heap);
+    if (ra.sign == 0 || rb.sign == 0) return copy_val(x, heap, ar);
+    if (rx.nn > RELP_OPL || rx.nd > RELP_OPL || ra.nn > RELP_OPL || ra.nd > RELP_OPL ||
+        rb.nn > RELP_OPL || rb.nd > RELP_OPL) { set_err(ar.err, ERR_LIMB_CAPACITY); return val_zero(); }
+    uint32_t n1[2 * RELP_OPL], d1[2 * RELP_OPL];
+    uint32_t p[RELP_TL], q[RELP_TL], den[RELP_TL], g1[RELP_TL], g2[RELP_TL];
+    int nn1 = mag_mul(n1, ra.num, ra.nn, rb.num, rb.nn);
+    int nd1 = mag_mul(d1, ra.den, ra.nd, rb.den, rb.nd);
+    int s1 = ra.sign * rb.sign * s;
+    if (rx.sign == 0) return reduce_store(s1, n1, nn1, d1, nd1, g1, g2, q, heap, ar);
+    int np = mag_mul(p, rx.num, rx.nn, d1, nd1);         // x.n * d1
+    int nq = mag_mul(q, rx.den, rx.nd, n1, nn1);         // x.d * n1
+    int nden = mag_mul(den, rx.den, rx.nd, d1, nd1);
+    int sign;
+    if (rx.sign == s1) { np = mag_add(p, p, np, q, nq); sign = s1; }
+    else {
+        int c = mag_cmp(p, np, q, nq);
+        if (c == 0) return val_zero();
+        if (c > 0) { np = mag_sub(p, p, np, q, nq); sign = rx.sign; }
+        else { np = mag_sub(p, q, nq, p, np); sign = s1; }
+    }
+    return reduce_store(sign, p, np, den, nden, g1, g2, q, heap, ar);
+}
+
+// out = x / y (y != 0) for arbitrary tiers.
+RELP_HDN Val big_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar) {
+    Ref rx, ry;
+    ref_load(rx, x, heap); ref_load(ry, y, heap);
+    if (rx.sign == 0) return val_zero();
+    if (rx.nn > RELP_OPL || rx.nd > RELP_OPL || ry.nn > RELP_OPL || ry.nd > RELP_OPL) {
+        set_err(ar.err, ERR_LIMB_CAPACITY); return val_zero();
+    }
+    uint32_t num[RELP_TL], den[RELP_TL], g1[RELP_TL], g2[RELP_TL], q[RELP_TL];
+    int nn = mag_mul(num, rx.num, rx.nn, ry.den, ry.nd);
+    int nd = mag_mul(den, rx.den, rx.nd, ry.num, ry.nn);
+    return reduce_store(rx.sign * ry.sign, num, nn, den, nd, g1, g2, q, heap, ar);
+}
+
+// sign(x - y) for arbitrary tiers.
+RELP_HDN int big_cmp(const Val& x, const Val& y, const uint32_t* heap) {
+    Ref rx, ry;
+    ref_load(rx, x, heap); ref_load(ry, y, heap);
+    if (rx.sign != ry.sign) return rx.sign < ry.sign ? -1 : 1;
+    if (rx.sign == 0) return 0;
+    uint32_t l[2 * RELP_OPL], r[2 * RELP_OPL];
+    int nl = mag_mul(l, rx.num, rx.nn, ry.den, ry.nd);
+    int nr = mag_mul(r, ry.num, ry.nn, rx.den, rx.nd);
+    int c = mag_cmp(l, nl, r, nr);
+    return rx.sign > 0 ? c : -c;
+}
+
+// ------------------------------------------------------------------------------------------
+// Tier-dispatching front ends
+// ------------------------------------------------------------------------------------------
+RELP_HD Val val_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) {
+    Val out;
+    if (x.d > 0 && a.d > 0 && b.d > 0 && small_fma(x, a, b, s, &out)) return out;
+    return big_fma(x, a, b, s, heap, ar);
+}
+RELP_HD Val val_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar) {
+    Val out;
+    if (x.d > 0 && y.d > 0 && small_div(x, y, &out)) return out;
+    return big_div(x, y, heap, ar);
+}
+RELP_HD int val_cmp(const Val& x, const Val& y, const uint32_t* heap) {
+    if (x.d > 0 && y.d > 0) return small_cmp(x, y);
+    return big_cmp(x, y, heap);
+}
+
+}  // namespace relp

@@ -1,0 +1,801 @@
+// Host side of librelp_b200.so: the C ABI of include/relp_b200.h over the kernels of
+// relp_kernels.cuh.  One context = one GPU = one row shard of the Carry matrix.
+//
+// The driver functions restate, launch for launch, the reference's two-phase control flow
+// (/root/reference/src/algorithm/two_phase/): mod.rs:30-75 solve_relaxation,
+// phase_one.rs:125-170 / 223-260, phase_two.rs:22-51, tableau/kind/artificial/partially.rs:125-205,
+// tableau/kind/non_artificial.rs:151-220.  All arithmetic happens in CUDA kernels; there is no CPU
+// fallback: without a device relp_create fails.
+#include "../../include/relp_b200.h"
+#include "relp_kernels.cuh"
+
+#include <algorithm>
+#include <climits>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <dlfcn.h>
+
+using namespace relp;
+
+static thread_local std::string g_last_error;
+static void set_error(const std::string& s) { g_last_error = s; }
+
+#define CUDA_TRY(expr)                                                                      \
+    do {                                                                                    \
+        cudaError_t _e = (expr);                                                            \
+        if (_e != cudaSuccess) {                                                            \
+            set_error(std::string(#expr) + ": " + cudaGetErrorString(_e));                  \
+            return RELP_ERR_CUDA;                                                           \
+        }                                                                                   \
+    } while (0)
+
+// ---- minimal NCCL surface, resolved with dlopen so that single-GPU use needs no NCCL ----------
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+struct NcclApi {
+    void* handle = nullptr;
+    int (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+static NcclApi g_nccl;
+static int load_nccl(const char* path) {
+    if (g_nccl.handle) return 0;
+    void* h = dlopen(path ? path : "libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) { set_error(std::string("dlopen nccl: ") + dlerror()); return RELP_ERR_COMM; }
+    g_nccl.handle = h;
+    g_nccl.GetUniqueId = (int (*)(ncclUniqueId*))dlsym(h, "ncclGetUniqueId");
+    g_nccl.CommInitRank = (int (*)(ncclComm_t*, int, ncclUniqueId, int))dlsym(h, "ncclCommInitRank");
+    g_nccl.CommDestroy = (int (*)(ncclComm_t))dlsym(h, "ncclCommDestroy");
+    g_nccl.AllGather = (int (*)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t))dlsym(h, "ncclAllGather");
+    g_nccl.AllReduce = (int (*)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t))dlsym(h, "ncclAllReduce");
+    g_nccl.GetErrorString = (const char* (*)(int))dlsym(h, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllGather || !g_nccl.AllReduce) {
+        set_error("libnccl lacks required symbols"); g_nccl.handle = nullptr; return RELP_ERR_COMM;
+    }
+    return 0;
+}
+enum { NCCL_INT8 = 0, NCCL_INT64 = 4, NCCL_SUM = 0 };
+
+template <typename T> struct DBuf {
+    T* p = nullptr; size_t n = 0;
+    int alloc(size_t count) {
+        release();
+        if (count == 0) count = 1;
+        cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+        if (e != cudaSuccess) { set_error(std::string("cudaMalloc: ") + cudaGetErrorString(e)); p = nullptr; return RELP_ERR_CUDA; }
+        n = count; return 0;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    ~DBuf() { release(); }
+};
+
+struct relp_ctx {
+    int device = 0, rank = 0, world = 1;
+    cudaStream_t stream = nullptr;
+    ncclComm_t comm = nullptr;
+    uint64_t heap_words = 0;
+    // host copy of the provider (needed for row removal and set-up)
+    int m = 0, n = 0;
+    std::vector<long long> col_ptr; std::vector<int> row_idx;
+    std::vector<int64_t> an, ad, cn, cd, rhsn, rhsd;
+    // device buffers
+    DBuf<DState> st; DBuf<uint32_t> heap;
+    DBuf<int64_t> xn, xd, an_d, ad_d, cn_d, cd_d, rhsn_d, rhsd_d, rcn, rcd, dn, dd, qn, qd, pnd;
+    DBuf<long long> col_ptr_d; DBuf<int> row_idx_d, basis, art_row, tlist, slist, cost_rows, scratch_i;
+    DBuf<unsigned char> in_basis;
+    DBuf<int2> worklist; DBuf<Cand> cand, gather; DBuf<LogEntry> log;
+    DState* h_st = nullptr;       // pinned mirror
+    Dev D;
+    bool loaded = false, carry_ready = false;
+    int mloc = 0, row_lo = 0, ld = 0, nr_art = 0, phase = 0;
+    std::vector<int> art_rows_h, rows_removed;
+    // resumable solve
+    int stage = 0, rule1 = 1, rule2 = 2, final_status = RELP_OK;
+    bool stop_at_handover = false;
+    uint64_t launches = 0;
+    double loop_ms = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int max_limbs = 0;
+    int sm_count = 148;
+};
+
+#ifdef RELP_EMUL
+#define LAUNCH(c, kern, grid, block, ...) do { kern(__VA_ARGS__); (c)->launches++; } while (0)
+#else
+#define LAUNCH(c, kern, grid, block, ...)                                                   \
+    do { kern<<<(grid), (block), 0, (c)->stream>>>(__VA_ARGS__); (c)->launches++; } while (0)
+#endif
+
+static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+static inline int clampi(long long v, long long lo, long long hi) { return (int)std::max(lo, std::min(hi, v)); }
+
+static int sync_state(relp_ctx* c) {
+    CUDA_TRY(cudaMemcpyAsync(c->h_st, c->st.p, sizeof(DState), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+static int push_state(relp_ctx* c) {
+    CUDA_TRY(cudaMemcpyAsync(c->st.p, c->h_st, sizeof(DState), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+static int err_status(const DState* s) {
+    if (s->err & ERR_ZERO_PIVOT) { set_error("Pivot value can't be zero"); return RELP_ERR_ZERO_PIVOT; }
+    if (s->err & ERR_LIMB_CAPACITY) { set_error("a numerator/denominator exceeded RELP_OPL limbs"); return RELP_ERR_LIMB_CAPACITY; }
+    if (s->err & ERR_HEAP_EXHAUSTED) { set_error("limb heap exhausted: create the context with a larger heap_words"); return RELP_ERR_HEAP_EXHAUSTED; }
+    return 0;
+}
+
+extern "C" {
+
+int relp_abi_version(void) { return 1; }
+const char* relp_last_error(void) { return g_last_error.c_str(); }
+
+relp_ctx* relp_create(int device, int rank, int world, uint64_t heap_words) {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        set_error(std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                  " (librelp_b200 has no CPU path)");
+        return nullptr;
+    }
+    if (device < 0 || device >= count || world < 1 || rank < 0 || rank >= world) { set_error("bad device/rank/world"); return nullptr; }
+    if (cudaSetDevice(device) != cudaSuccess) { set_error("cudaSetDevice failed"); return nullptr; }
+    relp_ctx* c = new relp_ctx();
+    c->device = device; c->rank = rank; c->world = world;
+    c->heap_words = heap_words ? heap_words : (1ull << 28);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaMallocHost((void**)&c->h_st, sizeof(DState)) != cudaSuccess ||
+        cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
+        c->st.alloc(1) || c->heap.alloc(c->heap_words)) {
+        if (g_last_error.empty()) set_error("context allocation failed");
+        relp_destroy(c); return nullptr;
+    }
+    memset(c->h_st, 0, sizeof(DState));
+    memset(&c->D, 0, sizeof(Dev));
+    return c;
+}
+
+void relp_destroy(relp_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    if (c->h_st) cudaFreeHost(c->h_st);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int relp_comm_unique_id(void* id128, const char* nccl_lib) {
+    if (load_nccl(nccl_lib)) return RELP_ERR_COMM;
+    ncclUniqueId id;
+    if (g_nccl.GetUniqueId(&id) != 0) { set_error("ncclGetUniqueId failed"); return RELP_ERR_COMM; }
+    memcpy(id128, &id, sizeof(id));
+    return RELP_OK;
+}
+
+int relp_attach_comm(relp_ctx* c, const void* id128, const char* nccl_lib) {
+    if (!c || !id128) return RELP_ERR_ARGUMENT;
+    if (load_nccl(nccl_lib)) return RELP_ERR_COMM;
+    CUDA_TRY(cudaSetDevice(c->device));
+    ncclUniqueId id; memcpy(&id, id128, sizeof(id));
+    int rc = g_nccl.CommInitRank(&c->comm, c->world, id, c->rank);
+    if (rc != 0) { set_error(std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?")); return RELP_ERR_COMM; }
+    return RELP_OK;
+}
+
+int relp_load_matrix(relp_ctx* c, int32_t m, int32_t n, const int64_t* col_ptr, const int32_t* row_idx,
+                     const int64_t* val_num, const int64_t* val_den, const int64_t* cost_num, const int64_t* cost_den,
+                     const int64_t* rhs_num, const int64_t* rhs_den) {
+    if (!c || m <= 0 || n <= 0 || !col_ptr || !row_idx) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    long long nnz = col_ptr[n];
+    c->m = m; c->n = n;
+    c->col_ptr.assign(col_ptr, col_ptr + n + 1);
+    c->row_idx.assign(row_idx, row_idx + nnz);
+    c->an.assign(val_num, val_num + nnz); c->ad.assign(val_den, val_den + nnz);
+    c->cn.assign(cost_num, cost_num + n); c->cd.assign(cost_den, cost_den + n);
+    c->rhsn.assign(rhs_num, rhs_num + m); c->rhsd.assign(rhs_den, rhs_den + m);
+    if (c->col_ptr_d.alloc(n + 1) || c->row_idx_d.alloc(nnz) || c->an_d.alloc(nnz) || c->ad_d.alloc(nnz) ||
+        c->cn_d.alloc(n) || c->cd_d.alloc(n) || c->rhsn_d.alloc(m) || c->rhsd_d.alloc(m)) return RELP_ERR_CUDA;
+    cudaStream_t s = c->stream;
+    CUDA_TRY(cudaMemcpyAsync(c->col_ptr_d.p, col_ptr, (n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaMemcpyAsync(c->row_idx_d.p, row_idx, nnz * sizeof(int), cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaMemcpyAsync(c->an_d.p, val_num, nnz * 8, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaMemcpyAsync(c->ad_d.p, val_den, nnz * 8, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaMemcpyAsync(c->cn_d.p, cost_num, n * 8, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaMemcpyAsync(c->cd_d.p, cost_den, n * 8, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaMemcpyAsync(c->rhsn_d.p, rhs_num, m * 8, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaMemcpyAsync(c->rhsd_d.p, rhs_den, m * 8, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    c->loaded = true; c->carry_ready = false; c->stage = 0;
+    return RELP_OK;
+}
+
+}  // extern "C"
+
+// ---- internal helpers -------------------------------------------------------------------------
+
+static void shard_rows(relp_ctx* c, int m) {
+    int per = (m + c->world - 1) / c->world;
+    c->row_lo = std::min(m, c->rank * per);
+    c->mloc = std::max(0, std::min(m, c->row_lo + per) - c->row_lo);
+}
+static void shard_cols(relp_ctx* c, DState* s) {
+    int per = (s->ncols + c->world - 1) / c->world;
+    s->col_lo = std::min(s->ncols, c->rank * per);
+    s->col_hi = std::min(s->ncols, s->col_lo + per);
+}
+
+static void wire_dev(relp_ctx* c) {
+    Dev& D = c->D;
+    D.st = c->st.p; D.heap = c->heap.p; D.xn = c->xn.p; D.xd = c->xd.p;
+    D.col_ptr = c->col_ptr_d.p; D.row_idx = c->row_idx_d.p; D.an = c->an_d.p; D.ad = c->ad_d.p;
+    D.cn = c->cn_d.p; D.cd = c->cd_d.p; D.basis = c->basis.p; D.in_basis = c->in_basis.p;
+    D.art_row = c->art_row.p; D.rcn = c->rcn.p; D.rcd = c->rcd.p; D.dn = c->dn.p; D.dd = c->dd.p;
+    D.qn = c->qn.p; D.qd = c->qd.p; D.pn = c->pnd.p; D.pd = c->pnd.p + (c->m + 1);
+    D.tlist = c->tlist.p; D.slist = c->slist.p; D.worklist = c->worklist.p; D.cand = c->cand.p;
+    D.gather = c->gather.p; D.log = c->log.p; D.log_cap = (long long)c->log.n;
+}
+
+static const int MAX_PARTIAL_BLOCKS = 1024;
+
+static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
+    shard_rows(c, m);
+    c->ld = (m + 1 + 15) / 16 * 16;
+    size_t plane = (size_t)(c->mloc + 1) * c->ld;
+    if (c->xn.alloc(plane) || c->xd.alloc(plane)) return RELP_ERR_CUDA;
+    if (c->rcn.alloc(ncols_max) || c->rcd.alloc(ncols_max) || c->in_basis.alloc(ncols_max)) return RELP_ERR_CUDA;
+    if (c->dn.alloc(c->mloc + 1) || c->dd.alloc(c->mloc + 1) || c->qn.alloc(c->mloc + 1) || c->qd.alloc(c->mloc + 1)) return RELP_ERR_CUDA;
+    if (c->pnd.alloc(2 * (size_t)(m + 1))) return RELP_ERR_CUDA;
+    if (c->basis.alloc(m) || c->art_row.alloc(m) || c->tlist.alloc(c->mloc + 1) || c->slist.alloc(m + 1)) return RELP_ERR_CUDA;
+    if (c->cost_rows.alloc(c->mloc + 1) || c->scratch_i.alloc(2 * (size_t)(m + 2))) return RELP_ERR_CUDA;
+    // worklist: worst case every element of the local block is escalated
+    if (c->worklist.alloc(plane)) return RELP_ERR_CUDA;
+    if (c->cand.alloc(MAX_PARTIAL_BLOCKS) || c->gather.alloc(std::max(c->world, 1))) return RELP_ERR_CUDA;
+    if (!c->log.p && c->log.alloc(1 << 20)) return RELP_ERR_CUDA;
+    return 0;
+}
+
+static void init_heap_regions(relp_ctx* c, DState* s) {
+    // [0, T) transient, then two persistent halves
+    unsigned long long T = c->heap_words / 4, P = (c->heap_words - T) / 2;
+    s->tr_base = 0; s->tr_top = 0; s->tr_limit = T;
+    s->pool_base = T; s->pool_top = T; s->pool_limit = T + P;
+    s->alt_base = T + P; s->alt_limit = T + 2 * P;
+}
+
+static int grid_for(relp_ctx* c, long long items, int per_sm = 8) {
+    return clampi(cdiv(items, RELP_THREADS), 1, (long long)c->sm_count * per_sm);
+}
+
+// device-side control block update without touching the rest of DState
+__global__ void k_set_control(DState* st, unsigned long long iter_limit, int tag, int reset_status, int reset_memory) {
+    st->iter_limit = iter_limit; st->tag = tag;
+    if (reset_status) st->status = ST_RUNNING;
+    if (reset_memory) st->last_selected = -1;
+}
+__global__ void k_set_pivot(DState* st, int j, int r, int set_zero_rc) {
+    if (j >= 0) st->j = j;
+    if (r >= 0) st->r = r;
+    if (set_zero_rc) st->rc = make_small(0, 1);
+}
+__global__ void k_reset_transient(DState* st) { st->tr_top = st->tr_base; st->T = 0; st->S = 0; st->wl_count = 0; }
+__global__ void k_reprice_selected(Dev D) {   // rc of st->j for the step-wise API (relp_generate_column)
+    DState* st = D.st;
+    Arena ar = transient(D);
+    st->rc = price_column(D, st, st->j, ar);
+}
+
+static void enqueue_price(relp_ctx* c, int rule) {
+    DState* hs = c->h_st;
+    int mode = rule == RULE_DANTZIG ? ARG_DANTZIG : ARG_FIRST;
+    int ncols_loc = hs->col_hi - hs->col_lo;
+    LAUNCH(c, k_price, grid_for(c, ncols_loc), RELP_THREADS, c->D);
+    int gb = clampi(cdiv(ncols_loc, RELP_THREADS * 4), 1, MAX_PARTIAL_BLOCKS);
+    LAUNCH(c, k_argmin_partial, gb, RELP_THREADS, c->D, mode);
+    if (c->world == 1) LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, mode, gb, 0, -1, rule);
+    else {
+        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, mode, gb, 0, c->rank, rule);
+        g_nccl.AllGather(c->gather.p + c->rank, c->gather.p, sizeof(Cand), NCCL_INT8, c->comm, c->stream);
+        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, mode, c->world, 1, -1, rule);
+    }
+}
+static void enqueue_column_and_ratio(relp_ctx* c, bool ratio) {
+    LAUNCH(c, k_gen_column, grid_for(c, c->mloc + 1), RELP_THREADS, c->D);
+    if (!ratio) return;
+    int gb = clampi(cdiv(c->mloc, RELP_THREADS * 4), 1, MAX_PARTIAL_BLOCKS);
+    LAUNCH(c, k_argmin_partial, gb, RELP_THREADS, c->D, (int)ARG_RATIO);
+    if (c->world == 1) LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, gb, 0, -1, 0);
+    else {
+        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, gb, 0, c->rank, 0);
+        g_nccl.AllGather(c->gather.p + c->rank, c->gather.p, sizeof(Cand), NCCL_INT8, c->comm, c->stream);
+        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, c->world, 1, -1, 0);
+    }
+}
+static void enqueue_change_basis(relp_ctx* c) {
+    LAUNCH(c, k_pivot_row, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D, c->world > 1 ? 1 : 0);
+    if (c->world > 1) {
+        g_nccl.AllReduce(c->pnd.p, c->pnd.p, 2 * (size_t)(c->m + 1), NCCL_INT64, NCCL_SUM, c->comm, c->stream);
+        LAUNCH(c, k_build_slist, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D);
+    }
+    LAUNCH(c, k_bookkeeping, 1, 1, c->D);
+    LAUNCH(c, k_update, c->sm_count * 8, RELP_THREADS, c->D);
+    LAUNCH(c, k_update_big, c->sm_count * 2, 128, c->D);
+    LAUNCH(c, k_iter_end, 1, 1, c->D);
+}
+static void enqueue_iteration(relp_ctx* c, int rule) {
+    LAUNCH(c, k_iter_begin, 1, 1, c->D);
+    LAUNCH(c, k_compact, c->sm_count * 4, RELP_THREADS, c->D);
+    enqueue_price(c, rule);
+    enqueue_column_and_ratio(c, true);
+    enqueue_change_basis(c);
+}
+
+static int check_cuda(relp_ctx* c) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error(std::string("kernel launch: ") + cudaGetErrorString(e)); return RELP_ERR_CUDA; }
+    return 0;
+}
+
+// the device-resident loop of phase_one::primal / phase_two::primal
+static int run_loop(relp_ctx* c, int rule, int64_t max_iters, int tag) {
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    unsigned long long limit = max_iters < 0 ? ~0ull : c->h_st->iter + (unsigned long long)max_iters;
+    LAUNCH(c, k_set_control, 1, 1, c->st.p, limit, tag, 1, 0);
+    cudaEventRecord(c->ev0, c->stream);
+    int batch = 8;
+    int result = RELP_OK;
+    for (;;) {
+        for (int b = 0; b < batch; b++) enqueue_iteration(c, rule);
+        if (check_cuda(c)) return RELP_ERR_CUDA;
+        if (sync_state(c)) return RELP_ERR_CUDA;
+        const DState* s = c->h_st;
+        if (s->err) { result = err_status(s); break; }
+        if (s->status == ST_NO_COLUMN) { result = RELP_OPTIMAL; break; }
+        if (s->status == ST_NO_ROW) { result = RELP_UNBOUNDED; break; }
+        if (s->iter >= limit) { result = RELP_OK; break; }
+        if (batch < 64) batch *= 2;
+    }
+    cudaEventRecord(c->ev1, c->stream);
+    cudaEventSynchronize(c->ev1);
+    float ms = 0; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->loop_ms += ms;
+    return result;
+}
+
+static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* piv_rows, const int32_t* piv_cols) {
+    if (!c->loaded) { set_error("relp_load_matrix first"); return RELP_ERR_ARGUMENT; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    int m = c->m, n = c->n;
+    std::vector<int> real_col(m, -1);
+    for (int k = 0; k < n_piv; k++) {
+        if (piv_rows[k] < 0 || piv_rows[k] >= m || piv_cols[k] < 0 || piv_cols[k] >= n) return RELP_ERR_ARGUMENT;
+        real_col[piv_rows[k]] = piv_cols[k];
+    }
+    c->art_rows_h.clear();
+    for (int i = 0; i < m; i++) if (real_col[i] < 0) c->art_rows_h.push_back(i);
+    int nr_art = (int)c->art_rows_h.size();
+    c->nr_art = nr_art; c->phase = 1;
+    int rc = alloc_carry(c, m, nr_art + n);
+    if (rc) return rc;
+    std::vector<int> basis(m);
+    std::vector<unsigned char> inb(nr_art + n, 0);
+    int k = 0;
+    for (int i = 0; i < m; i++) { basis[i] = real_col[i] < 0 ? k++ : nr_art + real_col[i]; inb[basis[i]] = 1; }
+    CUDA_TRY(cudaMemcpyAsync(c->basis.p, basis.data(), m * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(c->in_basis.p, inb.data(), inb.size(), cudaMemcpyHostToDevice, c->stream));
+    if (nr_art) CUDA_TRY(cudaMemcpyAsync(c->art_row.p, c->art_rows_h.data(), nr_art * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    DState* s = c->h_st;
+    unsigned long long iter_keep = 0;
+    memset(s, 0, sizeof(DState));
+    s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld; s->n = n; s->nr_art = nr_art;
+    s->phase = 1; s->ncols = nr_art + n; shard_cols(c, s);
+    s->status = ST_RUNNING; s->last_selected = -1; s->iter = iter_keep; s->iter_limit = ~0ull; s->tag = '1';
+    s->rc = make_small(0, 1); s->pivot = make_small(0, 1);
+    init_heap_regions(c, s);
+    if (push_state(c)) return RELP_ERR_CUDA;
+    wire_dev(c);
+    LAUNCH(c, k_init_planes, c->sm_count * 8, RELP_THREADS, c->D, c->rhsn_d.p, c->rhsd_d.p);
+    LAUNCH(c, k_init_cost_row_artificial, 1, 1, c->D, c->rhsn_d.p, c->rhsd_d.p);
+    if (check_cuda(c)) return RELP_ERR_CUDA;
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0;
+    return RELP_OK;
+}
+
+// K5 + index shift; `m` may already have shrunk (row removal).
+static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbering of phase 1, size m */) {
+    int m = c->m, n = c->n;
+    for (auto& b : basis) b -= c->nr_art;
+    std::vector<unsigned char> inb(n, 0);
+    for (int b : basis) if (b >= 0 && b < n) inb[b] = 1;
+    std::vector<int> cost_rows;
+    for (int li = 0; li < c->mloc; li++) { int jb = basis[c->row_lo + li]; if (jb >= 0 && jb < n && c->cn[jb] != 0) cost_rows.push_back(li); }
+    CUDA_TRY(cudaMemcpyAsync(c->basis.p, basis.data(), m * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(c->in_basis.p, inb.data(), n, cudaMemcpyHostToDevice, c->stream));
+    if (!cost_rows.empty()) CUDA_TRY(cudaMemcpyAsync(c->cost_rows.p, cost_rows.data(), cost_rows.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    DState* s = c->h_st;
+    s->phase = 2; s->ncols = n; shard_cols(c, s); s->last_selected = -1; s->status = ST_RUNNING;
+    s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld;
+    if (push_state(c)) return RELP_ERR_CUDA;
+    c->phase = 2;
+    wire_dev(c);
+    LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
+    LAUNCH(c, k_recompute_cost_row, grid_for(c, m + 1, 2), RELP_THREADS, c->D, c->cost_rows.p, (int)cost_rows.size(), c->D.pn, c->D.pd);
+    if (c->world > 1) {
+        // partial sums of small values only: all-gather and add (exact) -- done by k_sum_cost_rows
+        set_error("multi-GPU hand-over not wired"); return RELP_ERR_COMM;
+    }
+    size_t z = (size_t)c->mloc * c->ld;
+    CUDA_TRY(cudaMemcpyAsync(c->xn.p + z, c->D.pn, (m + 1) * 8, cudaMemcpyDeviceToDevice, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(c->xd.p + z, c->D.pd, (m + 1) * 8, cudaMemcpyDeviceToDevice, c->stream));
+    if (check_cuda(c)) return RELP_ERR_CUDA;
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    if (c->h_st->err) return err_status(c->h_st);
+    return RELP_OK;
+}
+
+static int read_basis_host(relp_ctx* c, std::vector<int>& basis) {
+    basis.resize(c->m);
+    CUDA_TRY(cudaMemcpyAsync(basis.data(), c->basis.p, c->m * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+static int from_artificial(relp_ctx* c) {
+    if (!c->carry_ready || c->phase != 1) { set_error("no artificial tableau"); return RELP_ERR_ARGUMENT; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    std::vector<int> basis;
+    if (read_basis_host(c, basis)) return RELP_ERR_CUDA;
+    return handover_common(c, basis);
+}
+
+static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* rows) {
+    if (!c->carry_ready || c->phase != 1) { set_error("no artificial tableau"); return RELP_ERR_ARGUMENT; }
+    if (c->world > 1) { set_error("row removal is single-GPU only"); return RELP_ERR_COMM; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    int m = c->m, n = c->n;
+    std::vector<int> basis;
+    if (read_basis_host(c, basis)) return RELP_ERR_CUDA;
+    std::vector<int> newidx(m, -1), keep;
+    { size_t q = 0; for (int i = 0; i < m; i++) { if (q < (size_t)n_rows && rows[q] == i) { q++; continue; } newidx[i] = (int)keep.size(); keep.push_back(i); } }
+    int m2 = (int)keep.size();
+    // planes: kept rows + cost row; columns 0 and 1 + kept
+    std::vector<int> keep_row(keep), keep_col(m2 + 1);
+    keep_row.push_back(m);
+    keep_col[0] = 0; for (int k = 0; k < m2; k++) keep_col[1 + k] = 1 + keep[k];
+    int ld2 = (m2 + 1 + 15) / 16 * 16;
+    DBuf<int64_t> nxn, nxd;
+    if (nxn.alloc((size_t)(m2 + 1) * ld2) || nxd.alloc((size_t)(m2 + 1) * ld2)) return RELP_ERR_CUDA;
+    int* kr = c->scratch_i.p; int* kc = c->scratch_i.p + (m + 2);
+    CUDA_TRY(cudaMemcpyAsync(kr, keep_row.data(), keep_row.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(kc, keep_col.data(), keep_col.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    LAUNCH(c, k_gather_planes, c->sm_count * 8, RELP_THREADS, c->xn.p, c->xd.p, c->ld, nxn.p, nxd.p, ld2, m2 + 1, m2 + 1, kr, kc);
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    std::swap(c->xn.p, nxn.p); std::swap(c->xn.n, nxn.n); std::swap(c->xd.p, nxd.p); std::swap(c->xd.n, nxd.n);
+    // provider without the removed rows (filter/generic_wrapper.rs:224-300)
+    std::vector<long long> cp(n + 1, 0); std::vector<int> ri; std::vector<int64_t> an, ad;
+    for (int j = 0; j < n; j++) {
+        for (long long t = c->col_ptr[j]; t < c->col_ptr[j + 1]; t++) {
+            int ni = newidx[c->row_idx[t]];
+            if (ni >= 0) { ri.push_back(ni); an.push_back(c->an[t]); ad.push_back(c->ad[t]); }
+        }
+        cp[j + 1] = (long long)ri.size();
+    }
+    c->col_ptr = cp; c->row_idx = ri; c->an = an; c->ad = ad;
+    std::vector<int64_t> rn(m2), rd(m2); std::vector<int> b2(m2);
+    for (int k = 0; k < m2; k++) { rn[k] = c->rhsn[keep[k]]; rd[k] = c->rhsd[keep[k]]; b2[k] = basis[keep[k]]; }
+    c->rhsn = rn; c->rhsd = rd;
+    CUDA_TRY(cudaMemcpyAsync(c->col_ptr_d.p, cp.data(), (n + 1) * sizeof(long long), cudaMemcpyHostToDevice, c->stream));
+    if (!ri.empty()) {
+        CUDA_TRY(cudaMemcpyAsync(c->row_idx_d.p, ri.data(), ri.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(cudaMemcpyAsync(c->an_d.p, an.data(), an.size() * 8, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(cudaMemcpyAsync(c->ad_d.p, ad.data(), ad.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    }
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    c->m = m2; shard_rows(c, m2); c->ld = ld2;
+    basis = b2;
+    return handover_common(c, basis);
+}
+
+// phase_one.rs:223-260
+static int remove_artificial_basis_variables(relp_ctx* c) {
+    std::vector<int> basis;
+    if (read_basis_host(c, basis)) return RELP_ERR_CUDA;
+    std::vector<int> arts;
+    for (int b : basis) if (b < c->nr_art) arts.push_back(b);
+    std::sort(arts.begin(), arts.end());
+    c->rows_removed.clear();
+    if (arts.empty()) return RELP_OK;
+    LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'z', 1, 0);
+    int* d_best = c->scratch_i.p;
+    for (int a : arts) {
+        int pivot_row = c->art_rows_h[a];
+        int best = INT_MAX;
+        CUDA_TRY(cudaMemcpyAsync(d_best, &best, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
+        LAUNCH(c, k_cleanup_select, grid_for(c, c->n), RELP_THREADS, c->D, pivot_row, d_best);
+        CUDA_TRY(cudaMemcpyAsync(&best, d_best, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        if (best == INT_MAX) { c->rows_removed.push_back(a); continue; }   // sic: the artificial's index (phase_one.rs:251)
+        LAUNCH(c, k_iter_begin, 1, 1, c->D);
+        LAUNCH(c, k_compact, c->sm_count * 4, RELP_THREADS, c->D);
+        LAUNCH(c, k_set_pivot, 1, 1, c->st.p, best, pivot_row, 1);
+        enqueue_column_and_ratio(c, false);
+        enqueue_change_basis(c);
+        if (check_cuda(c)) return RELP_ERR_CUDA;
+    }
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    if (c->h_st->err) return err_status(c->h_st);
+    return RELP_OK;
+}
+
+// `keep_transient`: the source itself lives in the transient region (generated column, element),
+// so the export appends behind it instead of recycling the region.
+static int read_block_impl(relp_ctx* c, const int64_t* sn, const int64_t* sd, int sld, int nrows, int ncols,
+                           int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used,
+                           bool keep_transient = false) {
+    size_t total = (size_t)nrows * ncols;
+    if (limb_used) *limb_used = 0;
+    if (total == 0) return RELP_OK;
+    DBuf<int64_t> on, od;
+    if (on.alloc(total) || od.alloc(total)) return RELP_ERR_CUDA;
+    if (!keep_transient) LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    unsigned long long base = c->h_st->tr_top;
+    LAUNCH(c, k_export, grid_for(c, (long long)total), RELP_THREADS, c->D, sn, sd, sld, nrows, ncols, on.p, od.p, base);
+    if (check_cuda(c)) return RELP_ERR_CUDA;
+    CUDA_TRY(cudaMemcpyAsync(num, on.p, total * 8, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(den, od.p, total * 8, cudaMemcpyDeviceToHost, c->stream));
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    if (c->h_st->err) return err_status(c->h_st);
+    size_t used = (size_t)(c->h_st->tr_top - base);
+    if (limb_used) *limb_used = used;
+    if (used) {
+        if (!limbs || used > limb_cap) { set_error("limb buffer too small"); return RELP_ERR_ARGUMENT; }
+        CUDA_TRY(cudaMemcpyAsync(limbs, c->heap.p + base, used * 4, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        for (size_t e = 0; e < total; e++) if (den[e] == 0) {
+            uint32_t h = limbs[num[e]];
+            c->max_limbs = std::max(c->max_limbs, (int)std::max(h & 0x3fff, (h >> 14) & 0x3fff));
+        }
+    }
+    return RELP_OK;
+}
+
+static int solve_continue(relp_ctx* c, int64_t max_pivots) {
+    CUDA_TRY(cudaSetDevice(c->device));
+    int64_t remaining = max_pivots;
+    for (;;) {
+        if (c->stage == 3) return c->final_status;
+        if (c->stage == 0) { set_error("no solve in progress"); return RELP_ERR_ARGUMENT; }
+        if (sync_state(c)) return RELP_ERR_CUDA;
+        unsigned long long before = c->h_st->iter;
+        int rule = c->stage == 1 ? c->rule1 : c->rule2;
+        int st = run_loop(c, rule, remaining, c->stage == 1 ? '1' : '2');
+        if (st < 0) { c->stage = 3; c->final_status = st; return st; }
+        if (remaining >= 0) remaining -= (int64_t)(c->h_st->iter - before);
+        if (st == RELP_OK) return RELP_OK;                       // budget reached
+        if (c->stage == 1) {
+            if (st == RELP_UNBOUNDED) { c->stage = 3; c->final_status = RELP_ERR_PHASE1_UNBOUNDED; return c->final_status; }
+            // phase 1 finished: feasible iff the artificial objective is exactly zero (phase_one.rs:146-167)
+            int64_t on, od; size_t used = 0; uint32_t limbs[2 * RELP_OPL + 2];
+            int rc = read_block_impl(c, c->xn.p + (size_t)c->mloc * c->ld, c->xd.p + (size_t)c->mloc * c->ld, c->ld, 1, 1,
+                                     &on, &od, limbs, sizeof(limbs) / 4, &used);
+            if (rc) return rc;
+            if (!(on == 0 && od == 1)) { c->stage = 3; c->final_status = RELP_INFEASIBLE; return RELP_INFEASIBLE; }
+            rc = remove_artificial_basis_variables(c);
+            if (rc) { c->stage = 3; c->final_status = rc; return rc; }
+            if (c->rows_removed.empty()) rc = from_artificial(c);
+            else rc = from_artificial_remove_rows(c, (int)c->rows_removed.size(), c->rows_removed.data());
+            if (rc) { c->stage = 3; c->final_status = rc; return rc; }
+            c->stage = 2;
+            if (c->stop_at_handover) { c->stop_at_handover = false; return RELP_OK; }
+            continue;
+        }
+        c->stage = 3; c->final_status = st;
+        return st;
+    }
+}
+
+extern "C" {
+
+int relp_carry_create_partially_artificial(relp_ctx* c, int32_t n_piv, const int32_t* piv_rows, const int32_t* piv_cols) {
+    if (!c) return RELP_ERR_ARGUMENT;
+    c->stage = 0;
+    return create_partially_artificial(c, n_piv, piv_rows, piv_cols);
+}
+int relp_carry_from_artificial(relp_ctx* c) { return c ? from_artificial(c) : RELP_ERR_ARGUMENT; }
+int relp_carry_from_artificial_remove_rows(relp_ctx* c, int32_t n_rows, const int32_t* sorted_rows) {
+    return c ? from_artificial_remove_rows(c, n_rows, sorted_rows) : RELP_ERR_ARGUMENT;
+}
+
+int relp_price(relp_ctx* c, int rule, int32_t* j_out, int64_t* rc_num, int64_t* rc_den, uint32_t* limbs, size_t limb_cap) {
+    if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)(c->phase == 1 ? '1' : '2'), 1, 0);
+    LAUNCH(c, k_iter_begin, 1, 1, c->D);
+    LAUNCH(c, k_compact, c->sm_count * 4, RELP_THREADS, c->D);
+    enqueue_price(c, rule);
+    if (check_cuda(c)) return RELP_ERR_CUDA;
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    if (c->h_st->err) return err_status(c->h_st);
+    if (c->h_st->status == ST_NO_COLUMN) return RELP_OPTIMAL;
+    if (j_out) *j_out = c->h_st->j;
+    if (rc_num && rc_den) {
+        Val rc = c->h_st->rc;
+        rc_num[0] = rc.n; rc_den[0] = rc.d;
+        if (rc.d == 0) {
+            uint32_t h; CUDA_TRY(cudaMemcpy(&h, c->heap.p + rc.n, 4, cudaMemcpyDeviceToHost));
+            size_t w = 1 + (h & 0x3fff) + ((h >> 14) & 0x3fff);
+            if (!limbs || w > limb_cap) { set_error("limb buffer too small"); return RELP_ERR_ARGUMENT; }
+            CUDA_TRY(cudaMemcpy(limbs, c->heap.p + rc.n, w * 4, cudaMemcpyDeviceToHost));
+            rc_num[0] = 0;
+        }
+    }
+    return RELP_OK;
+}
+
+int relp_generate_column(relp_ctx* c, int32_t j) {
+    if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    if (j < 0 || j >= c->h_st->ncols) return RELP_ERR_ARGUMENT;
+    LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)(c->phase == 1 ? '1' : '2'), 1, 0);
+    LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
+    LAUNCH(c, k_set_pivot, 1, 1, c->st.p, (int)j, -1, 0);
+    LAUNCH(c, k_reprice_selected, 1, 1, c->D);
+    LAUNCH(c, k_gen_column, grid_for(c, c->mloc + 1), RELP_THREADS, c->D);
+    if (check_cuda(c)) return RELP_ERR_CUDA;
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    return c->h_st->err ? err_status(c->h_st) : RELP_OK;
+}
+
+int relp_ratio_test(relp_ctx* c, int32_t* r_out) {
+    if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    int gb = clampi(cdiv(c->mloc, RELP_THREADS * 4), 1, MAX_PARTIAL_BLOCKS);
+    LAUNCH(c, k_argmin_partial, gb, RELP_THREADS, c->D, (int)ARG_RATIO);
+    if (c->world == 1) LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, gb, 0, -1, 0);
+    else {
+        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, gb, 0, c->rank, 0);
+        g_nccl.AllGather(c->gather.p + c->rank, c->gather.p, sizeof(Cand), NCCL_INT8, c->comm, c->stream);
+        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, c->world, 1, -1, 0);
+    }
+    if (check_cuda(c)) return RELP_ERR_CUDA;
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    if (c->h_st->err) return err_status(c->h_st);
+    if (c->h_st->status == ST_NO_ROW) { LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, c->h_st->tag, 1, 0); return RELP_UNBOUNDED; }
+    if (r_out) *r_out = c->h_st->r;
+    return RELP_OK;
+}
+
+int relp_change_basis(relp_ctx* c, int32_t r, int32_t* leaving_out) {
+    if (!c || !c->carry_ready || r < 0 || r >= c->m) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    LAUNCH(c, k_set_pivot, 1, 1, c->st.p, -1, (int)r, 0);
+    enqueue_change_basis(c);
+    if (check_cuda(c)) return RELP_ERR_CUDA;
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    if (c->h_st->err) return err_status(c->h_st);
+    if (leaving_out) *leaving_out = c->h_st->leaving;
+    return RELP_OK;
+}
+
+int relp_generate_element(relp_ctx* c, int32_t i, int32_t j, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap) {
+    if (!c || !c->carry_ready || i < c->row_lo || i >= c->row_lo + c->mloc) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
+    LAUNCH(c, k_generate_element, 1, 1, c->D, (int)i, (int)j, c->qn.p + c->mloc, c->qd.p + c->mloc);
+    size_t used;
+    return read_block_impl(c, c->qn.p + c->mloc, c->qd.p + c->mloc, 1, 1, 1, num, den, limbs, limb_cap, &used, true);
+}
+
+int relp_iterate(relp_ctx* c, int rule, int64_t max_iters) {
+    if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    return run_loop(c, rule, max_iters, c->phase == 1 ? '1' : '2');
+}
+
+int relp_solve_relaxation(relp_ctx* c, int rule_phase1, int rule_phase2, int32_t n_piv, const int32_t* piv_rows,
+                          const int32_t* piv_cols, int64_t max_pivots) {
+    if (!c) return RELP_ERR_ARGUMENT;
+    int rc = create_partially_artificial(c, n_piv, piv_rows, piv_cols);
+    if (rc) return rc;
+    c->rule1 = rule_phase1; c->rule2 = rule_phase2; c->stage = 1; c->stop_at_handover = false;
+    return solve_continue(c, max_pivots);
+}
+int relp_solve_continue(relp_ctx* c, int64_t max_pivots) { return c ? solve_continue(c, max_pivots) : RELP_ERR_ARGUMENT; }
+int relp_solve_to_handover(relp_ctx* c, int rule_phase1, int32_t n_piv, const int32_t* piv_rows, const int32_t* piv_cols) {
+    if (!c) return RELP_ERR_ARGUMENT;
+    int rc = create_partially_artificial(c, n_piv, piv_rows, piv_cols);
+    if (rc) return rc;
+    c->rule1 = rule_phase1; c->rule2 = RELP_STEEPEST_DESCENT; c->stage = 1; c->stop_at_handover = true;
+    return solve_continue(c, -1);
+}
+
+int relp_dims(relp_ctx* c, int32_t* m, int32_t* n, int32_t* nr_artificial, int32_t* phase) {
+    if (!c) return RELP_ERR_ARGUMENT;
+    if (m) *m = c->m; if (n) *n = c->n; if (nr_artificial) *nr_artificial = c->nr_art; if (phase) *phase = c->phase;
+    return RELP_OK;
+}
+int relp_read_basis(relp_ctx* c, int32_t* out) {
+    if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaMemcpyAsync(out, c->basis.p, c->m * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return RELP_OK;
+}
+int relp_read_block(relp_ctx* c, int32_t row0, int32_t nrows, int32_t col0, int32_t ncols,
+                    int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used) {
+    if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
+    // rows are LOCAL rows of this rank's shard followed by the cost row (local index mloc)
+    if (row0 < 0 || nrows < 0 || row0 + nrows > c->mloc + 1 || col0 < 0 || ncols < 0 || col0 + ncols > c->m + 1) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    size_t off = (size_t)row0 * c->ld + col0;
+    return read_block_impl(c, c->xn.p + off, c->xd.p + off, c->ld, nrows, ncols, num, den, limbs, limb_cap, limb_used);
+}
+int relp_read_carry(relp_ctx* c, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used) {
+    return c ? relp_read_block(c, 0, c->mloc + 1, 0, c->m + 1, num, den, limbs, limb_cap, limb_used) : RELP_ERR_ARGUMENT;
+}
+int relp_read_b(relp_ctx* c, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used) {
+    return c ? relp_read_block(c, 0, c->mloc, 0, 1, num, den, limbs, limb_cap, limb_used) : RELP_ERR_ARGUMENT;
+}
+int relp_read_minus_pi(relp_ctx* c, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used) {
+    return c ? relp_read_block(c, c->mloc, 1, 1, c->m, num, den, limbs, limb_cap, limb_used) : RELP_ERR_ARGUMENT;
+}
+int relp_read_minus_objective(relp_ctx* c, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used) {
+    return c ? relp_read_block(c, c->mloc, 1, 0, 1, num, den, limbs, limb_cap, limb_used) : RELP_ERR_ARGUMENT;
+}
+int relp_read_column(relp_ctx* c, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used) {
+    if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    return read_block_impl(c, c->dn.p, c->dd.p, 1, c->mloc, 1, num, den, limbs, limb_cap, limb_used, true);
+}
+int64_t relp_log_size(relp_ctx* c) {
+    if (!c || !c->carry_ready) return 0;
+    cudaSetDevice(c->device);
+    if (sync_state(c)) return 0;
+    return (int64_t)std::min<unsigned long long>(c->h_st->iter, c->log.n);
+}
+int relp_read_log(relp_ctx* c, int64_t first, int64_t count, relp_iter_log* out) {
+    if (!c || first < 0 || count < 0 || (size_t)(first + count) > c->log.n) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    static_assert(sizeof(relp_iter_log) == sizeof(LogEntry), "log layout");
+    if (count) CUDA_TRY(cudaMemcpy(out, c->log.p + first, count * sizeof(LogEntry), cudaMemcpyDeviceToHost));
+    return RELP_OK;
+}
+int relp_stats_get(relp_ctx* c, relp_stats* out) {
+    if (!c || !out) return RELP_ERR_ARGUMENT;
+    memset(out, 0, sizeof(*out));
+    out->m = c->m; out->n = c->n; out->nr_artificial = c->nr_art; out->phase = c->phase;
+    out->kernel_launches = c->launches; out->loop_ms = c->loop_ms; out->max_limbs = c->max_limbs;
+    if (c->carry_ready) {
+        cudaSetDevice(c->device);
+        if (sync_state(c)) return RELP_ERR_CUDA;
+        const DState* s = c->h_st;
+        out->pivots = s->iter; out->escalated = s->escalated; out->sum_T = s->sum_T; out->sum_S = s->sum_S;
+        out->sum_TS = s->sum_TS; out->heap_peak_words = s->pool_peak; out->compactions = s->compactions;
+    }
+    return RELP_OK;
+}
+int relp_rows_removed(relp_ctx* c, int32_t* out, int32_t cap) {
+    if (!c) return RELP_ERR_ARGUMENT;
+    int n = (int)c->rows_removed.size();
+    for (int i = 0; i < n && i < cap; i++) out[i] = c->rows_removed[i];
+    return n;
+}
+
+}  // extern "C"

@@ -1,0 +1,54 @@
+// TEST INFRASTRUCTURE ONLY.  A sequential stand-in for the handful of CUDA runtime calls and
+// device intrinsics that rust-lp_b200/csrc/*.cu use, so that the HOST control flow of the C ABI
+// (phase state machine, hand-over, row removal, index bookkeeping) and the kernels' indexing can
+// be exercised by `pytest -m "not gpu"` in a container without a GPU.  Every launch runs as one
+// block of one thread (all kernels are grid-stride loops), so this checks logic, not parallelism.
+// The product library (librelp_b200.so) is never built with RELP_EMUL and has no CPU path.
+#pragma once
+#include <cstdlib>
+#include <cstring>
+#include <cstdint>
+
+#define __global__
+#define __device__
+#define __host__
+#define __forceinline__ inline
+#define __noinline__
+#define __shared__ static
+
+struct emul_dim3 { unsigned x, y, z; };
+static emul_dim3 blockIdx = {0, 0, 0}, threadIdx = {0, 0, 0}, blockDim = {1, 1, 1}, gridDim = {1, 1, 1};
+struct int2 { int x, y; };
+static inline int2 make_int2(int x, int y) { int2 r; r.x = x; r.y = y; return r; }
+
+template <typename T> static inline T atomicAdd(T* p, T v) { T o = *p; *p += v; return o; }
+static inline int atomicOr(int* p, int v) { int o = *p; *p |= v; return o; }
+static inline int atomicMin(int* p, int v) { int o = *p; if (v < o) *p = v; return o; }
+template <typename T> static inline T __shfl_down_sync(unsigned, T v, int) { return v; }
+static inline void __syncthreads() {}
+
+typedef int cudaError_t;
+typedef void* cudaStream_t;
+typedef void* cudaEvent_t;
+enum { cudaSuccess = 0, cudaStreamNonBlocking = 1 };
+enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice };
+struct cudaDeviceProp { int multiProcessorCount; };
+static inline cudaError_t cudaGetDeviceCount(int* n) { *n = 1; return 0; }
+static inline cudaError_t cudaSetDevice(int) { return 0; }
+static inline cudaError_t cudaGetDeviceProperties(cudaDeviceProp* p, int) { p->multiProcessorCount = 2; return 0; }
+static inline const char* cudaGetErrorString(cudaError_t) { return "emulated"; }
+static inline cudaError_t cudaGetLastError() { return 0; }
+static inline cudaError_t cudaMalloc(void** p, size_t n) { *p = calloc(1, n); return *p ? 0 : 2; }
+static inline cudaError_t cudaFree(void* p) { free(p); return 0; }
+static inline cudaError_t cudaMallocHost(void** p, size_t n) { *p = calloc(1, n); return *p ? 0 : 2; }
+static inline cudaError_t cudaFreeHost(void* p) { free(p); return 0; }
+static inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, cudaMemcpyKind) { memmove(d, s, n); return 0; }
+static inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, cudaMemcpyKind, cudaStream_t) { memmove(d, s, n); return 0; }
+static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t* s, int) { *s = (void*)1; return 0; }
+static inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return 0; }
+static inline cudaError_t cudaStreamDestroy(cudaStream_t) { return 0; }
+static inline cudaError_t cudaEventCreate(cudaEvent_t* e) { *e = (void*)1; return 0; }
+static inline cudaError_t cudaEventDestroy(cudaEvent_t) { return 0; }
+static inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return 0; }
+static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return 0; }
+static inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t, cudaEvent_t) { *ms = 0; return 0; }

@@ -1,0 +1,139 @@
+"""Parity checks shared by the GPU suite (tests/test_gpu_parity.py, the real librelp_b200.so on a
+B200) and the CPU-only logic suite (tests/test_emul_logic.py, the same sources compiled against
+tests/native/cuda_emul.h).  Every check drives the C ABI and compares with the oracle."""
+from fractions import Fraction as Fr
+
+import numpy as np
+
+from helpers import pa_from_lp, log_tuples
+from oracle import coracle, pyref
+from rust_lp_b200 import capi
+
+STATUS = {coracle.OPTIMAL: capi.OPTIMAL, coracle.UNBOUNDED: capi.UNBOUNDED, coracle.INFEASIBLE: capi.INFEASIBLE}
+
+
+def oracle_log(o):
+    return [(chr(int(t)), int(j), int(r), int(l), int(T), int(S)) for (t, j, r, l, T, S) in o.log()]
+
+
+def assert_same_carry(c, o, what=""):
+    got = c.carry()
+    exp = o.carry()
+    assert got[3] == exp[3], f"basis differs {what}"
+    assert got[0] == exp[0], f"-obj differs {what}: {got[0]} vs {exp[0]}"
+    assert got[1] == exp[1], f"-pi differs {what}"
+    assert got[2] == exp[2], f"b differs {what}"
+    assert got[4] == exp[4], f"B^-1 differs {what}"
+
+
+def check_full_solve(pa, lib_path, rule1=1, rule2=2, heap_words=1 << 22, expect_escalation=None):
+    """Whole solve through relp_solve_relaxation: identical status, pivot log (entering column,
+    row, leaving column, T, S per pivot), objective, basic solution and every Carry entry."""
+    o = coracle.COracle(pa)
+    st_o = o.solve(rule1, rule2)
+    c = capi.Carry(pa, heap_words=heap_words, lib_path=lib_path)
+    st = c.solve_relaxation(rule1, rule2)
+    assert st == STATUS[st_o], (st, st_o)
+    assert c.log() == oracle_log(o)
+    if st_o != coracle.INFEASIBLE:
+        assert_same_carry(c, o, "at termination")
+        assert c.get_objective_function_value() == o.objective()
+        assert c.current_bfs() == o.current_bfs()
+    assert c.rows_removed() == [] or o.m < pa.m
+    s = c.stats()
+    if expect_escalation is True:
+        assert s.escalated > 0 and o.max_bits() > 63
+    if expect_escalation is False:
+        assert s.escalated == 0
+    c.close()
+    return s, o
+
+
+def check_resumable(pa, lib_path, chunk=3, rule1=1, rule2=2):
+    """Pivot budget: solve in chunks of `chunk` pivots; the Carry equals the oracle's after each."""
+    o = coracle.COracle(pa); o.begin(rule1, rule2)
+    c = capi.Carry(pa, heap_words=1 << 22, lib_path=lib_path)
+    st = c.solve_relaxation(rule1, rule2, max_pivots=chunk)
+    st_o = o.advance(chunk)
+    for _ in range(10000):
+        assert (st == capi.OK) == (st_o == coracle.RUNNING)
+        assert c.log() == oracle_log(o)
+        if st_o == coracle.INFEASIBLE:
+            break
+        assert_same_carry(c, o, f"after {o.nr_pivots} pivots")
+        if st != capi.OK:
+            break
+        st = c.solve_continue(chunk); st_o = o.advance(chunk)
+    assert st == STATUS.get(st_o, capi.OK)
+    c.close()
+
+
+def check_stepwise(lp, lib_path, rule1=1, rule2=2):
+    """Trait-level calls (price / generate_column / ratio test / change_basis), one at a time,
+    against the Python restatement: reduced cost, generated column, pivot row, leaving column and
+    the full Carry after every pivot.  Phase 1 only up to its end, then hand-over and phase 2."""
+    pa = pa_from_lp(lp)
+    t = pyref.partially_artificial_tableau(lp)
+    c = capi.Carry(pa, heap_words=1 << 22, lib_path=lib_path)
+    c.create_for_partially_artificial()
+
+    def same(tab):
+        got = c.carry()
+        k = tab.carry
+        assert got[0] == k.minus_obj and got[1] == list(k.minus_pi) and got[2] == list(k.b)
+        assert got[3] == list(k.basis_indices) and got[4] == [dict(r) for r in k.rows]
+
+    def loop(tab, rule, tag):
+        pr = pyref.PivotRule(rule)
+        for _ in range(10000):
+            sel = pr.select(tab)
+            got = c.select_primal_pivot_column(rule)
+            if sel is None:
+                assert got is None
+                return "done"
+            assert got == (sel[0], sel[1]), (got, sel)
+            col = tab.generate_column(sel[0])
+            assert c.generate_column(sel[0]) == col
+            r = tab.select_primal_pivot_row(col)
+            assert c.select_primal_pivot_row() == r
+            if r is None:
+                return "unbounded"
+            leaving = tab.carry.basis_indices[r]
+            tab.bring_into_basis(sel[0], r, col, sel[1], tag)
+            assert c.change_basis(r) == leaving
+            same(tab)
+        raise AssertionError("no termination")
+
+    same(t)
+    assert loop(t, rule1, "1") == "done"
+    if t.carry.minus_obj != 0:
+        c.close(); return "infeasible"
+    if any(j < t.nr_art for j in t.basis):
+        c.close(); return "artificials left"        # covered by check_full_solve
+    t2 = pyref.to_phase_two(t, [])
+    c.from_artificial()
+    same(t2)
+    res = loop(t2, rule2, "2")
+    c.close()
+    return res
+
+
+def check_fixture(make_lp, art, bfs, opt, obj, lib_path):
+    """src/tests/problem_1.rs / problem_2.rs: the pinned Carry states, FirstProfitable in both phases."""
+    pa = pa_from_lp(make_lp())
+    c = capi.Carry(pa, heap_words=1 << 20, lib_path=lib_path)
+    c.create_for_partially_artificial()
+    _check_state(c.carry(), art)
+    assert c.solve_to_handover(capi.FIRST_PROFITABLE) == capi.OK
+    _check_state(c.carry(), bfs)
+    assert c.iterate(capi.FIRST_PROFITABLE) == capi.OPTIMAL
+    assert c.current_bfs() == opt and c.get_objective_function_value() == obj
+    c.close()
+
+
+def _check_state(state, expected):
+    mo, mpi, b, basis, rows = state
+    emo, empi, eb, ebasis, erows = expected
+    assert mo == emo and list(mpi) == empi and list(b) == eb and list(basis) == ebasis
+    m = len(eb)
+    assert [[r.get(k, Fr(0)) for k in range(m)] for r in rows] == [[Fr(x) for x in r] for r in erows]

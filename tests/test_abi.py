@@ -1,0 +1,48 @@
+"""CPU: the CUDA library builds (nvcc cross-compiles sm_100a without a GPU), loads, exports every
+symbol include/relp_b200.h declares, and refuses to run without a device (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+import __graft_entry__ as entry
+from rust_lp_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    entry.build_library()
+    return C.CDLL(capi.LIB_PATH)
+
+
+def test_header_symbols_match_binding_list():
+    hdr = open(os.path.join(ROOT, "include", "relp_b200.h")).read()
+    declared = set(re.findall(r"\b(relp_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(capi.SYMBOLS)
+
+
+def test_library_exports_every_symbol(lib):
+    for s in capi.SYMBOLS:
+        assert hasattr(lib, s), s
+    assert lib.relp_abi_version() == 1
+
+
+def test_no_cpu_fallback(lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    L = capi.load_library()
+    assert not L.relp_create(0, 0, 1, 1 << 20)
+    assert b"no CUDA device" in L.relp_last_error()
+    from rust_lp_b200.synth import synthetic_lp
+    with pytest.raises(capi.RelpError):
+        capi.Carry(synthetic_lp(30, 60, 5))
+
+
+def test_sass_is_sm100(lib):
+    import subprocess
+    out = subprocess.run(["cuobjdump", "-lelf", capi.LIB_PATH], capture_output=True, text=True).stdout
+    assert "sm_100a" in out

@@ -1,0 +1,129 @@
+"""The product's __host__ __device__ rational arithmetic (rust-lp_b200/csrc/relp_arith.cuh), built
+for the host with g++, against fractions.Fraction.  CPU only: this is how the device number code
+is validated before it ever runs in a kernel.  Canonical-form KATs follow
+/root/reference/src/data/number_types/rational/mod.rs:14-104."""
+import ctypes as C
+import math
+import os
+import random
+import subprocess
+from fractions import Fraction as Fr
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SRC = os.path.join(ROOT, "tests", "native", "arith_host_test.cpp")
+INC = os.path.join(ROOT, "rust-lp_b200", "csrc")
+OUT = os.path.join(ROOT, "tests", "native", "_build", "libarith_host_test.so")
+
+
+@pytest.fixture(scope="module")
+def L():
+    os.makedirs(os.path.dirname(OUT), exist_ok=True)
+    deps = [SRC, os.path.join(INC, "relp_arith.cuh")]
+    if not os.path.exists(OUT) or any(os.path.getmtime(d) > os.path.getmtime(OUT) for d in deps):
+        subprocess.check_call(["g++", "-O1", "-g", "-std=c++17", "-fPIC", "-shared", "-fsanitize=undefined",
+                               "-fno-sanitize-recover=undefined", "-I", INC, "-x", "c++", SRC, "-o", OUT])
+    lib = C.CDLL(OUT)
+    lib.t_gcd64.restype = C.c_uint64
+    lib.t_gcd64.argtypes = [C.c_uint64, C.c_uint64]
+    lib.t_reset()
+    return lib
+
+
+def limbs(x):
+    out = []
+    while x:
+        out.append(x & 0xffffffff); x >>= 32
+    return np.array(out if out else [0], dtype=np.uint32), len(out)
+
+
+def mk(lib, f):
+    f = Fr(f)
+    n, nn = limbs(abs(f.numerator)); d, nd = limbs(f.denominator)
+    out = (C.c_int64 * 2)()
+    lib.t_make(-1 if f < 0 else 1, n.ctypes.data_as(C.c_void_p), nn, d.ctypes.data_as(C.c_void_p), nd, out)
+    return out
+
+
+def rd(lib, v):
+    if v[1] > 0:
+        return Fr(v[0], v[1])
+    assert v[1] == 0
+    buf = np.zeros(1 + 2 * 16384, dtype=np.uint32)
+    w = lib.t_read(v, buf.ctypes.data_as(C.c_void_p))
+    h = int(buf[0]); nn = h & 0x3fff; nd = (h >> 14) & 0x3fff
+    assert w == 1 + nn + nd
+    num = sum(int(buf[1 + i]) << (32 * i) for i in range(nn))
+    den = sum(int(buf[1 + nn + i]) << (32 * i) for i in range(nd))
+    f = Fr(num, den)
+    assert f.numerator == num and f.denominator == den, "stored value not canonical"
+    assert buf[nn] != 0 and buf[nn + nd] != 0, "leading zero limb"
+    assert num > 2**63 - 1 or den > 2**63 - 1, "big representation of a value that fits small"
+    return -f if h >> 31 else f
+
+
+def rnd_frac(rnd, bits):
+    nb = rnd.choice([1, 3, 8, 20, 31, 32, 33, 50, 62, 63, 64, 65, 90, 127, 128, 200, 500])
+    nb = min(nb, bits)
+    db = rnd.choice([0, 0, 1, 5, 31, 32, 40, 63, 64, 100, 300])
+    db = min(db, bits)
+    n = rnd.getrandbits(nb) * rnd.choice([1, -1])
+    d = rnd.getrandbits(db) + 1 if db else 1
+    if rnd.random() < 0.1:
+        n = 0
+    return Fr(n, d)
+
+
+def test_gcd64(L):
+    rnd = random.Random(1)
+    for _ in range(3000):
+        a = rnd.getrandbits(rnd.randint(0, 64)); b = rnd.getrandbits(rnd.randint(0, 64))
+        assert L.t_gcd64(a, b) == math.gcd(a, b)
+
+
+def test_canonical_form_kats(L):
+    """rational/mod.rs:26-60: 3/2 == 6/4, 0/2 == 0/5, 3/2 + 6/4 = 3, 3/2 * 6/4 = 9/4, (3/2)/(6/4) = 1"""
+    a = mk(L, Fr(3, 2)); b = mk(L, Fr(6, 4)); z = mk(L, 0); one = mk(L, 1)
+    assert (a[0], a[1]) == (b[0], b[1]) == (3, 2)
+    assert (z[0], z[1]) == (0, 1)
+    out = (C.c_int64 * 2)()
+    L.t_fma(a, b, one, 1, out); assert (out[0], out[1]) == (3, 1)
+    L.t_fma(z, a, b, 1, out); assert (out[0], out[1]) == (9, 4)
+    L.t_div(a, b, out); assert (out[0], out[1]) == (1, 1)
+    L.t_fma(a, b, one, -1, out); assert (out[0], out[1]) == (0, 1)
+
+
+@pytest.mark.parametrize("bits,seed", [(40, 0), (64, 1), (64, 2), (130, 3), (500, 4), (500, 5)])
+def test_fma_div_cmp_random(L, bits, seed):
+    rnd = random.Random(seed)
+    out = (C.c_int64 * 2)()
+    for it in range(1500):
+        if it % 200 == 0:
+            L.t_reset()
+        x, a, b = (rnd_frac(rnd, bits) for _ in range(3))
+        if rnd.random() < 0.2:       # force cancellations / shared factors
+            x = a * b * rnd.choice([1, -1]) if rnd.random() < 0.5 else x * Fr(a.denominator, max(1, b.denominator))
+        vx, va, vb = mk(L, x), mk(L, a), mk(L, b)
+        assert rd(L, vx) == x and rd(L, va) == a
+        s = rnd.choice([1, -1])
+        L.t_fma(vx, va, vb, s, out)
+        assert rd(L, out) == x + s * a * b, (x, a, b, s)
+        if b != 0:
+            L.t_div(vx, vb, out)
+            assert rd(L, out) == x / b, (x, b)
+        assert L.t_cmp(vx, va) == (x > a) - (x < a)
+        assert L.t_sign(vx) == (x > 0) - (x < 0)
+        assert L.t_err() == 0
+
+
+def test_limb_capacity_is_reported(L):
+    L.t_reset()
+    opl = L.t_opl()
+    big = Fr(2 ** (32 * opl - 1) + 1, 3)
+    v = mk(L, big)
+    out = (C.c_int64 * 2)()
+    L.t_fma(mk(L, 0), v, v, 1, out)          # square needs 2*opl limbs -> capacity error, not garbage
+    assert L.t_err() & 1
+    L.t_reset()

@@ -1,0 +1,117 @@
+"""Parity tests proper: the real librelp_b200.so on a B200, through the C ABI, against the oracle.
+Bit-exact (integer/rational work): identical pivot sequence, every Carry entry, objective, solution."""
+import os
+from fractions import Fraction as Fr
+
+import pytest
+
+import parity
+from helpers import pa_from_lp, problem_1_lp, problem_2_lp, feasible_lp, random_lp
+from rust_lp_b200 import capi
+from rust_lp_b200.synth import synthetic_lp
+from test_oracle_fixtures import P1_ART, P1_BFS, P2_ART, P2_BFS
+
+pytestmark = pytest.mark.gpu
+LIB = capi.LIB_PATH
+
+
+def test_library_is_the_cuda_build():
+    import torch
+    assert torch.cuda.is_available()
+    assert os.path.exists(LIB), "librelp_b200.so missing: the product has no fallback"
+
+
+@pytest.mark.parametrize("make_lp,art,bfs,opt,obj", [
+    (problem_2_lp, P2_ART, P2_BFS, [(1, Fr(1, 2)), (3, Fr(5, 2)), (4, Fr(3, 2))], Fr(9, 2)),
+    (problem_1_lp, P1_ART, P1_BFS, [(0, Fr(4)), (2, Fr(6)), (5, Fr(2))], Fr(58)),
+])
+def test_reference_fixtures(make_lp, art, bfs, opt, obj):
+    parity.check_fixture(make_lp, art, bfs, opt, obj, LIB)
+
+
+@pytest.mark.parametrize("seed", range(30))
+def test_full_solve_random(seed):
+    lp = feasible_lp(seed, 3, 1, 3, 2, 10, frac=(seed % 2 == 0), dup_rows=(1 if seed % 5 == 0 else 0))
+    parity.check_full_solve(pa_from_lp(lp), LIB)
+
+
+@pytest.mark.parametrize("seed", range(100, 110))
+def test_full_solve_random_unfiltered(seed):
+    lp = random_lp(seed, 2, 1, 3, 2, 8, frac=(seed % 2 == 0))
+    parity.check_full_solve(pa_from_lp(lp), LIB)
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_stepwise_traits(seed):
+    lp = feasible_lp(seed + 50, 2, 1, 3, 1, 8, frac=(seed % 2 == 1))
+    parity.check_stepwise(lp, LIB)
+
+
+@pytest.mark.parametrize("seed", range(2))
+def test_resumable(seed):
+    lp = feasible_lp(seed + 70, 3, 0, 3, 2, 9, frac=True)
+    parity.check_resumable(pa_from_lp(lp), LIB)
+
+
+@pytest.mark.parametrize("m,n,k", [(60, 400, 6), (200, 2000, 20), (2000, 20000, 20)])
+def test_synthetic_tu(m, n, k):
+    """BASELINE config 5a scaled down to sizes the oracle finishes: int64 tier, no escalation."""
+    parity.check_full_solve(synthetic_lp(m, n, k, "tu"), LIB, expect_escalation=False, heap_words=1 << 24)
+
+
+def test_synthetic_growth():
+    parity.check_full_solve(synthetic_lp(80, 400, 10, "growth"), LIB, expect_escalation=True)
+
+
+def test_escalation_to_multi_limb():
+    parity.check_full_solve(pa_from_lp(feasible_lp(0, 6, 2, 6, 4, 24, frac=True, maxval=9, density=0.4)), LIB,
+                            expect_escalation=True)
+    s, o = parity.check_full_solve(pa_from_lp(feasible_lp(0, 10, 2, 10, 6, 40, frac=True, maxval=9, density=0.4)), LIB,
+                                   expect_escalation=True)
+    assert o.max_bits() > 128 and s.max_limbs >= 5
+
+
+def test_limb_pool_compaction():
+    pa = pa_from_lp(feasible_lp(0, 10, 2, 10, 6, 40, frac=True, maxval=9, density=0.4))
+    s, _ = parity.check_full_solve(pa, LIB, heap_words=1 << 17, expect_escalation=True)
+    assert s.compactions > 0
+
+
+def test_heap_exhaustion_is_an_error_not_garbage():
+    pa = pa_from_lp(feasible_lp(0, 10, 2, 10, 6, 40, frac=True, maxval=9, density=0.4))
+    c = capi.Carry(pa, heap_words=1 << 11)
+    with pytest.raises(capi.RelpError) as e:
+        c.solve_relaxation()
+    assert e.value.status == capi.ERR_HEAP_EXHAUSTED
+
+
+def test_full_size_properties():
+    """BASELINE config 5a at full size (m=20k, n=200k): the oracle cannot finish it, so check
+    size-independent properties of the optimum: primal feasibility A x <= b, x >= 0 (exact, int64
+    tier), dual feasibility (no negative reduced cost: the loop's own termination), objective
+    = c.x, and that a second solve reproduces the identical pivot log (determinism)."""
+    import numpy as np
+    pa = synthetic_lp(20000, 200000, 20, "tu")
+    c = capi.Carry(pa, heap_words=1 << 24)
+    assert c.solve_relaxation() == capi.OPTIMAL
+    s = c.stats()
+    assert s.escalated == 0
+    bfs = c.current_bfs()
+    x = np.zeros(pa.n, dtype=object)
+    for j, v in bfs:
+        assert v > 0
+        x[j] = v
+    # A x = b with slacks included (every row has its slack column): check row sums exactly
+    ax = [Fr(0)] * pa.m
+    for j, v in bfs:
+        for t in range(int(pa.col_ptr[j]), int(pa.col_ptr[j + 1])):
+            ax[int(pa.row_idx[t])] += v * Fr(int(pa.val_num[t]), int(pa.val_den[t]))
+    assert all(ax[i] == Fr(int(pa.rhs_num[i]), int(pa.rhs_den[i])) for i in range(pa.m))
+    obj = sum(v * Fr(int(pa.cost_num[j]), int(pa.cost_den[j])) for j, v in bfs)
+    assert obj == c.get_objective_function_value()
+    log1 = c.log()
+    c.close()
+    c2 = capi.Carry(pa, heap_words=1 << 24)
+    assert c2.solve_relaxation() == capi.OPTIMAL
+    assert c2.log() == log1
+    c2.close()
