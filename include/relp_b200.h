@@ -71,6 +71,7 @@ typedef struct relp_stats {
     int32_t  max_limbs;         /* longest stored numerator/denominator seen at read-back    */
     int32_t  m, n, nr_artificial, phase;
     double   loop_ms;           /* device time (CUDA events) spent inside relp_iterate loops */
+    uint64_t stage_ns[8];       /* persistent loop, ns per stage: price, column+ratio, pivot row, update, multi-limb+housekeeping */
 } relp_stats;
 
 /* ---- life cycle ------------------------------------------------------------------------- */
@@ -81,6 +82,11 @@ relp_ctx* relp_create(int device, int rank, int world, uint64_t heap_words);
 void relp_destroy(relp_ctx*);
 const char* relp_last_error(void);
 int relp_abi_version(void);
+/* options: "persistent" = 1 (default) runs single-GPU loops as one cooperative kernel, 0 as one
+ * launch per stage (the path multi-GPU solves use, with NCCL between the stages). */
+int relp_set_option(relp_ctx*, const char* name, int64_t value);
+/* the cudaStream_t all work of this context is enqueued on (for CUDA-event timing by the caller) */
+void* relp_stream(relp_ctx*);
 
 /* Multi-GPU only: attach an NCCL communicator (ncclComm_t, created by the caller from
  * torch.distributed's rendezvous) used for the per-pivot pivot-row broadcast and the two

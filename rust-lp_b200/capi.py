@@ -21,7 +21,7 @@ FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
 
 # every symbol include/relp_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
-    "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_comm_unique_id",
+    "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_comm_unique_id",
     "relp_attach_comm", "relp_load_matrix", "relp_carry_create_partially_artificial",
     "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_price",
     "relp_generate_column", "relp_ratio_test", "relp_change_basis", "relp_generate_element",
@@ -48,7 +48,7 @@ class Stats(C.Structure):
                 ("sum_S", C.c_uint64), ("sum_TS", C.c_uint64), ("heap_peak_words", C.c_uint64),
                 ("compactions", C.c_uint64), ("kernel_launches", C.c_uint64), ("max_limbs", C.c_int32),
                 ("m", C.c_int32), ("n", C.c_int32), ("nr_artificial", C.c_int32), ("phase", C.c_int32),
-                ("loop_ms", C.c_double)]
+                ("loop_ms", C.c_double), ("stage_ns", C.c_uint64 * 8)]
 
 
 _libs = {}
@@ -68,6 +68,9 @@ def load_library(path=None):
     L.relp_destroy.argtypes = [vp]
     L.relp_destroy.restype = None
     L.relp_last_error.restype = C.c_char_p
+    L.relp_set_option.argtypes = [vp, C.c_char_p, i64]
+    L.relp_stream.argtypes = [vp]
+    L.relp_stream.restype = vp
     L.relp_comm_unique_id.argtypes = [vp, C.c_char_p]
     L.relp_attach_comm.argtypes = [vp, vp, C.c_char_p]
     L.relp_load_matrix.argtypes = [vp, i32, i32] + [vp] * 8
@@ -135,6 +138,12 @@ class Carry:
         self.rank, self.world = rank, world
         self._limb_cap = 1 << 16
         self.load_matrix(provider)
+
+    def set_option(self, name, value):
+        self._chk(self.L.relp_set_option(self.h, name.encode(), int(value)))
+
+    def stream(self):
+        return self.L.relp_stream(self.h)
 
     def close(self):
         if getattr(self, "h", None):

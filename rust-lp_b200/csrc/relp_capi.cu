@@ -86,10 +86,12 @@ struct relp_ctx {
     std::vector<int64_t> an, ad, cn, cd, rhsn, rhsd;
     // device buffers
     DBuf<DState> st; DBuf<uint32_t> heap;
-    DBuf<int64_t> xn, xd, an_d, ad_d, cn_d, cd_d, rhsn_d, rhsd_d, rcn, rcd, dn, dd, qn, qd, pnd;
-    DBuf<long long> col_ptr_d; DBuf<int> row_idx_d, basis, art_row, tlist, slist, cost_rows, scratch_i;
+    DBuf<int64_t> xn, xd, zn, zd, an_d, ad_d, cn_d, cd_d, rhsn_d, rhsd_d, dn, dd, pnd, tmpn, tmpd, sell_an, sell_ad;
+    DBuf<long long> col_ptr_d, sell_ptr; DBuf<int> row_idx_d, sell_row, basis, art_row, tlist, slist, cost_rows, scratch_i;
     DBuf<unsigned char> in_basis;
-    DBuf<int2> worklist; DBuf<Cand> cand, gather; DBuf<LogEntry> log;
+    DBuf<int2> worklist; DBuf<Cand> cand, cand2, gather; DBuf<LogEntry> log;
+    int n_slices = 0, a_int = 1, coop_blocks = 0, last_ratio_blocks = 1;
+    bool use_persistent = true;
     DState* h_st = nullptr;       // pinned mirror
     Dev D;
     bool loaded = false, carry_ready = false;
@@ -129,6 +131,41 @@ static int err_status(const DState* s) {
     if (s->err & ERR_ZERO_PIVOT) { set_error("Pivot value can't be zero"); return RELP_ERR_ZERO_PIVOT; }
     if (s->err & ERR_LIMB_CAPACITY) { set_error("a numerator/denominator exceeded RELP_OPL limbs"); return RELP_ERR_LIMB_CAPACITY; }
     if (s->err & ERR_HEAP_EXHAUSTED) { set_error("limb heap exhausted: create the context with a larger heap_words"); return RELP_ERR_HEAP_EXHAUSTED; }
+    return 0;
+}
+
+// SELL-32 copy of A for pricing: slice s = columns 32s .. 32s+31, width = longest column of the
+// slice, entry t of lane l at sell_ptr[s] + 32 t + l; padding has row -1.
+static int build_sell(relp_ctx* c) {
+    int n = c->n;
+    int ns = (n + 31) / 32;
+    std::vector<long long> sp(ns + 1, 0);
+    for (int s = 0; s < ns; s++) {
+        long long w = 0;
+        for (int j = s * 32; j < std::min(n, s * 32 + 32); j++) w = std::max(w, c->col_ptr[j + 1] - c->col_ptr[j]);
+        sp[s + 1] = sp[s] + 32 * w;
+    }
+    size_t total = (size_t)sp[ns];
+    std::vector<int> sr(std::max<size_t>(total, 1), -1);
+    std::vector<int64_t> sa(std::max<size_t>(total, 1), 0), sd(std::max<size_t>(total, 1), 1);
+    int a_int = 1;
+    for (int j = 0; j < n; j++) {
+        int s = j >> 5, l = j & 31;
+        long long t0 = c->col_ptr[j], len = c->col_ptr[j + 1] - t0;
+        for (long long t = 0; t < len; t++) {
+            size_t e = (size_t)(sp[s] + 32 * t + l);
+            sr[e] = c->row_idx[t0 + t]; sa[e] = c->an[t0 + t]; sd[e] = c->ad[t0 + t];
+            if (sd[e] != 1) a_int = 0;
+        }
+    }
+    c->n_slices = ns; c->a_int = a_int;
+    if (c->sell_ptr.alloc(ns + 1) || c->sell_row.alloc(total) || c->sell_an.alloc(total) || c->sell_ad.alloc(total)) return RELP_ERR_CUDA;
+    cudaStream_t st = c->stream;
+    CUDA_TRY(cudaMemcpyAsync(c->sell_ptr.p, sp.data(), (ns + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(c->sell_row.p, sr.data(), sr.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(c->sell_an.p, sa.data(), sa.size() * 8, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(c->sell_ad.p, sd.data(), sd.size() * 8, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
     return 0;
 }
 
@@ -218,6 +255,8 @@ int relp_load_matrix(relp_ctx* c, int32_t m, int32_t n, const int64_t* col_ptr, 
     CUDA_TRY(cudaMemcpyAsync(c->rhsn_d.p, rhs_num, m * 8, cudaMemcpyHostToDevice, s));
     CUDA_TRY(cudaMemcpyAsync(c->rhsd_d.p, rhs_den, m * 8, cudaMemcpyHostToDevice, s));
     CUDA_TRY(cudaStreamSynchronize(s));
+    int rc = build_sell(c);
+    if (rc) return rc;
     c->loaded = true; c->carry_ready = false; c->stage = 0;
     return RELP_OK;
 }
@@ -231,115 +270,125 @@ static void shard_rows(relp_ctx* c, int m) {
     c->row_lo = std::min(m, c->rank * per);
     c->mloc = std::max(0, std::min(m, c->row_lo + per) - c->row_lo);
 }
+// pricing shard: contiguous SELL slices and contiguous artificial columns
 static void shard_cols(relp_ctx* c, DState* s) {
-    int per = (s->ncols + c->world - 1) / c->world;
-    s->col_lo = std::min(s->ncols, c->rank * per);
-    s->col_hi = std::min(s->ncols, s->col_lo + per);
+    int per = (c->n_slices + c->world - 1) / c->world;
+    s->sl_lo = std::min(c->n_slices, c->rank * per);
+    s->sl_hi = std::min(c->n_slices, s->sl_lo + per);
+    int na = s->phase == 1 ? s->nr_art : 0;
+    int pera = (na + c->world - 1) / c->world;
+    s->art_lo = std::min(na, c->rank * pera);
+    s->art_hi = std::min(na, s->art_lo + pera);
 }
 
 static void wire_dev(relp_ctx* c) {
     Dev& D = c->D;
-    D.st = c->st.p; D.heap = c->heap.p; D.xn = c->xn.p; D.xd = c->xd.p;
+    D.st = c->st.p; D.heap = c->heap.p; D.xn = c->xn.p; D.xd = c->xd.p; D.zn = c->zn.p; D.zd = c->zd.p;
     D.col_ptr = c->col_ptr_d.p; D.row_idx = c->row_idx_d.p; D.an = c->an_d.p; D.ad = c->ad_d.p;
+    D.sell_ptr = c->sell_ptr.p; D.sell_row = c->sell_row.p; D.sell_an = c->sell_an.p; D.sell_ad = c->sell_ad.p;
     D.cn = c->cn_d.p; D.cd = c->cd_d.p; D.basis = c->basis.p; D.in_basis = c->in_basis.p;
-    D.art_row = c->art_row.p; D.rcn = c->rcn.p; D.rcd = c->rcd.p; D.dn = c->dn.p; D.dd = c->dd.p;
-    D.qn = c->qn.p; D.qd = c->qd.p; D.pn = c->pnd.p; D.pd = c->pnd.p + (c->m + 1);
-    D.tlist = c->tlist.p; D.slist = c->slist.p; D.worklist = c->worklist.p; D.cand = c->cand.p;
+    D.art_row = c->art_row.p; D.dn = c->dn.p; D.dd = c->dd.p;
+    D.pn = c->pnd.p; D.pd = c->pnd.p + (c->m + 1);
+    D.tlist = c->tlist.p; D.slist = c->slist.p; D.worklist = c->worklist.p; D.cand = c->cand.p; D.cand2 = c->cand2.p;
     D.gather = c->gather.p; D.log = c->log.p; D.log_cap = (long long)c->log.n;
 }
 
-static const int MAX_PARTIAL_BLOCKS = 1024;
+static const int MAX_PARTIAL_BLOCKS = 2048;
 
 static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
     shard_rows(c, m);
-    c->ld = (m + 1 + 15) / 16 * 16;
-    size_t plane = (size_t)(c->mloc + 1) * c->ld;
-    if (c->xn.alloc(plane) || c->xd.alloc(plane)) return RELP_ERR_CUDA;
-    if (c->rcn.alloc(ncols_max) || c->rcd.alloc(ncols_max) || c->in_basis.alloc(ncols_max)) return RELP_ERR_CUDA;
-    if (c->dn.alloc(c->mloc + 1) || c->dd.alloc(c->mloc + 1) || c->qn.alloc(c->mloc + 1) || c->qd.alloc(c->mloc + 1)) return RELP_ERR_CUDA;
+    c->ld = std::max(16, (c->mloc + 15) / 16 * 16);
+    size_t plane = (size_t)(m + 1) * c->ld;
+    if (c->xn.alloc(plane) || c->xd.alloc(plane) || c->zn.alloc(m + 1) || c->zd.alloc(m + 1)) return RELP_ERR_CUDA;
+    if (c->in_basis.alloc(ncols_max)) return RELP_ERR_CUDA;
+    if (c->dn.alloc(c->mloc + 1) || c->dd.alloc(c->mloc + 1) || c->tmpn.alloc(m + 2) || c->tmpd.alloc(m + 2)) return RELP_ERR_CUDA;
     if (c->pnd.alloc(2 * (size_t)(m + 1))) return RELP_ERR_CUDA;
     if (c->basis.alloc(m) || c->art_row.alloc(m) || c->tlist.alloc(c->mloc + 1) || c->slist.alloc(m + 1)) return RELP_ERR_CUDA;
     if (c->cost_rows.alloc(c->mloc + 1) || c->scratch_i.alloc(2 * (size_t)(m + 2))) return RELP_ERR_CUDA;
     // worklist: worst case every element of the local block is escalated
-    if (c->worklist.alloc(plane)) return RELP_ERR_CUDA;
-    if (c->cand.alloc(MAX_PARTIAL_BLOCKS) || c->gather.alloc(std::max(c->world, 1))) return RELP_ERR_CUDA;
+    if (c->worklist.alloc((size_t)(m + 1) * std::max(c->mloc, 1))) return RELP_ERR_CUDA;
+    if (c->cand.alloc(MAX_PARTIAL_BLOCKS) || c->cand2.alloc(MAX_PARTIAL_BLOCKS) || c->gather.alloc(std::max(c->world, 1))) return RELP_ERR_CUDA;
     if (!c->log.p && c->log.alloc(1 << 20)) return RELP_ERR_CUDA;
     return 0;
 }
 
 static void init_heap_regions(relp_ctx* c, DState* s) {
-    // [0, T) transient, then two persistent halves
+    // [16, T) transient (offset 0 is never a handle), then two persistent halves
     unsigned long long T = c->heap_words / 4, P = (c->heap_words - T) / 2;
-    s->tr_base = 0; s->tr_top = 0; s->tr_limit = T;
+    s->tr_base = 16; s->tr_top = 16; s->tr_limit = T;
     s->pool_base = T; s->pool_top = T; s->pool_limit = T + P;
     s->alt_base = T + P; s->alt_limit = T + 2 * P;
 }
 
 static int grid_for(relp_ctx* c, long long items, int per_sm = 8) {
-    return clampi(cdiv(items, RELP_THREADS), 1, (long long)c->sm_count * per_sm);
+    return clampi(cdiv(items, RELP_THREADS), 1, std::min<long long>((long long)c->sm_count * per_sm, MAX_PARTIAL_BLOCKS));
 }
 
 // device-side control block update without touching the rest of DState
-__global__ void k_set_control(DState* st, unsigned long long iter_limit, int tag, int reset_status, int reset_memory) {
+__global__ void k_set_control(DState* st, unsigned long long iter_limit, int tag, int reset_status, int reset_transient) {
     st->iter_limit = iter_limit; st->tag = tag;
     if (reset_status) st->status = ST_RUNNING;
-    if (reset_memory) st->last_selected = -1;
+    if (reset_transient) { st->tr_top = st->tr_base; st->T = 0; st->S = 0; st->wl_count = 0; }
+    st->go = !(st->status != ST_RUNNING || st->err != 0 || st->iter >= st->iter_limit);
 }
 __global__ void k_set_pivot(DState* st, int j, int r, int set_zero_rc) {
     if (j >= 0) st->j = j;
     if (r >= 0) st->r = r;
     if (set_zero_rc) st->rc = make_small(0, 1);
 }
-__global__ void k_reset_transient(DState* st) { st->tr_top = st->tr_base; st->T = 0; st->S = 0; st->wl_count = 0; }
-__global__ void k_reprice_selected(Dev D) {   // rc of st->j for the step-wise API (relp_generate_column)
-    DState* st = D.st;
-    Arena ar = transient(D);
-    st->rc = price_column(D, st, st->j, ar);
+__global__ void k_reset_transient(DState* st) { st->tr_top = st->tr_base; }
+
+static int nccl_check(int rc, const char* what) {
+    if (rc == 0) return 0;
+    set_error(std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "nccl error"));
+    return RELP_ERR_COMM;
 }
 
-static void enqueue_price(relp_ctx* c, int rule) {
-    DState* hs = c->h_st;
+// select: reduce this rank's block candidates; multi-GPU: all-gather the per-rank winners and
+// reduce again, identically on every rank ("gather-then-reduce-identically")
+static int enqueue_select(relp_ctx* c, int mode, int nblocks, int rule) {
+    if (c->world == 1) { LAUNCH(c, k_select, 1, RELP_THREADS, c->D, mode, nblocks, 0, -1, rule); return 0; }
+    LAUNCH(c, k_select, 1, RELP_THREADS, c->D, mode, nblocks, 0, c->rank, rule);
+    if (nccl_check(g_nccl.AllGather(c->gather.p + c->rank, c->gather.p, sizeof(Cand), NCCL_INT8, c->comm, c->stream), "ncclAllGather")) return RELP_ERR_COMM;
+    LAUNCH(c, k_select, 1, RELP_THREADS, c->D, mode, c->world, 1, -1, rule);
+    return 0;
+}
+static int enqueue_price(relp_ctx* c, int rule) {
     int mode = rule == RULE_DANTZIG ? ARG_DANTZIG : ARG_FIRST;
-    int ncols_loc = hs->col_hi - hs->col_lo;
-    LAUNCH(c, k_price, grid_for(c, ncols_loc), RELP_THREADS, c->D);
-    int gb = clampi(cdiv(ncols_loc, RELP_THREADS * 4), 1, MAX_PARTIAL_BLOCKS);
-    LAUNCH(c, k_argmin_partial, gb, RELP_THREADS, c->D, mode);
-    if (c->world == 1) LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, mode, gb, 0, -1, rule);
-    else {
-        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, mode, gb, 0, c->rank, rule);
-        g_nccl.AllGather(c->gather.p + c->rank, c->gather.p, sizeof(Cand), NCCL_INT8, c->comm, c->stream);
-        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, mode, c->world, 1, -1, rule);
-    }
+    DState* hs = c->h_st;
+    long long lanes = (long long)(hs->sl_hi - hs->sl_lo) * 32 + (hs->art_hi - hs->art_lo);
+    int gb = grid_for(c, std::max<long long>(lanes, 1));
+    LAUNCH(c, k_price, gb, RELP_THREADS, c->D, mode);
+    return enqueue_select(c, mode, gb, rule);
 }
-static void enqueue_column_and_ratio(relp_ctx* c, bool ratio) {
-    LAUNCH(c, k_gen_column, grid_for(c, c->mloc + 1), RELP_THREADS, c->D);
-    if (!ratio) return;
-    int gb = clampi(cdiv(c->mloc, RELP_THREADS * 4), 1, MAX_PARTIAL_BLOCKS);
-    LAUNCH(c, k_argmin_partial, gb, RELP_THREADS, c->D, (int)ARG_RATIO);
-    if (c->world == 1) LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, gb, 0, -1, 0);
-    else {
-        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, gb, 0, c->rank, 0);
-        g_nccl.AllGather(c->gather.p + c->rank, c->gather.p, sizeof(Cand), NCCL_INT8, c->comm, c->stream);
-        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, c->world, 1, -1, 0);
-    }
+static int enqueue_column_and_ratio(relp_ctx* c, bool select_row) {
+    int gb = grid_for(c, std::max(c->mloc, 1));
+    LAUNCH(c, k_gen_column, gb, RELP_THREADS, c->D);
+    c->last_ratio_blocks = gb;
+    if (!select_row) return 0;
+    return enqueue_select(c, (int)ARG_RATIO, gb, 0);
 }
-static void enqueue_change_basis(relp_ctx* c) {
+static int enqueue_change_basis(relp_ctx* c) {
     LAUNCH(c, k_pivot_row, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D, c->world > 1 ? 1 : 0);
     if (c->world > 1) {
-        g_nccl.AllReduce(c->pnd.p, c->pnd.p, 2 * (size_t)(c->m + 1), NCCL_INT64, NCCL_SUM, c->comm, c->stream);
+        if (nccl_check(g_nccl.AllReduce(c->pnd.p, c->pnd.p, 2 * (size_t)(c->m + 1), NCCL_INT64, NCCL_SUM, c->comm, c->stream), "ncclAllReduce")) return RELP_ERR_COMM;
         LAUNCH(c, k_build_slist, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D);
     }
-    LAUNCH(c, k_bookkeeping, 1, 1, c->D);
     LAUNCH(c, k_update, c->sm_count * 8, RELP_THREADS, c->D);
     LAUNCH(c, k_update_big, c->sm_count * 2, 128, c->D);
     LAUNCH(c, k_iter_end, 1, 1, c->D);
+    return 0;
 }
-static void enqueue_iteration(relp_ctx* c, int rule) {
-    LAUNCH(c, k_iter_begin, 1, 1, c->D);
-    LAUNCH(c, k_compact, c->sm_count * 4, RELP_THREADS, c->D);
-    enqueue_price(c, rule);
-    enqueue_column_and_ratio(c, true);
-    enqueue_change_basis(c);
+static int enqueue_begin(relp_ctx* c) {
+    LAUNCH(c, k_begin, c->sm_count * 4, RELP_THREADS, c->D);
+    LAUNCH(c, k_begin2, 1, 1, c->D);
+    return 0;
+}
+static int enqueue_iteration(relp_ctx* c, int rule) {
+    enqueue_begin(c);
+    if (enqueue_price(c, rule)) return RELP_ERR_COMM;
+    if (enqueue_column_and_ratio(c, true)) return RELP_ERR_COMM;
+    return enqueue_change_basis(c);
 }
 
 static int check_cuda(relp_ctx* c) {
@@ -348,16 +397,40 @@ static int check_cuda(relp_ctx* c) {
     return 0;
 }
 
+static int launch_persistent(relp_ctx* c, int rule, int max_iters) {
+#ifdef RELP_EMUL
+    k_simplex_loop(c->D, rule, max_iters);
+    c->launches++;
+    return 0;
+#else
+    if (c->coop_blocks == 0) {
+        int per_sm = 0;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_simplex_loop, RELP_PTHREADS, 0));
+        if (per_sm < 1) { set_error("persistent kernel does not fit on an SM"); return RELP_ERR_CUDA; }
+        c->coop_blocks = c->sm_count;        // one CTA per SM
+    }
+    void* args[] = { (void*)&c->D, (void*)&rule, (void*)&max_iters };
+    CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_simplex_loop, dim3(c->coop_blocks), dim3(RELP_PTHREADS), args, 0, c->stream));
+    c->launches++;
+    return 0;
+#endif
+}
+
 // the device-resident loop of phase_one::primal / phase_two::primal
 static int run_loop(relp_ctx* c, int rule, int64_t max_iters, int tag) {
     if (sync_state(c)) return RELP_ERR_CUDA;
     unsigned long long limit = max_iters < 0 ? ~0ull : c->h_st->iter + (unsigned long long)max_iters;
-    LAUNCH(c, k_set_control, 1, 1, c->st.p, limit, tag, 1, 0);
+    LAUNCH(c, k_set_control, 1, 1, c->st.p, limit, tag, 1, 1);
     cudaEventRecord(c->ev0, c->stream);
-    int batch = 8;
     int result = RELP_OK;
+    int batch = 8;
     for (;;) {
-        for (int b = 0; b < batch; b++) enqueue_iteration(c, rule);
+        if (c->world == 1 && c->use_persistent) {
+            if (launch_persistent(c, rule, 1 << 20)) return RELP_ERR_CUDA;
+        } else {
+            for (int b = 0; b < batch; b++) if (enqueue_iteration(c, rule)) return RELP_ERR_COMM;
+            if (batch < 64) batch *= 2;
+        }
         if (check_cuda(c)) return RELP_ERR_CUDA;
         if (sync_state(c)) return RELP_ERR_CUDA;
         const DState* s = c->h_st;
@@ -365,7 +438,6 @@ static int run_loop(relp_ctx* c, int rule, int64_t max_iters, int tag) {
         if (s->status == ST_NO_COLUMN) { result = RELP_OPTIMAL; break; }
         if (s->status == ST_NO_ROW) { result = RELP_UNBOUNDED; break; }
         if (s->iter >= limit) { result = RELP_OK; break; }
-        if (batch < 64) batch *= 2;
     }
     cudaEventRecord(c->ev1, c->stream);
     cudaEventSynchronize(c->ev1);
@@ -397,12 +469,11 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     CUDA_TRY(cudaMemcpyAsync(c->in_basis.p, inb.data(), inb.size(), cudaMemcpyHostToDevice, c->stream));
     if (nr_art) CUDA_TRY(cudaMemcpyAsync(c->art_row.p, c->art_rows_h.data(), nr_art * sizeof(int), cudaMemcpyHostToDevice, c->stream));
     DState* s = c->h_st;
-    unsigned long long iter_keep = 0;
     memset(s, 0, sizeof(DState));
     s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld; s->n = n; s->nr_art = nr_art;
-    s->phase = 1; s->ncols = nr_art + n; shard_cols(c, s);
-    s->status = ST_RUNNING; s->last_selected = -1; s->iter = iter_keep; s->iter_limit = ~0ull; s->tag = '1';
-    s->rc = make_small(0, 1); s->pivot = make_small(0, 1);
+    s->phase = 1; s->ncols = nr_art + n; shard_cols(c, s); s->a_int = c->a_int;
+    s->status = ST_RUNNING; s->last_selected = -1; s->iter = 0; s->iter_limit = ~0ull; s->tag = '1'; s->go = 1;
+    s->rc = make_small(0, 1);
     init_heap_regions(c, s);
     if (push_state(c)) return RELP_ERR_CUDA;
     wire_dev(c);
@@ -412,6 +483,22 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0;
     return RELP_OK;
+}
+
+// exact sum of the per-rank partial cost rows (multi-GPU hand-over): int64 tier only
+__global__ void k_sum_partials(Dev D, const int64_t* allp, int world, int count, int64_t* outn, int64_t* outd) {
+    Arena ar = persistent(D);
+    Val one = make_small(1, 1);
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
+        Val acc = val_zero();
+        for (int r = 0; r < world; r++) {
+            const int64_t* base = allp + (size_t)r * 2 * count;
+            Val v = make_small(base[k], base[count + k]);
+            if (v.d <= 0) { atomicOr(&D.st->err, ERR_LIMB_CAPACITY); continue; }
+            acc = val_fma(acc, v, one, 1, D.heap, ar);
+        }
+        outn[k] = acc.n; outd[k] = acc.d;
+    }
 }
 
 // K5 + index shift; `m` may already have shrunk (row removal).
@@ -429,18 +516,22 @@ static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbe
     DState* s = c->h_st;
     s->phase = 2; s->ncols = n; shard_cols(c, s); s->last_selected = -1; s->status = ST_RUNNING;
     s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld;
+    s->tr_top = s->tr_base; s->T = 0; s->S = 0; s->wl_count = 0;
     if (push_state(c)) return RELP_ERR_CUDA;
     c->phase = 2;
     wire_dev(c);
-    LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
-    LAUNCH(c, k_recompute_cost_row, grid_for(c, m + 1, 2), RELP_THREADS, c->D, c->cost_rows.p, (int)cost_rows.size(), c->D.pn, c->D.pd);
-    if (c->world > 1) {
-        // partial sums of small values only: all-gather and add (exact) -- done by k_sum_cost_rows
-        set_error("multi-GPU hand-over not wired"); return RELP_ERR_COMM;
+    if (c->world == 1) {
+        LAUNCH(c, k_recompute_cost_row, grid_for(c, m + 1, 2), RELP_THREADS, c->D, c->cost_rows.p, (int)cost_rows.size(), c->zn.p, c->zd.p);
+    } else {
+        // each rank sums over its rows into pn|pd, the partials are all-gathered and added exactly
+        int cnt = m + 1;
+        DBuf<int64_t> all;
+        if (all.alloc((size_t)c->world * 2 * cnt)) return RELP_ERR_CUDA;
+        LAUNCH(c, k_recompute_cost_row, grid_for(c, cnt, 2), RELP_THREADS, c->D, c->cost_rows.p, (int)cost_rows.size(), c->D.pn, c->D.pd);
+        if (nccl_check(g_nccl.AllGather(c->pnd.p, all.p, 2 * (size_t)cnt * 8, NCCL_INT8, c->comm, c->stream), "ncclAllGather")) return RELP_ERR_COMM;
+        LAUNCH(c, k_sum_partials, grid_for(c, cnt, 2), RELP_THREADS, c->D, all.p, c->world, cnt, c->zn.p, c->zd.p);
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
     }
-    size_t z = (size_t)c->mloc * c->ld;
-    CUDA_TRY(cudaMemcpyAsync(c->xn.p + z, c->D.pn, (m + 1) * 8, cudaMemcpyDeviceToDevice, c->stream));
-    CUDA_TRY(cudaMemcpyAsync(c->xd.p + z, c->D.pd, (m + 1) * 8, cudaMemcpyDeviceToDevice, c->stream));
     if (check_cuda(c)) return RELP_ERR_CUDA;
     if (sync_state(c)) return RELP_ERR_CUDA;
     if (c->h_st->err) return err_status(c->h_st);
@@ -472,17 +563,16 @@ static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* r
     std::vector<int> newidx(m, -1), keep;
     { size_t q = 0; for (int i = 0; i < m; i++) { if (q < (size_t)n_rows && rows[q] == i) { q++; continue; } newidx[i] = (int)keep.size(); keep.push_back(i); } }
     int m2 = (int)keep.size();
-    // planes: kept rows + cost row; columns 0 and 1 + kept
-    std::vector<int> keep_row(keep), keep_col(m2 + 1);
-    keep_row.push_back(m);
+    // planes: kept rows; columns 0 and 1 + kept
+    std::vector<int> keep_col(m2 + 1);
     keep_col[0] = 0; for (int k = 0; k < m2; k++) keep_col[1 + k] = 1 + keep[k];
-    int ld2 = (m2 + 1 + 15) / 16 * 16;
+    int ld2 = std::max(16, (m2 + 15) / 16 * 16);
     DBuf<int64_t> nxn, nxd;
     if (nxn.alloc((size_t)(m2 + 1) * ld2) || nxd.alloc((size_t)(m2 + 1) * ld2)) return RELP_ERR_CUDA;
     int* kr = c->scratch_i.p; int* kc = c->scratch_i.p + (m + 2);
-    CUDA_TRY(cudaMemcpyAsync(kr, keep_row.data(), keep_row.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    if (m2) CUDA_TRY(cudaMemcpyAsync(kr, keep.data(), keep.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(cudaMemcpyAsync(kc, keep_col.data(), keep_col.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
-    LAUNCH(c, k_gather_planes, c->sm_count * 8, RELP_THREADS, c->xn.p, c->xd.p, c->ld, nxn.p, nxd.p, ld2, m2 + 1, m2 + 1, kr, kc);
+    LAUNCH(c, k_gather_planes, c->sm_count * 8, RELP_THREADS, c->xn.p, c->xd.p, c->ld, nxn.p, nxd.p, ld2, m2, m2 + 1, kr, kc);
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     std::swap(c->xn.p, nxn.p); std::swap(c->xn.n, nxn.n); std::swap(c->xd.p, nxd.p); std::swap(c->xd.n, nxd.n);
     // provider without the removed rows (filter/generic_wrapper.rs:224-300)
@@ -505,6 +595,8 @@ static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* r
         CUDA_TRY(cudaMemcpyAsync(c->ad_d.p, ad.data(), ad.size() * 8, cudaMemcpyHostToDevice, c->stream));
     }
     CUDA_TRY(cudaStreamSynchronize(c->stream));
+    int rc = build_sell(c);
+    if (rc) return rc;
     c->m = m2; shard_rows(c, m2); c->ld = ld2;
     basis = b2;
     return handover_common(c, basis);
@@ -519,22 +611,22 @@ static int remove_artificial_basis_variables(relp_ctx* c) {
     std::sort(arts.begin(), arts.end());
     c->rows_removed.clear();
     if (arts.empty()) return RELP_OK;
-    LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'z', 1, 0);
     int* d_best = c->scratch_i.p;
     for (int a : arts) {
         int pivot_row = c->art_rows_h[a];
         int best = INT_MAX;
         CUDA_TRY(cudaMemcpyAsync(d_best, &best, sizeof(int), cudaMemcpyHostToDevice, c->stream));
-        LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
+        LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'z', 1, 1);
         LAUNCH(c, k_cleanup_select, grid_for(c, c->n), RELP_THREADS, c->D, pivot_row, d_best);
         CUDA_TRY(cudaMemcpyAsync(&best, d_best, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
         CUDA_TRY(cudaStreamSynchronize(c->stream));
+        if (c->world > 1) { set_error("artificial clean-up is single-GPU only"); return RELP_ERR_COMM; }
         if (best == INT_MAX) { c->rows_removed.push_back(a); continue; }   // sic: the artificial's index (phase_one.rs:251)
-        LAUNCH(c, k_iter_begin, 1, 1, c->D);
-        LAUNCH(c, k_compact, c->sm_count * 4, RELP_THREADS, c->D);
+        LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'z', 1, 1);
+        enqueue_begin(c);
         LAUNCH(c, k_set_pivot, 1, 1, c->st.p, best, pivot_row, 1);
-        enqueue_column_and_ratio(c, false);
-        enqueue_change_basis(c);
+        if (enqueue_column_and_ratio(c, false)) return RELP_ERR_COMM;
+        if (enqueue_change_basis(c)) return RELP_ERR_COMM;
         if (check_cuda(c)) return RELP_ERR_CUDA;
     }
     if (sync_state(c)) return RELP_ERR_CUDA;
@@ -542,11 +634,12 @@ static int remove_artificial_basis_variables(relp_ctx* c) {
     return RELP_OK;
 }
 
+// Export (element (i, k) at i * rstride + k * cstride) as a row-major nrows x ncols rat array.
 // `keep_transient`: the source itself lives in the transient region (generated column, element),
 // so the export appends behind it instead of recycling the region.
-static int read_block_impl(relp_ctx* c, const int64_t* sn, const int64_t* sd, int sld, int nrows, int ncols,
-                           int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used,
-                           bool keep_transient = false) {
+static int read_block_impl(relp_ctx* c, const int64_t* sn, const int64_t* sd, long long rstride, long long cstride,
+                           int nrows, int ncols, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap,
+                           size_t* limb_used, bool keep_transient = false) {
     size_t total = (size_t)nrows * ncols;
     if (limb_used) *limb_used = 0;
     if (total == 0) return RELP_OK;
@@ -555,7 +648,7 @@ static int read_block_impl(relp_ctx* c, const int64_t* sn, const int64_t* sd, in
     if (!keep_transient) LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
     if (sync_state(c)) return RELP_ERR_CUDA;
     unsigned long long base = c->h_st->tr_top;
-    LAUNCH(c, k_export, grid_for(c, (long long)total), RELP_THREADS, c->D, sn, sd, sld, nrows, ncols, on.p, od.p, base);
+    LAUNCH(c, k_export, grid_for(c, (long long)total), RELP_THREADS, c->D, sn, sd, rstride, cstride, nrows, ncols, on.p, od.p, base);
     if (check_cuda(c)) return RELP_ERR_CUDA;
     CUDA_TRY(cudaMemcpyAsync(num, on.p, total * 8, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaMemcpyAsync(den, od.p, total * 8, cudaMemcpyDeviceToHost, c->stream));
@@ -592,8 +685,7 @@ static int solve_continue(relp_ctx* c, int64_t max_pivots) {
             if (st == RELP_UNBOUNDED) { c->stage = 3; c->final_status = RELP_ERR_PHASE1_UNBOUNDED; return c->final_status; }
             // phase 1 finished: feasible iff the artificial objective is exactly zero (phase_one.rs:146-167)
             int64_t on, od; size_t used = 0; uint32_t limbs[2 * RELP_OPL + 2];
-            int rc = read_block_impl(c, c->xn.p + (size_t)c->mloc * c->ld, c->xd.p + (size_t)c->mloc * c->ld, c->ld, 1, 1,
-                                     &on, &od, limbs, sizeof(limbs) / 4, &used);
+            int rc = read_block_impl(c, c->zn.p, c->zd.p, 1, 1, 1, 1, &on, &od, limbs, sizeof(limbs) / 4, &used);
             if (rc) return rc;
             if (!(on == 0 && od == 1)) { c->stage = 3; c->final_status = RELP_INFEASIBLE; return RELP_INFEASIBLE; }
             rc = remove_artificial_basis_variables(c);
@@ -625,10 +717,9 @@ int relp_carry_from_artificial_remove_rows(relp_ctx* c, int32_t n_rows, const in
 int relp_price(relp_ctx* c, int rule, int32_t* j_out, int64_t* rc_num, int64_t* rc_den, uint32_t* limbs, size_t limb_cap) {
     if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
     CUDA_TRY(cudaSetDevice(c->device));
-    LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)(c->phase == 1 ? '1' : '2'), 1, 0);
-    LAUNCH(c, k_iter_begin, 1, 1, c->D);
-    LAUNCH(c, k_compact, c->sm_count * 4, RELP_THREADS, c->D);
-    enqueue_price(c, rule);
+    LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)(c->phase == 1 ? '1' : '2'), 1, 1);
+    enqueue_begin(c);
+    if (enqueue_price(c, rule)) return RELP_ERR_COMM;
     if (check_cuda(c)) return RELP_ERR_CUDA;
     if (sync_state(c)) return RELP_ERR_CUDA;
     if (c->h_st->err) return err_status(c->h_st);
@@ -653,11 +744,10 @@ int relp_generate_column(relp_ctx* c, int32_t j) {
     CUDA_TRY(cudaSetDevice(c->device));
     if (sync_state(c)) return RELP_ERR_CUDA;
     if (j < 0 || j >= c->h_st->ncols) return RELP_ERR_ARGUMENT;
-    LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)(c->phase == 1 ? '1' : '2'), 1, 0);
-    LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
+    LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)(c->phase == 1 ? '1' : '2'), 1, 1);
     LAUNCH(c, k_set_pivot, 1, 1, c->st.p, (int)j, -1, 0);
     LAUNCH(c, k_reprice_selected, 1, 1, c->D);
-    LAUNCH(c, k_gen_column, grid_for(c, c->mloc + 1), RELP_THREADS, c->D);
+    if (enqueue_column_and_ratio(c, false)) return RELP_ERR_COMM;
     if (check_cuda(c)) return RELP_ERR_CUDA;
     if (sync_state(c)) return RELP_ERR_CUDA;
     return c->h_st->err ? err_status(c->h_st) : RELP_OK;
@@ -666,14 +756,7 @@ int relp_generate_column(relp_ctx* c, int32_t j) {
 int relp_ratio_test(relp_ctx* c, int32_t* r_out) {
     if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
     CUDA_TRY(cudaSetDevice(c->device));
-    int gb = clampi(cdiv(c->mloc, RELP_THREADS * 4), 1, MAX_PARTIAL_BLOCKS);
-    LAUNCH(c, k_argmin_partial, gb, RELP_THREADS, c->D, (int)ARG_RATIO);
-    if (c->world == 1) LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, gb, 0, -1, 0);
-    else {
-        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, gb, 0, c->rank, 0);
-        g_nccl.AllGather(c->gather.p + c->rank, c->gather.p, sizeof(Cand), NCCL_INT8, c->comm, c->stream);
-        LAUNCH(c, k_argmin_final, 1, RELP_THREADS, c->D, (int)ARG_RATIO, c->world, 1, -1, 0);
-    }
+    if (enqueue_select(c, (int)ARG_RATIO, c->last_ratio_blocks, 0)) return RELP_ERR_COMM;
     if (check_cuda(c)) return RELP_ERR_CUDA;
     if (sync_state(c)) return RELP_ERR_CUDA;
     if (c->h_st->err) return err_status(c->h_st);
@@ -686,7 +769,7 @@ int relp_change_basis(relp_ctx* c, int32_t r, int32_t* leaving_out) {
     if (!c || !c->carry_ready || r < 0 || r >= c->m) return RELP_ERR_ARGUMENT;
     CUDA_TRY(cudaSetDevice(c->device));
     LAUNCH(c, k_set_pivot, 1, 1, c->st.p, -1, (int)r, 0);
-    enqueue_change_basis(c);
+    if (enqueue_change_basis(c)) return RELP_ERR_COMM;
     if (check_cuda(c)) return RELP_ERR_CUDA;
     if (sync_state(c)) return RELP_ERR_CUDA;
     if (c->h_st->err) return err_status(c->h_st);
@@ -698,9 +781,9 @@ int relp_generate_element(relp_ctx* c, int32_t i, int32_t j, int64_t* num, int64
     if (!c || !c->carry_ready || i < c->row_lo || i >= c->row_lo + c->mloc) return RELP_ERR_ARGUMENT;
     CUDA_TRY(cudaSetDevice(c->device));
     LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
-    LAUNCH(c, k_generate_element, 1, 1, c->D, (int)i, (int)j, c->qn.p + c->mloc, c->qd.p + c->mloc);
+    LAUNCH(c, k_generate_element, 1, 1, c->D, (int)i, (int)j, c->tmpn.p, c->tmpd.p);
     size_t used;
-    return read_block_impl(c, c->qn.p + c->mloc, c->qd.p + c->mloc, 1, 1, 1, num, den, limbs, limb_cap, &used, true);
+    return read_block_impl(c, c->tmpn.p, c->tmpd.p, 1, 1, 1, 1, num, den, limbs, limb_cap, &used, true);
 }
 
 int relp_iterate(relp_ctx* c, int rule, int64_t max_iters) {
@@ -741,14 +824,28 @@ int relp_read_basis(relp_ctx* c, int32_t* out) {
 int relp_read_block(relp_ctx* c, int32_t row0, int32_t nrows, int32_t col0, int32_t ncols,
                     int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used) {
     if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
-    // rows are LOCAL rows of this rank's shard followed by the cost row (local index mloc)
-    if (row0 < 0 || nrows < 0 || row0 + nrows > c->mloc + 1 || col0 < 0 || ncols < 0 || col0 + ncols > c->m + 1) return RELP_ERR_ARGUMENT;
+    // rows are LOCAL rows of this rank's shard; the cost row is local index mloc (alone in its call)
+    if (row0 < 0 || nrows < 0 || col0 < 0 || ncols < 0 || col0 + ncols > c->m + 1) return RELP_ERR_ARGUMENT;
     CUDA_TRY(cudaSetDevice(c->device));
-    size_t off = (size_t)row0 * c->ld + col0;
-    return read_block_impl(c, c->xn.p + off, c->xd.p + off, c->ld, nrows, ncols, num, den, limbs, limb_cap, limb_used);
+    if (row0 == c->mloc && nrows == 1)
+        return read_block_impl(c, c->zn.p + col0, c->zd.p + col0, 0, 1, 1, ncols, num, den, limbs, limb_cap, limb_used);
+    if (row0 + nrows > c->mloc) return RELP_ERR_ARGUMENT;
+    size_t off = (size_t)col0 * c->ld + row0;
+    return read_block_impl(c, c->xn.p + off, c->xd.p + off, 1, c->ld, nrows, ncols, num, den, limbs, limb_cap, limb_used);
 }
 int relp_read_carry(relp_ctx* c, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used) {
-    return c ? relp_read_block(c, 0, c->mloc + 1, 0, c->m + 1, num, den, limbs, limb_cap, limb_used) : RELP_ERR_ARGUMENT;
+    // local rows first, then the cost row: two exports sharing one limb buffer
+    if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
+    size_t w = (size_t)c->m + 1, used1 = 0, used2 = 0;
+    int rc = relp_read_block(c, 0, c->mloc, 0, c->m + 1, num, den, limbs, limb_cap, &used1);
+    if (limb_used) *limb_used = used1;
+    if (rc) return rc;
+    int64_t* n2 = num + (size_t)c->mloc * w; int64_t* d2 = den + (size_t)c->mloc * w;
+    rc = relp_read_block(c, c->mloc, 1, 0, c->m + 1, n2, d2, limbs ? limbs + used1 : nullptr, limb_cap > used1 ? limb_cap - used1 : 0, &used2);
+    if (limb_used) *limb_used = used1 + used2;
+    if (rc) return rc;
+    for (size_t k = 0; k < w; k++) if (d2[k] == 0) n2[k] += (int64_t)used1;
+    return RELP_OK;
 }
 int relp_read_b(relp_ctx* c, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used) {
     return c ? relp_read_block(c, 0, c->mloc, 0, 1, num, den, limbs, limb_cap, limb_used) : RELP_ERR_ARGUMENT;
@@ -762,7 +859,7 @@ int relp_read_minus_objective(relp_ctx* c, int64_t* num, int64_t* den, uint32_t*
 int relp_read_column(relp_ctx* c, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used) {
     if (!c || !c->carry_ready) return RELP_ERR_ARGUMENT;
     CUDA_TRY(cudaSetDevice(c->device));
-    return read_block_impl(c, c->dn.p, c->dd.p, 1, c->mloc, 1, num, den, limbs, limb_cap, limb_used, true);
+    return read_block_impl(c, c->dn.p, c->dd.p, 1, 1, c->mloc, 1, num, den, limbs, limb_cap, limb_used, true);
 }
 int64_t relp_log_size(relp_ctx* c) {
     if (!c || !c->carry_ready) return 0;
@@ -788,6 +885,7 @@ int relp_stats_get(relp_ctx* c, relp_stats* out) {
         const DState* s = c->h_st;
         out->pivots = s->iter; out->escalated = s->escalated; out->sum_T = s->sum_T; out->sum_S = s->sum_S;
         out->sum_TS = s->sum_TS; out->heap_peak_words = s->pool_peak; out->compactions = s->compactions;
+        for (int k = 0; k < 8; k++) out->stage_ns[k] = s->stage_ns[k];
     }
     return RELP_OK;
 }
@@ -797,5 +895,11 @@ int relp_rows_removed(relp_ctx* c, int32_t* out, int32_t cap) {
     for (int i = 0; i < n && i < cap; i++) out[i] = c->rows_removed[i];
     return n;
 }
+int relp_set_option(relp_ctx* c, const char* name, int64_t value) {
+    if (!c || !name) return RELP_ERR_ARGUMENT;
+    if (!strcmp(name, "persistent")) { c->use_persistent = value != 0; return RELP_OK; }
+    return RELP_ERR_ARGUMENT;
+}
+void* relp_stream(relp_ctx* c) { return c ? (void*)c->stream : nullptr; }
 
 }  // extern "C"

@@ -1,55 +1,69 @@
 // CUDA kernels (sm_100a) of the exact revised-simplex iteration: SURVEY.md section 8(a) rows a3-a10.
 //
-//   K3 k_price + k_argmin_*     pricing          pivot_rule.rs:38-127, tableau/mod.rs:102-108,
-//                                                carry/mod.rs:572-577, dense.rs:81-92
-//   K2 k_gen_column             B^-1 a_j         basis_inverse_rows.rs:144-173, sparse.rs:82-106
-//   K4 (fused into K2) + argmin ratio test       tableau/mod.rs:221-247
-//   K1 k_pivot_row, k_update,   Carry update     carry/mod.rs:283-333, 549-570,
-//      k_update_big                              basis_inverse_rows.rs:42-83, sparse.rs:213-301
-//   K5 k_recompute_cost_row     phase hand-over  carry/mod.rs:214-271
+//   stage A  price        K3  pivot_rule.rs:38-127, tableau/mod.rs:102-108, carry/mod.rs:572-577,
+//                             dense.rs:81-92             (fused with the block-level argmin)
+//   stage C  gen_column   K2  basis_inverse_rows.rs:144-173, sparse.rs:82-106
+//            + ratios     K4  tableau/mod.rs:221-247      (fused, block-level argmin)
+//   stage D  pivot_row    K1a basis_inverse_rows.rs:42-51, sparse.rs:291-301, carry/mod.rs:283-295
+//   stage E  update       K1b basis_inverse_rows.rs:63-83 -> sparse.rs:213-248, carry/mod.rs:296-333
+//   stage F  update_big   K1c the same elements, multi-limb tier
+//   K5       recompute_cost_row   carry/mod.rs:214-271 (phase hand-over)
 //
-// Control is device resident: every kernel reads (j, r, status, list sizes) from DState, and is a
-// no-op once the loop has terminated, so the host can enqueue a batch of iterations (or replay a
-// CUDA graph) without a round trip per pivot.
+// Two drivers share these stage functions:
+//   * k_simplex_loop -- ONE persistent cooperative kernel (one CTA per SM) that runs whole
+//     iterations back to back with grid-wide barriers between the stages; (j, r, status) never
+//     leave the device.  Single-GPU solves use this.
+//   * one __global__ wrapper per stage -- the step-wise trait API (relp_price, ...) and the
+//     multi-GPU path, where NCCL collectives sit between the stages.
 //
-// HBM layout.  The Carry matrix is two dense row-major int64 planes xn (numerators) and xd
-// (denominators), (mloc + 1) rows x ld columns per GPU: local row li < mloc is
-// [b_i | B^-1 row i] for global row i = row_lo + li, local row mloc is the replicated cost row
-// [-obj | -pi].  A denominator of 0 tags an element escalated to the multi-limb heap
-// (relp_arith.cuh).  Zero (0/1) is the reference's "absent" sparse entry (sparse.rs:235-237).
+// HBM layout.  The Carry block of this GPU is two dense COLUMN-major int64 planes xn, xd
+// (numerators / denominators): element (local row li, column k) at k * ld + li, k = 0 is b,
+// k = 1 + c is column c of B^-1.  Column generation reads whole columns (coalesced); the rank-1
+// update touches the T x S block of rows with d_i != 0 and columns with p_k != 0.  The cost row
+// [-obj | -pi] is a separate contiguous vector zn, zd (replicated on every GPU): pricing gathers
+// from it.  A denominator of 0 tags an element escalated to the multi-limb heap (relp_arith.cuh);
+// heap offsets are never 0, so "numerator == 0" alone means the reference's absent sparse entry
+// (sparse.rs:235-237).  A is stored twice: CSC (column generation) and SELL-32 (pricing: slice s
+// holds columns 32s..32s+31 interleaved, so a warp reads 128 contiguous bytes of row indices per
+// step and each lane owns one column).
 #pragma once
 #ifdef RELP_EMUL
 #include "cuda_emul.h"   // tests/native: sequential stand-in, CPU-only CI of the host logic
 #else
 #include <cuda_runtime.h>
+#include <cooperative_groups.h>
 #endif
 #include "relp_arith.cuh"
 
 namespace relp {
 
 enum { RULE_FIRST = 0, RULE_FIRST_MEMORY = 1, RULE_DANTZIG = 2 };
-enum { ARG_DANTZIG = 0, ARG_FIRST = 1, ARG_RATIO = 2, ARG_CLEANUP = 3 };
+enum { ARG_DANTZIG = 0, ARG_FIRST = 1, ARG_RATIO = 2 };
 enum { ST_RUNNING = 0, ST_NO_COLUMN = 1, ST_NO_ROW = 2 };
+enum { NSTAGE = 8 };
 
 struct LogEntry { int tag, j, r, leaving, T, S; };
 
 struct DState {
     int m, mloc, row_lo, ld;       // global rows, local rows, first local row, leading dimension
     int n, nr_art, phase, ncols;   // provider columns, artificials, 1|2, tableau columns
-    int col_lo, col_hi;            // tableau columns priced by this rank
+    int sl_lo, sl_hi;              // SELL slices priced by this rank
+    int art_lo, art_hi;            // artificial columns priced by this rank
     int status, err;
     int j, r, leaving;
     int T, S, wl_count;
     int last_selected;             // FirstProfitableWithMemory (pivot_rule.rs:62-94)
     int tag;                       // log tag of the running loop
     int compacting;
+    int a_int;                     // every A value has denominator 1
+    int go;                        // persistent loop: continue? (written by one thread between barriers)
     unsigned long long iter, iter_limit;
-    unsigned long long pool_top, pool_limit;     // active persistent region of the limb heap
-    unsigned long long pool_base;
-    unsigned long long alt_base, alt_limit;      // the other persistent region (compaction target)
-    unsigned long long tr_top, tr_base, tr_limit;  // per-iteration transient region
+    unsigned long long pool_top, pool_limit, pool_base;   // active persistent region of the limb heap
+    unsigned long long alt_base, alt_limit;               // the other persistent region (compaction target)
+    unsigned long long tr_top, tr_base, tr_limit;         // per-iteration transient region
     unsigned long long escalated, sum_T, sum_S, sum_TS, pool_peak, compactions;
-    Val rc, pivot;
+    unsigned long long stage_ns[NSTAGE];                  // persistent kernel: time per stage (globaltimer)
+    Val rc;
 };
 
 struct Cand { Val v; int key; int idx; };
@@ -57,25 +71,35 @@ struct Cand { Val v; int key; int idx; };
 struct Dev {
     DState* st;
     uint32_t* heap;
-    int64_t* xn; int64_t* xd;                 // Carry planes
+    int64_t* xn; int64_t* xd;                 // Carry planes, column-major
+    int64_t* zn; int64_t* zd;                 // cost row [-obj | -pi], m + 1
     const long long* col_ptr; const int* row_idx;
     const int64_t* an; const int64_t* ad;     // CSC values
+    const long long* sell_ptr; const int* sell_row;
+    const int64_t* sell_an; const int64_t* sell_ad;
     const int64_t* cn; const int64_t* cd;     // cost
     int* basis;                               // basis_indices[m], tableau numbering, replicated
     unsigned char* in_basis;                  // per tableau column
     const int* art_row;                       // artificial column -> row (Partially::column_to_row)
-    int64_t* rcn; int64_t* rcd;               // reduced cost per tableau column (transient)
-    int64_t* dn; int64_t* dd;                 // generated column, local rows; entry mloc = rc
-    int64_t* qn; int64_t* qd;                 // ratios b_i / d_i, local rows
+    int64_t* dn; int64_t* dd;                 // generated column, local rows
     int64_t* pn; int64_t* pd;                 // normalised pivot row (m + 1), replicated
     int* tlist; int* slist;
     int2* worklist;
-    Cand* cand;                               // per-block partial argmin results
+    Cand* cand;                               // per-block partial argmin: pricing
+    Cand* cand2;                              // per-block partial argmin: ratio test
     Cand* gather;                             // world candidates (multi-GPU all-gather buffer)
     LogEntry* log; long long log_cap;
 };
 
-#define RELP_THREADS 256
+#define RELP_THREADS 256          // stage wrappers
+#define RELP_PTHREADS 1024        // persistent kernel: one CTA of 1024 threads per SM
+#define RELP_MAXWARPS 32
+
+struct Grid { int tid, nth, bid, nb; };
+__device__ __forceinline__ Grid this_grid_dims() {
+    Grid g; g.tid = blockIdx.x * blockDim.x + threadIdx.x; g.nth = gridDim.x * blockDim.x;
+    g.bid = blockIdx.x; g.nb = gridDim.x; return g;
+}
 
 __device__ __forceinline__ Arena transient(const Dev& D) {
     Arena a; a.top = &D.st->tr_top; a.limit = D.st->tr_limit; a.err = &D.st->err; return a;
@@ -93,76 +117,16 @@ __device__ __forceinline__ void st_val(int64_t* n, int64_t* d, size_t i, const V
     n[i] = v.n; d[i] = v.d;
 }
 
-// ---------------------------------------------------------------------------------------------
-// Start of an iteration: recycle the transient limb region, clear the lists, and decide whether
-// the persistent limb pool must be compacted before this iteration allocates more.
-// ---------------------------------------------------------------------------------------------
-__global__ void k_iter_begin(Dev D) {
-    DState* st = D.st;
-    if (halted(st)) return;
-    st->tr_top = st->tr_base;
-    st->T = 0; st->S = 0; st->wl_count = 0;
-    unsigned long long used = st->pool_top - st->pool_base;
-    if (used > st->pool_peak) st->pool_peak = used;
-    if (used > (st->pool_limit - st->pool_base) / 2) {
-        // flip regions; k_compact (next launch) re-homes every live value
-        unsigned long long b = st->alt_base, l = st->alt_limit;
-        st->alt_base = st->pool_base; st->alt_limit = st->pool_limit;
-        st->pool_base = b; st->pool_limit = l; st->pool_top = b;
-        st->compacting = 1; st->compactions++;
-    } else st->compacting = 0;
-}
-
-// Copy every live escalated Carry element into the fresh pool region (order is irrelevant).
-__global__ void k_compact(Dev D) {
-    DState* st = D.st;
-    if (halted(st) || !st->compacting) return;
-    size_t total = (size_t)(st->mloc + 1) * st->ld;
-    Arena ar = persistent(D);
-    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
-        if (D.xd[e] == 0) {
-            Val v; v.n = D.xn[e]; v.d = 0;
-            Val c = copy_val(v, D.heap, ar);
-            D.xn[e] = c.n; D.xd[e] = c.d;
-        }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// K3 pricing: rc_j = c_j + sum_i (-pi_i) A_ij for every non-basic tableau column of this rank.
-// One thread per column; -pi is row mloc of the planes (L2 resident).
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ Val price_column(const Dev& D, const DState* st, int j, const Arena& ar) {
-    const int64_t* zn = D.xn + (size_t)st->mloc * st->ld + 1;
-    const int64_t* zd = D.xd + (size_t)st->mloc * st->ld + 1;
-    if (st->phase == 1 && j < st->nr_art) {
-        // artificial column e_row with Cost::One: -pi_row + 1   (big/special.rs:36-48)
-        int row = D.art_row[j];
-        Val one = make_small(1, 1);
-        return val_fma(ld_val(zn, zd, row), one, one, 1, D.heap, ar);
-    }
-    int jj = st->phase == 1 ? j - st->nr_art : j;
-    Val acc = st->phase == 1 ? val_zero() : make_small(D.cn[jj], D.cd[jj]);
-    long long e = D.col_ptr[jj + 1];
-    for (long long t = D.col_ptr[jj]; t < e; t++) {
-        int row = D.row_idx[t];
-        int64_t z = zn[row];
-        int64_t zden = zd[row];
-        if (z == 0 && zden == 1) continue;
-        Val zv; zv.n = z; zv.d = zden;
-        acc = val_fma(acc, zv, make_small(D.an[t], D.ad[t]), 1, D.heap, ar);
-    }
-    return acc;
-}
-
-__global__ void k_price(Dev D) {
-    DState* st = D.st;
-    if (halted(st)) return;
-    Arena ar = transient(D);
-    for (int j = st->col_lo + blockIdx.x * blockDim.x + threadIdx.x; j < st->col_hi; j += gridDim.x * blockDim.x) {
-        Val rc = D.in_basis[j] ? val_absent() : price_column(D, st, j, ar);
-        st_val(D.rcn, D.rcd, j, rc);
-    }
+// position in a list shared by the whole grid; one atomic per warp
+__device__ __forceinline__ int list_append(int* counter) {
+#ifdef RELP_EMUL
+    return atomicAdd(counter, 1);
+#else
+    cooperative_groups::coalesced_group g = cooperative_groups::coalesced_threads();
+    int base = 0;
+    if (g.thread_rank() == 0) base = atomicAdd(counter, (int)g.size());
+    return g.shfl(base, 0) + (int)g.thread_rank();
+#endif
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -171,6 +135,8 @@ __global__ void k_price(Dev D) {
 //   ARG_FIRST   : candidates rc_j < 0, order cyclic distance from `start`   :53-57, :78-93
 //   ARG_RATIO   : candidates present,  order (ratio_i, basis_indices[i])    tableau/mod.rs:221-247
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ Cand cand_none() { Cand c; c.idx = -1; c.key = 0; c.v = val_absent(); return c; }
+
 __device__ __forceinline__ bool cand_better(const Cand& a, const Cand& b, int mode, const uint32_t* heap) {
     if (a.idx < 0) return false;
     if (b.idx < 0) return true;
@@ -190,8 +156,10 @@ __device__ __forceinline__ Cand cand_shfl(const Cand& c, int delta) {
     return o;
 }
 
+// Block-wide argmin; the result is returned to EVERY thread of the block.
 __device__ Cand block_argmin(Cand best, int mode, const uint32_t* heap) {
-    __shared__ Cand sh[RELP_THREADS / 32];
+    __shared__ Cand sh[RELP_MAXWARPS];
+    __shared__ Cand winner;
     for (int d = 16; d > 0; d >>= 1) {
         Cand o = cand_shfl(best, d);
         if (cand_better(o, best, mode, heap)) best = o;
@@ -201,236 +169,423 @@ __device__ Cand block_argmin(Cand best, int mode, const uint32_t* heap) {
     __syncthreads();
     if (w == 0) {
         int nw = (blockDim.x + 31) >> 5;
-        if (lane < nw) best = sh[lane]; else best.idx = -1;
+        if (lane < nw) best = sh[lane]; else best = cand_none();
         for (int d = 16; d > 0; d >>= 1) {
             Cand o = cand_shfl(best, d);
             if (cand_better(o, best, mode, heap)) best = o;
         }
+        if (lane == 0) winner = best;
     }
     __syncthreads();
-    return best;   // valid in thread 0
+    best = winner;
+    __syncthreads();
+    return best;
 }
 
-// partial: one candidate per block into D.cand[blockIdx.x]
-__global__ void k_argmin_partial(Dev D, int mode) {
-    DState* st = D.st;
-    if (halted(st)) return;
-    Cand best; best.idx = -1; best.key = 0; best.v = val_absent();
-    if (mode == ARG_RATIO) {
-        for (int li = blockIdx.x * blockDim.x + threadIdx.x; li < st->mloc; li += gridDim.x * blockDim.x) {
-            Val v = ld_val(D.qn, D.qd, li);
-            if (is_absent(v)) continue;
-            Cand c; c.v = v; c.idx = st->row_lo + li; c.key = D.basis[c.idx];
-            if (cand_better(c, best, mode, D.heap)) best = c;
-        }
-    } else {
-        int ncols = st->ncols;
-        int start = (mode == ARG_FIRST && st->last_selected >= 0) ? st->last_selected : 0;
-        for (int j = st->col_lo + blockIdx.x * blockDim.x + threadIdx.x; j < st->col_hi; j += gridDim.x * blockDim.x) {
-            Val v = ld_val(D.rcn, D.rcd, j);
-            if (is_absent(v) || val_sign(v, D.heap) >= 0) continue;
-            Cand c; c.v = v; c.idx = j;
-            c.key = mode == ARG_FIRST ? (j >= start ? j - start : j - start + ncols) : j;
-            if (cand_better(c, best, mode, D.heap)) best = c;
-        }
-    }
-    best = block_argmin(best, mode, D.heap);
-    if (threadIdx.x == 0) D.cand[blockIdx.x] = best;
-}
-
-// final: reduce `count` candidates (from this rank's blocks, or from the all-gather buffer)
-// and commit the decision to DState.  `to_gather`: write the winner to D.gather[rank] instead
-// (multi-GPU stage 1).
-__global__ void k_argmin_final(Dev D, int mode, int count, int from_gather, int to_gather_slot, int rule) {
-    DState* st = D.st;
-    if (halted(st)) return;
-    const Cand* src = from_gather ? D.gather : D.cand;
-    Cand best; best.idx = -1; best.key = 0; best.v = val_absent();
+// Reduce `count` candidates of `src` (every block can do this redundantly: same input, same
+// deterministic order, same winner).
+__device__ Cand reduce_candidates(const Cand* src, int count, int mode, const uint32_t* heap) {
+    Cand best = cand_none();
     for (int i = threadIdx.x; i < count; i += blockDim.x) {
         Cand c = src[i];
-        if (cand_better(c, best, mode, D.heap)) best = c;
+        if (cand_better(c, best, mode, heap)) best = c;
     }
-    best = block_argmin(best, mode, D.heap);
-    if (threadIdx.x != 0) return;
-    if (to_gather_slot >= 0) { D.gather[to_gather_slot] = best; return; }
-    if (mode == ARG_RATIO) {
-        if (best.idx < 0) st->status = ST_NO_ROW; else st->r = best.idx;
-    } else {
-        if (best.idx < 0) { st->status = ST_NO_COLUMN; st->last_selected = -1; }
-        else {
-            st->j = best.idx; st->rc = best.v;
-            if (rule == RULE_FIRST_MEMORY) st->last_selected = best.idx;
-        }
-    }
+    return block_argmin(best, mode, heap);
 }
 
 // ---------------------------------------------------------------------------------------------
-// K2 + K4: d_i = sum_k Binv[i][k] a_kj for every local row, the list of rows with d_i != 0, and
-// the ratio b_i / d_i for rows with d_i > 0.
+// Stage A -- K3 pricing: rc_j = c_j + sum_i (-pi_i) A_ij for every non-basic tableau column of
+// this rank, fused with the argmin (no reduced-cost vector is ever stored).
 // ---------------------------------------------------------------------------------------------
-__global__ void k_gen_column(Dev D) {
-    DState* st = D.st;
-    if (halted(st)) return;
+__device__ __forceinline__ Val price_column_csc(const Dev& D, const DState* st, int j, const Arena& ar) {
+    const int64_t* zn = D.zn + 1; const int64_t* zd = D.zd + 1;
+    if (st->phase == 1 && j < st->nr_art) {
+        // artificial column e_row with Cost::One: -pi_row + 1   (big/special.rs:36-48)
+        int row = D.art_row[j];
+        Val one = make_small(1, 1);
+        return val_fma(ld_val(zn, zd, row), one, one, 1, D.heap, ar);
+    }
+    int jj = st->phase == 1 ? j - st->nr_art : j;
+    Val acc = st->phase == 1 ? val_zero() : make_small(D.cn[jj], D.cd[jj]);
+    long long e = D.col_ptr[jj + 1];
+    for (long long t = D.col_ptr[jj]; t < e; t++) {
+        int row = D.row_idx[t];
+        int64_t z = zn[row];
+        if (z == 0) continue;
+        Val zv; zv.n = z; zv.d = zd[row];
+        acc = val_fma(acc, zv, make_small(D.an[t], D.ad[t]), 1, D.heap, ar);
+    }
+    return acc;
+}
+
+__device__ __forceinline__ void price_consider(const Dev& D, Val rc, int j, int mode, int start, int ncols, Cand& best) {
+    if (val_sign(rc, D.heap) >= 0) return;
+    Cand c; c.v = rc; c.idx = j;
+    c.key = mode == ARG_FIRST ? (j >= start ? j - start : j - start + ncols) : j;
+    if (cand_better(c, best, mode, D.heap)) best = c;
+}
+
+__device__ void stage_price(const Dev& D, const Grid& g, int mode) {
+    const DState* st = D.st;
     Arena ar = transient(D);
-    int j = st->j;
+    const int phase = st->phase, nr_art = st->nr_art, ncols = st->ncols, n = st->n;
+    const int start = (mode == ARG_FIRST && st->last_selected >= 0) ? st->last_selected : 0;
+    const int off = phase == 1 ? nr_art : 0;
+    const int64_t* __restrict__ zn = D.zn + 1; const int64_t* __restrict__ zd = D.zd + 1;
+    Cand best = cand_none();
+    if (phase == 1) {
+        Val one = make_small(1, 1);
+        for (int a = st->art_lo + g.tid; a < st->art_hi; a += g.nth) {
+            if (D.in_basis[a]) continue;
+            Val rc = val_fma(ld_val(zn, zd, D.art_row[a]), one, one, 1, D.heap, ar);
+            price_consider(D, rc, a, mode, start, ncols, best);
+        }
+    }
+#ifdef RELP_EMUL
+    const int gw = 0, nw = 1;        // sequential stand-in: one thread plays every lane in turn
+    for (int lane = 0; lane < 32; lane++)
+#else
+    const int lane = g.tid & 31, gw = g.tid >> 5, nw = g.nth >> 5;
+#endif
+    for (int s = st->sl_lo + gw; s < st->sl_hi; s += nw) {
+        const int a_int = st->a_int;
+        int jj = s * 32 + lane;
+        long long base = D.sell_ptr[s];
+        int width = (int)((D.sell_ptr[s + 1] - base) >> 5);
+        bool live = jj < n && !D.in_basis[off + jj];
+        Val acc = (phase == 2 && live) ? make_small(D.cn[jj], D.cd[jj]) : val_zero();
+        const int* __restrict__ rows = D.sell_row + base + lane;
+        for (int t = 0; t < width; t += 4) {
+            int rr[4]; int64_t zz[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) rr[u] = (live && t + u < width) ? rows[(size_t)(t + u) * 32] : -1;
+#pragma unroll
+            for (int u = 0; u < 4; u++) zz[u] = rr[u] >= 0 ? zn[rr[u]] : 0;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (zz[u] == 0) continue;
+                size_t e = (size_t)base + (size_t)(t + u) * 32 + lane;
+                Val zv; zv.n = zz[u]; zv.d = zd[rr[u]];
+                Val av = make_small(D.sell_an[e], a_int ? 1 : D.sell_ad[e]);
+                acc = val_fma(acc, zv, av, 1, D.heap, ar);
+            }
+        }
+        if (live) price_consider(D, acc, off + jj, mode, start, ncols, best);
+    }
+    best = block_argmin(best, mode, D.heap);
+    if (threadIdx.x == 0) D.cand[g.bid] = best;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Stage C -- K2 + K4: d_i = sum_k Binv[i][k] a_kj for every local row, the list of rows with
+// d_i != 0, and the exact argmin of b_i / d_i over rows with d_i > 0 (block level).
+// ---------------------------------------------------------------------------------------------
+__device__ void stage_gen_column(const Dev& D, const Grid& g, int j) {
+    DState* st = D.st;
+    Arena ar = transient(D);
     int unit_row = -1; long long t0 = 0, t1 = 0;
     if (st->phase == 1 && j < st->nr_art) unit_row = D.art_row[j];
     else { int jj = st->phase == 1 ? j - st->nr_art : j; t0 = D.col_ptr[jj]; t1 = D.col_ptr[jj + 1]; }
-    int mloc = st->mloc, ld = st->ld;
-    for (int li = blockIdx.x * blockDim.x + threadIdx.x; li <= mloc; li += gridDim.x * blockDim.x) {
-        if (li == mloc) {                       // cost-row factor: z -= rc * p   (carry/mod.rs:326-333)
-            Val rc = copy_val(st->rc, D.heap, ar);
-            st_val(D.dn, D.dd, li, rc);
-            if (!val_is_zero(rc)) { int p = atomicAdd(&st->T, 1); D.tlist[p] = li; }
-            continue;
-        }
-        const int64_t* rn = D.xn + (size_t)li * ld + 1;
-        const int64_t* rd = D.xd + (size_t)li * ld + 1;
+    const int mloc = st->mloc; const size_t ld = st->ld;
+    const int64_t* __restrict__ xn = D.xn + ld;     // column 1 + k at xn + k * ld
+    const int64_t* __restrict__ xd = D.xd + ld;
+    Cand best = cand_none();
+    for (int li = g.tid; li < mloc; li += g.nth) {
         Val acc = val_zero();
-        if (unit_row >= 0) acc = copy_val(ld_val(rn, rd, unit_row), D.heap, ar);
-        else for (long long t = t0; t < t1; t++) {
-            int k = D.row_idx[t];
-            int64_t xn = rn[k], xd = rd[k];
-            if (xn == 0 && xd == 1) continue;
-            Val xv; xv.n = xn; xv.d = xd;
-            acc = val_fma(acc, xv, make_small(D.an[t], D.ad[t]), 1, D.heap, ar);
-        }
-        st_val(D.dn, D.dd, li, acc);
-        Val q = val_absent();
-        if (!val_is_zero(acc)) {
-            int p = atomicAdd(&st->T, 1); D.tlist[p] = li;
-            if (val_sign(acc, D.heap) > 0) {
-                Val b = ld_val(D.xn, D.xd, (size_t)li * ld);
-                q = val_div(b, acc, D.heap, ar);
+        if (unit_row >= 0) acc = copy_val(ld_val(xn, xd, (size_t)unit_row * ld + li), D.heap, ar);
+        else for (long long t = t0; t < t1; t += 4) {
+            int kk[4]; int64_t xx[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) kk[u] = t + u < t1 ? D.row_idx[t + u] : -1;
+#pragma unroll
+            for (int u = 0; u < 4; u++) xx[u] = kk[u] >= 0 ? xn[(size_t)kk[u] * ld + li] : 0;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (xx[u] == 0) continue;
+                Val xv; xv.n = xx[u]; xv.d = xd[(size_t)kk[u] * ld + li];
+                acc = val_fma(acc, xv, make_small(D.an[t + u], D.ad[t + u]), 1, D.heap, ar);
             }
         }
-        st_val(D.qn, D.qd, li, q);
+        st_val(D.dn, D.dd, li, acc);
+        if (acc.n != 0) {
+            int p = list_append(&st->T); D.tlist[p] = li;
+            if (val_sign(acc, D.heap) > 0) {
+                Cand c; c.v = val_div(ld_val(D.xn, D.xd, li), acc, D.heap, ar);
+                c.idx = st->row_lo + li; c.key = D.basis[c.idx];
+                if (cand_better(c, best, ARG_RATIO, D.heap)) best = c;
+            }
+        }
     }
+    best = block_argmin(best, ARG_RATIO, D.heap);
+    if (threadIdx.x == 0) D.cand2[g.bid] = best;
 }
 
 // ---------------------------------------------------------------------------------------------
-// K1 part 1 (owner of row r): p_k = X[r][k] / d_r for k = 0..m, written back to row r and staged
-// in the replicated pivot-row buffer; list of columns with p_k != 0; basis bookkeeping.
-// basis_inverse_rows.rs:42-51, sparse.rs:291-301, carry/mod.rs:283-313 (b_r), tableau/mod.rs:72-84
+// Stage D -- K1a (owner of row r): p_k = X[r][k] / d_r for k = 0..m, written back to row r and
+// staged in the pivot-row buffer; list of columns with p_k != 0.
 // ---------------------------------------------------------------------------------------------
-__global__ void k_pivot_row(Dev D, int multi) {
+__device__ void stage_pivot_row(const Dev& D, const Grid& g, int r, int multi) {
     DState* st = D.st;
-    if (halted(st)) return;
-    int r = st->r, lr = r - st->row_lo;
+    int lr = r - st->row_lo;
     bool owner = lr >= 0 && lr < st->mloc;
     if (!owner) {   // multi-GPU: contribute zeros to the sum all-reduce that replicates the row
-        for (int k = blockIdx.x * blockDim.x + threadIdx.x; k <= st->m; k += gridDim.x * blockDim.x) { D.pn[k] = 0; D.pd[k] = 0; }
+        for (int k = g.tid; k <= st->m; k += g.nth) { D.pn[k] = 0; D.pd[k] = 0; }
         return;
     }
     Val pivot = ld_val(D.dn, D.dd, lr);
-    if (val_is_zero(pivot)) { if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&st->err, ERR_ZERO_PIVOT); return; }
+    if (pivot.n == 0) { if (g.tid == 0) atomicOr(&st->err, ERR_ZERO_PIVOT); return; }
     Arena ar = persistent(D);
-    int64_t* rn = D.xn + (size_t)lr * st->ld;
-    int64_t* rd = D.xd + (size_t)lr * st->ld;
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k <= st->m; k += gridDim.x * blockDim.x) {
-        Val x = ld_val(rn, rd, k);
-        Val p = x;
-        if (!val_is_zero(x)) {
-            p = val_div(x, pivot, D.heap, ar);
-            st_val(rn, rd, k, p);
-            if (!multi) { int s = atomicAdd(&st->S, 1); D.slist[s] = k; }
-            else if (p.d == 0) atomicOr(&st->err, ERR_LIMB_CAPACITY);   // escalated pivot rows do not cross GPUs yet
-        }
+    const size_t ld = st->ld;
+    for (int k = g.tid; k <= st->m; k += g.nth) {
+        size_t e = (size_t)k * ld + lr;
+        int64_t x = D.xn[e];
+        if (x == 0) { if (multi) { D.pn[k] = 0; D.pd[k] = 1; } continue; }
+        Val xv; xv.n = x; xv.d = D.xd[e];
+        Val p = val_div(xv, pivot, D.heap, ar);
+        st_val(D.xn, D.xd, e, p);
         st_val(D.pn, D.pd, k, p);
+        if (!multi) { int s = list_append(&st->S); D.slist[s] = k; }
+        else if (p.d == 0) atomicOr(&st->err, ERR_LIMB_CAPACITY);   // escalated pivot rows do not cross GPUs yet
     }
 }
 
 // multi-GPU: every rank derives the column list from the replicated pivot row
-__global__ void k_build_slist(Dev D) {
+__device__ void stage_build_slist(const Dev& D, const Grid& g) {
     DState* st = D.st;
-    if (halted(st)) return;
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k <= st->m; k += gridDim.x * blockDim.x) {
-        if (!(D.pn[k] == 0 && D.pd[k] == 1)) { int s = atomicAdd(&st->S, 1); D.slist[s] = k; }
-    }
-}
-
-// Basis bookkeeping + statistics + log, one thread, after k_pivot_row (every rank).
-__global__ void k_bookkeeping(Dev D) {
-    DState* st = D.st;
-    if (halted(st)) return;
-    int r = st->r, j = st->j;
-    int leaving = D.basis[r];
-    D.basis[r] = j;
-    D.in_basis[leaving] = 0; D.in_basis[j] = 1;
-    st->leaving = leaving;
-    Val b = ld_val(D.pn, D.pd, 0);
-    int costrow = val_is_zero(st->rc) ? 0 : 1;
-    int Tl = st->T - 1 - costrow;                     // reference's col.len() - 1 (rows eliminated), this rank
-    int Sl = st->S - (val_is_zero(b) ? 0 : 1) + 1;    // nnz(B^-1 row r) + 1
-    if ((long long)st->iter < D.log_cap) {
-        LogEntry e; e.tag = st->tag; e.j = j; e.r = r; e.leaving = leaving; e.T = Tl; e.S = Sl;
-        D.log[st->iter] = e;
-    }
-    st->sum_T += (unsigned long long)(st->T - 1); st->sum_S += (unsigned long long)st->S;
-    st->sum_TS += (unsigned long long)(st->T - 1) * (unsigned long long)st->S;
+    for (int k = g.tid; k <= st->m; k += g.nth)
+        if (D.pn[k] != 0) { int s = list_append(&st->S); D.slist[s] = k; }
 }
 
 // ---------------------------------------------------------------------------------------------
-// K1 part 2: x_ik -= d_i * p_k over the T x S block (local rows incl. the cost row, i != r).
-// Fixed-width tier in place; elements whose operands or result leave int64/int64 are queued for
-// the multi-limb kernel.   basis_inverse_rows.rs:63-83 -> sparse.rs:213-248; carry/mod.rs:296-312,
-// :326-333.
+// Stage E -- K1b: x_ik -= d_i * p_k over the T x S block (i != r), and z_k -= rc * p_k on the cost
+// row.  Fixed-width tier in place; elements whose operands or result leave int64/int64 are queued
+// for the multi-limb stage.  One thread does the basis bookkeeping (tableau/mod.rs:72-84).
 // ---------------------------------------------------------------------------------------------
-__global__ void k_update(Dev D) {
+__device__ void stage_update(const Dev& D, const Grid& g, int j, int r, Val rc) {
     DState* st = D.st;
-    if (halted(st)) return;
-    int T = st->T, S = st->S, ld = st->ld;
-    int lr = st->r - st->row_lo;
-    long long total = (long long)T * S;
-    for (long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x; w < total; w += (long long)gridDim.x * blockDim.x) {
-        int t = (int)(w / S), s = (int)(w - (long long)t * S);
+    const int T = st->T, S = st->S; const size_t ld = st->ld;
+    const int lr = r - st->row_lo;
+    const long long total = (long long)T * S;
+    for (long long w = g.tid; w < total; w += g.nth) {
+        int s = (int)(w / T), t = (int)(w - (long long)s * T);
         int li = D.tlist[t];
         if (li == lr) continue;
         int k = D.slist[s];
-        size_t e = (size_t)li * ld + k;
+        size_t e = (size_t)k * ld + li;
         Val x = ld_val(D.xn, D.xd, e);
         Val dv = ld_val(D.dn, D.dd, li);
         Val p = ld_val(D.pn, D.pd, k);
         Val out;
-        if (x.d > 0 && dv.d > 0 && p.d > 0 && small_fma(x, dv, p, -1, &out)) {
-            st_val(D.xn, D.xd, e, out);
-        } else {
-            int q = atomicAdd(&st->wl_count, 1);
-            D.worklist[q] = make_int2(li, k);
+        if (x.d > 0 && dv.d > 0 && p.d > 0 && small_fma(x, dv, p, -1, &out)) st_val(D.xn, D.xd, e, out);
+        else { int q = atomicAdd(&st->wl_count, 1); D.worklist[q] = make_int2(li, k); }
+    }
+    if (rc.n != 0) {   // carry/mod.rs:326-333; rc == 0 only for the zero-cost clean-up pivots
+        Arena ar = persistent(D);
+        for (int s = g.tid; s < S; s += g.nth) {
+            int k = D.slist[s];
+            Val z = val_fma(ld_val(D.zn, D.zd, k), rc, ld_val(D.pn, D.pd, k), -1, D.heap, ar);
+            st_val(D.zn, D.zd, k, z);
         }
+    }
+    if (g.tid == 0) {
+        int leaving = D.basis[r];
+        D.basis[r] = j;
+        D.in_basis[leaving] = 0; D.in_basis[j] = 1;
+        st->leaving = leaving; st->j = j; st->r = r;
+        int b_nz = (lr >= 0 && lr < st->mloc) ? (D.xn[lr] != 0) : (D.pn[0] != 0);   // p_0 = b_r / pivot
+        int Tl = T - 1;                       // reference's col.len() - 1 (rows eliminated) on this rank
+        int Sl = S - b_nz + 1;                // nnz(B^-1 row r) + 1
+        if ((long long)st->iter < D.log_cap) {
+            LogEntry e; e.tag = st->tag; e.j = j; e.r = r; e.leaving = leaving; e.T = Tl; e.S = Sl;
+            D.log[st->iter] = e;
+        }
+        unsigned long long rows = (unsigned long long)(T - 1 + (rc.n != 0));
+        st->sum_T += rows; st->sum_S += (unsigned long long)S; st->sum_TS += rows * (unsigned long long)S;
     }
 }
 
-__global__ void k_update_big(Dev D) {
+// Stage F -- K1c: the queued elements in the multi-limb tier.
+__device__ void stage_update_big(const Dev& D, const Grid& g) {
     DState* st = D.st;
-    if (halted(st)) return;
-    int n = st->wl_count, ld = st->ld;
+    const int n = st->wl_count; const size_t ld = st->ld;
     Arena ar = persistent(D);
-    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < n; w += gridDim.x * blockDim.x) {
+    for (int w = g.tid; w < n; w += g.nth) {
         int2 it = D.worklist[w];
-        size_t e = (size_t)it.x * ld + it.y;
+        size_t e = (size_t)it.y * ld + it.x;
         Val x = ld_val(D.xn, D.xd, e);
         Val out = big_fma(x, ld_val(D.dn, D.dd, it.x), ld_val(D.pn, D.pd, it.y), -1, D.heap, ar);
         st_val(D.xn, D.xd, e, out);
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) st->escalated += (unsigned long long)n;
 }
 
-__global__ void k_iter_end(Dev D) {
+// one thread, after stage F has completed everywhere
+__device__ void end_of_iteration(const Dev& D) {
+    DState* st = D.st;
+    st->escalated += (unsigned long long)st->wl_count;
+    st->iter++;
+    st->go = !halted(st);
+    st->tr_top = st->tr_base;
+    st->T = 0; st->S = 0; st->wl_count = 0;
+    unsigned long long used = st->pool_top - st->pool_base;
+    if (used > st->pool_peak) st->pool_peak = used;
+    if (used > (st->pool_limit - st->pool_base) / 2) {
+        // flip regions; stage_compact re-homes every live value before anything allocates again
+        unsigned long long b = st->alt_base, l = st->alt_limit;
+        st->alt_base = st->pool_base; st->alt_limit = st->pool_limit;
+        st->pool_base = b; st->pool_limit = l; st->pool_top = b;
+        st->compacting = 1; st->compactions++;
+    }
+}
+
+// Copy every live escalated Carry element into the fresh pool region (order is irrelevant).
+__device__ void stage_compact(const Dev& D, const Grid& g) {
+    DState* st = D.st;
+    size_t total = (size_t)(st->m + 1) * st->ld;
+    Arena ar = persistent(D);
+    for (size_t e = g.tid; e < total; e += g.nth) {
+        if (D.xd[e] == 0) {
+            Val v; v.n = D.xn[e]; v.d = 0;
+            Val c = copy_val(v, D.heap, ar);
+            D.xn[e] = c.n; D.xd[e] = c.d;
+        }
+    }
+    for (int k = g.tid; k <= st->m; k += g.nth) {
+        if (D.zd[k] == 0) {
+            Val v; v.n = D.zn[k]; v.d = 0;
+            Val c = copy_val(v, D.heap, ar);
+            D.zn[k] = c.n; D.zd[k] = c.d;
+        }
+    }
+}
+
+// commit helpers (one thread)
+__device__ __forceinline__ void commit_column(DState* st, const Cand& w, int rule) {
+    if (w.idx < 0) { st->status = ST_NO_COLUMN; st->last_selected = -1; }
+    else { st->j = w.idx; st->rc = w.v; if (rule == RULE_FIRST_MEMORY) st->last_selected = w.idx; }
+}
+__device__ __forceinline__ void commit_row(DState* st, const Cand& w) {
+    if (w.idx < 0) st->status = ST_NO_ROW; else st->r = w.idx;
+}
+
+#ifndef RELP_EMUL
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t;
+}
+#define GRID_SYNC() cooperative_groups::this_grid().sync()
+#else
+static inline unsigned long long gtime() { return 0; }
+#define GRID_SYNC() do {} while (0)
+#endif
+
+// ---------------------------------------------------------------------------------------------
+// The persistent loop: phase_one::primal / phase_two::primal (phase_one.rs:135-169,
+// phase_two.rs:32-50) entirely on the device.  Cooperative launch, one CTA per SM.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int rule, int max_iters) {
+    DState* st = D.st;
+    const Grid g = this_grid_dims();
+    const int mode = rule == RULE_DANTZIG ? ARG_DANTZIG : ARG_FIRST;
+    unsigned long long t0 = gtime();
+    for (int it = 0; it < max_iters; it++) {
+        // `go` and `compacting` are written by one thread between the last two barriers of an
+        // iteration (or by the host before the launch): every thread reads the same value here
+        if (!st->go) break;
+        if (st->compacting) {
+            stage_compact(D, g);
+            GRID_SYNC();
+            if (g.tid == 0) st->compacting = 0;
+        }
+        stage_price(D, g, mode);
+        GRID_SYNC();
+        unsigned long long t1 = gtime();
+        Cand col = reduce_candidates(D.cand, g.nb, mode, D.heap);      // same winner in every CTA
+        if (g.tid == 0) commit_column(st, col, rule);
+        if (col.idx < 0) break;
+        stage_gen_column(D, g, col.idx);
+        GRID_SYNC();
+        unsigned long long t2 = gtime();
+        Cand row = reduce_candidates(D.cand2, g.nb, ARG_RATIO, D.heap);
+        if (g.tid == 0) commit_row(st, row);
+        if (row.idx < 0) break;
+        stage_pivot_row(D, g, row.idx, 0);
+        GRID_SYNC();
+        unsigned long long t3 = gtime();
+        stage_update(D, g, col.idx, row.idx, col.v);
+        GRID_SYNC();
+        unsigned long long t4 = gtime();
+        if (st->wl_count > 0) {                 // final after the barrier: uniform
+            stage_update_big(D, g);
+            GRID_SYNC();
+        }
+        if (g.tid == 0) {
+            end_of_iteration(D);
+            unsigned long long t5 = gtime();
+            st->stage_ns[0] += t1 - t0; st->stage_ns[1] += t2 - t1; st->stage_ns[2] += t3 - t2;
+            st->stage_ns[3] += t4 - t3; st->stage_ns[4] += t5 - t4;
+            t0 = t5;
+        }
+        GRID_SYNC();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// One wrapper per stage: step-wise trait API and the multi-GPU path (NCCL between the stages).
+// ---------------------------------------------------------------------------------------------
+__global__ void k_begin(Dev D) {      // housekeeping that the persistent loop does inline
     DState* st = D.st;
     if (halted(st)) return;
-    st->iter++;
+    if (st->compacting) stage_compact(D, this_grid_dims());
+}
+__global__ void k_begin2(Dev D) { if (!halted(D.st)) D.st->compacting = 0; }
+__global__ void k_price(Dev D, int mode) {
+    if (halted(D.st)) return;
+    stage_price(D, this_grid_dims(), mode);
+}
+// reduce `count` candidates (this rank's blocks, or the all-gather buffer) and either commit the
+// decision or post this rank's winner to gather[slot] (multi-GPU stage 1)
+__global__ void k_select(Dev D, int mode, int count, int from_gather, int slot, int rule) {
+    DState* st = D.st;
+    if (halted(st)) return;
+    const Cand* src = from_gather ? D.gather : (mode == ARG_RATIO ? D.cand2 : D.cand);
+    Cand w = reduce_candidates(src, count, mode, D.heap);
+    if (threadIdx.x != 0) return;
+    if (slot >= 0) { D.gather[slot] = w; return; }
+    if (mode == ARG_RATIO) commit_row(st, w); else commit_column(st, w, rule);
+}
+__global__ void k_gen_column(Dev D) {
+    if (halted(D.st)) return;
+    stage_gen_column(D, this_grid_dims(), D.st->j);
+}
+__global__ void k_pivot_row(Dev D, int multi) {
+    if (halted(D.st)) return;
+    stage_pivot_row(D, this_grid_dims(), D.st->r, multi);
+}
+__global__ void k_build_slist(Dev D) {
+    if (halted(D.st)) return;
+    stage_build_slist(D, this_grid_dims());
+}
+__global__ void k_update(Dev D) {
+    if (halted(D.st)) return;
+    stage_update(D, this_grid_dims(), D.st->j, D.st->r, D.st->rc);
+}
+__global__ void k_update_big(Dev D) {
+    if (halted(D.st)) return;
+    stage_update_big(D, this_grid_dims());
+}
+__global__ void k_iter_end(Dev D) {
+    if (halted(D.st)) return;
+    end_of_iteration(D);
 }
 
 // ---------------------------------------------------------------------------------------------
 // Set-up and hand-over kernels (run once per solve)
 // ---------------------------------------------------------------------------------------------
-// B^-1 = I, b = rhs (local rows); cost row cleared.   carry/mod.rs:381-426, basis_inverse_rows.rs:97-101
+// B^-1 = I, b = rhs (local rows).   carry/mod.rs:381-426, basis_inverse_rows.rs:97-101
 __global__ void k_init_planes(Dev D, const int64_t* rhs_n, const int64_t* rhs_d) {
     DState* st = D.st;
-    size_t ld = st->ld, total = (size_t)(st->mloc + 1) * ld;
+    size_t ld = st->ld, total = (size_t)(st->m + 1) * ld;
     for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
-        int li = (int)(e / ld), k = (int)(e - (size_t)li * ld);
+        int k = (int)(e / ld), li = (int)(e - (size_t)k * ld);
         int64_t n = 0, d = 1;
         if (li < st->mloc) {
             int i = st->row_lo + li;
@@ -446,15 +601,15 @@ __global__ void k_init_cost_row_artificial(Dev D, const int64_t* rhs_n, const in
     DState* st = D.st;
     if (blockIdx.x != 0 || threadIdx.x != 0) return;
     Arena ar = persistent(D);
-    size_t z = (size_t)st->mloc * st->ld;
+    for (int k = 0; k <= st->m; k++) { D.zn[k] = 0; D.zd[k] = 1; }
     Val acc = val_zero();
     Val one = make_small(1, 1);
     for (int a = 0; a < st->nr_art; a++) {
         int i = D.art_row[a];
         acc = val_fma(acc, make_small(rhs_n[i], rhs_d[i]), one, -1, D.heap, ar);
-        D.xn[z + 1 + i] = -1; D.xd[z + 1 + i] = 1;
+        D.zn[1 + i] = -1; D.zd[1 + i] = 1;
     }
-    st_val(D.xn, D.xd, z, acc);
+    st_val(D.zn, D.zd, 0, acc);
 }
 
 // K5: z_k = -sum_i c_B(i) X[i][k] over this rank's rows, for k = 0..m (column 0 gives -obj).
@@ -462,16 +617,16 @@ __global__ void k_init_cost_row_artificial(Dev D, const int64_t* rhs_n, const in
 __global__ void k_recompute_cost_row(Dev D, const int* cost_rows, int n_cost_rows, int64_t* outn, int64_t* outd) {
     DState* st = D.st;
     Arena ar = persistent(D);
-    int ld = st->ld;
+    const size_t ld = st->ld;
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k <= st->m; k += gridDim.x * blockDim.x) {
         Val acc = val_zero();
         for (int q = 0; q < n_cost_rows; q++) {
             int li = cost_rows[q];
-            size_t e = (size_t)li * ld + k;
-            int64_t xn = D.xn[e], xd = D.xd[e];
-            if (xn == 0 && xd == 1) continue;
+            size_t e = (size_t)k * ld + li;
+            int64_t xn = D.xn[e];
+            if (xn == 0) continue;
             int jb = D.basis[st->row_lo + li];
-            Val xv; xv.n = xn; xv.d = xd;
+            Val xv; xv.n = xn; xv.d = D.xd[e];
             acc = val_fma(acc, xv, make_small(D.cn[jb], D.cd[jb]), -1, D.heap, ar);
         }
         st_val(outn, outd, k, acc);
@@ -486,22 +641,22 @@ __global__ void k_cleanup_select(Dev D, int pivot_row, int* best_j) {
     Arena ar = transient(D);
     int lr = pivot_row - st->row_lo;
     bool owner = lr >= 0 && lr < st->mloc;
+    const size_t ld = st->ld;
     for (int j = st->nr_art + blockIdx.x * blockDim.x + threadIdx.x; j < st->ncols; j += gridDim.x * blockDim.x) {
         if (D.in_basis[j]) continue;
-        Val rc = price_column(D, st, j, ar);
-        if (!val_is_zero(rc)) continue;
+        Val rc = price_column_csc(D, st, j, ar);
+        if (rc.n != 0) continue;
         if (!owner) continue;
         int jj = j - st->nr_art;
-        const int64_t* rn = D.xn + (size_t)lr * st->ld + 1;
-        const int64_t* rd = D.xd + (size_t)lr * st->ld + 1;
         Val acc = val_zero();
         for (long long t = D.col_ptr[jj]; t < D.col_ptr[jj + 1]; t++) {
-            int k = D.row_idx[t];
-            Val xv = ld_val(rn, rd, k);
-            if (val_is_zero(xv)) continue;
+            size_t e = (size_t)(1 + D.row_idx[t]) * ld + lr;
+            int64_t xn = D.xn[e];
+            if (xn == 0) continue;
+            Val xv; xv.n = xn; xv.d = D.xd[e];
             acc = val_fma(acc, xv, make_small(D.an[t], D.ad[t]), 1, D.heap, ar);
         }
-        if (!val_is_zero(acc)) atomicMin(best_j, j);
+        if (acc.n != 0) atomicMin(best_j, j);
     }
 }
 
@@ -511,44 +666,55 @@ __global__ void k_generate_element(Dev D, int i, int j, int64_t* outn, int64_t* 
     if (blockIdx.x != 0 || threadIdx.x != 0) return;
     Arena ar = transient(D);
     int li = i - st->row_lo;
-    const int64_t* rn = D.xn + (size_t)li * st->ld + 1;
-    const int64_t* rd = D.xd + (size_t)li * st->ld + 1;
+    const size_t ld = st->ld;
     Val acc = val_zero();
-    if (st->phase == 1 && j < st->nr_art) acc = ld_val(rn, rd, D.art_row[j]);
+    if (st->phase == 1 && j < st->nr_art) acc = ld_val(D.xn, D.xd, (size_t)(1 + D.art_row[j]) * ld + li);
     else {
         int jj = st->phase == 1 ? j - st->nr_art : j;
         for (long long t = D.col_ptr[jj]; t < D.col_ptr[jj + 1]; t++) {
-            Val xv = ld_val(rn, rd, D.row_idx[t]);
-            if (val_is_zero(xv)) continue;
+            Val xv = ld_val(D.xn, D.xd, (size_t)(1 + D.row_idx[t]) * ld + li);
+            if (xv.n == 0) continue;
             acc = val_fma(acc, xv, make_small(D.an[t], D.ad[t]), 1, D.heap, ar);
         }
     }
     outn[0] = acc.n; outd[0] = acc.d;
 }
 
+__global__ void k_reprice_selected(Dev D) {   // rc of st->j for the step-wise API (relp_generate_column)
+    DState* st = D.st;
+    Arena ar = transient(D);
+    st->rc = price_column_csc(D, st, st->j, ar);
+}
+
 // Row/column removal (basis_inverse_rows.rs:194-205, carry/mod.rs:650-689): gather the kept rows
-// and columns of the planes into fresh planes.  keep_row[i'] / keep_col[k'] give source indices.
+// and columns of the column-major planes into fresh planes.
 __global__ void k_gather_planes(const int64_t* sn, const int64_t* sd, int sld,
                                 int64_t* tn, int64_t* td, int tld, int trows, int tcols,
                                 const int* keep_row, const int* keep_col) {
-    size_t total = (size_t)trows * tld;
+    size_t total = (size_t)tcols * tld;
     for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
-        int i = (int)(e / tld), k = (int)(e - (size_t)i * tld);
+        int k = (int)(e / tld), i = (int)(e - (size_t)k * tld);
         int64_t n = 0, d = 1;
-        if (k < tcols) { size_t s = (size_t)keep_row[i] * sld + keep_col[k]; n = sn[s]; d = sd[s]; }
+        if (i < trows) { size_t s = (size_t)keep_col[k] * sld + keep_row[i]; n = sn[s]; d = sd[s]; }
         tn[e] = n; td[e] = d;
     }
 }
+__global__ void k_gather_vec(const int64_t* sn, const int64_t* sd, int64_t* tn, int64_t* td, int count, const int* keep) {
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
+        tn[k] = sn[keep[k]]; td[k] = sd[keep[k]];
+    }
+}
 
-// Export a block of rats: escalated values are copied to the end of the transient region so that
-// one D2H copy of [export_base, tr_top) carries all limbs; handles become offsets from export_base.
-__global__ void k_export(Dev D, const int64_t* sn, const int64_t* sd, int sld, int nrows, int ncols,
-                         int64_t* on, int64_t* od, unsigned long long export_base) {
+// Export a block of rats (element (i, k) at i * rstride + k * cstride): escalated values are
+// copied to the end of the transient region so that one D2H copy of [export_base, tr_top) carries
+// all limbs; handles become offsets from export_base.  Output is row-major nrows x ncols.
+__global__ void k_export(Dev D, const int64_t* sn, const int64_t* sd, long long rstride, long long cstride,
+                         int nrows, int ncols, int64_t* on, int64_t* od, unsigned long long export_base) {
     Arena ar = transient(D);
     size_t total = (size_t)nrows * ncols;
     for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
         int i = (int)(e / ncols), k = (int)(e - (size_t)i * ncols);
-        Val v = ld_val(sn, sd, (size_t)i * sld + k);
+        Val v = ld_val(sn, sd, (size_t)((long long)i * rstride + (long long)k * cstride));
         if (v.d == 0) { v = copy_val(v, D.heap, ar); if (v.d == 0) v.n -= (int64_t)export_base; }
         on[e] = v.n; od[e] = v.d;
     }

@@ -15,6 +15,8 @@
 #define __forceinline__ inline
 #define __noinline__
 #define __shared__ static
+#define __launch_bounds__(...)
+#define __restrict__
 
 struct emul_dim3 { unsigned x, y, z; };
 static emul_dim3 blockIdx = {0, 0, 0}, threadIdx = {0, 0, 0}, blockDim = {1, 1, 1}, gridDim = {1, 1, 1};

@@ -64,6 +64,16 @@ def test_resumable(lib, seed):
     parity.check_resumable(pa_from_lp(lp), lib)
 
 
+@pytest.mark.parametrize("seed", range(8))
+def test_stage_per_launch_path(lib, seed):
+    """the one-launch-per-stage driver (what multi-GPU solves use) gives the same results"""
+    lp = feasible_lp(seed + 200, 3, 1, 3, 2, 10, frac=(seed % 2 == 0), dup_rows=(1 if seed % 4 == 0 else 0))
+    parity.check_full_solve(pa_from_lp(lp), lib, persistent=False)
+    if seed == 0:
+        parity.check_full_solve(pa_from_lp(feasible_lp(0, 6, 2, 6, 4, 24, frac=True, maxval=9, density=0.4)), lib,
+                                expect_escalation=True, persistent=False)
+
+
 def test_synthetic_tu(lib):
     parity.check_full_solve(synthetic_lp(60, 400, 6, "tu"), lib, expect_escalation=False)
 

@@ -53,6 +53,16 @@ def test_resumable(seed):
     parity.check_resumable(pa_from_lp(lp), LIB)
 
 
+@pytest.mark.parametrize("seed", range(8))
+def test_stage_per_launch_path(seed):
+    """the one-launch-per-stage driver (what multi-GPU solves use) gives the same results"""
+    lp = feasible_lp(seed + 200, 3, 1, 3, 2, 10, frac=(seed % 2 == 0), dup_rows=(1 if seed % 4 == 0 else 0))
+    parity.check_full_solve(pa_from_lp(lp), LIB, persistent=False)
+    if seed == 0:
+        parity.check_full_solve(pa_from_lp(feasible_lp(0, 6, 2, 6, 4, 24, frac=True, maxval=9, density=0.4)), LIB,
+                                expect_escalation=True, persistent=False)
+
+
 @pytest.mark.parametrize("m,n,k", [(60, 400, 6), (200, 2000, 20), (2000, 20000, 20)])
 def test_synthetic_tu(m, n, k):
     """BASELINE config 5a scaled down to sizes the oracle finishes: int64 tier, no escalation."""
