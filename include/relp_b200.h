@@ -87,6 +87,8 @@ int relp_abi_version(void);
 int relp_set_option(relp_ctx*, const char* name, int64_t value);
 /* the cudaStream_t all work of this context is enqueued on (for CUDA-event timing by the caller) */
 void* relp_stream(relp_ctx*);
+/* debug (option "trace" = 1): globaltimer of every CTA at 16 points of the last loop iteration */
+int relp_debug_trace(relp_ctx*, uint64_t* out /* n_ctas x 16 */, int32_t n_ctas);
 
 /* Multi-GPU only: attach an NCCL communicator (ncclComm_t, created by the caller from
  * torch.distributed's rendezvous) used for the per-pivot pivot-row broadcast and the two

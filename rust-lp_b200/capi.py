@@ -21,7 +21,7 @@ FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
 
 # every symbol include/relp_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
-    "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_comm_unique_id",
+    "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_comm_unique_id",
     "relp_attach_comm", "relp_load_matrix", "relp_carry_create_partially_artificial",
     "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_price",
     "relp_generate_column", "relp_ratio_test", "relp_change_basis", "relp_generate_element",
@@ -71,6 +71,7 @@ def load_library(path=None):
     L.relp_set_option.argtypes = [vp, C.c_char_p, i64]
     L.relp_stream.argtypes = [vp]
     L.relp_stream.restype = vp
+    L.relp_debug_trace.argtypes = [vp, vp, i32]
     L.relp_comm_unique_id.argtypes = [vp, C.c_char_p]
     L.relp_attach_comm.argtypes = [vp, vp, C.c_char_p]
     L.relp_load_matrix.argtypes = [vp, i32, i32] + [vp] * 8
@@ -144,6 +145,11 @@ class Carry:
 
     def stream(self):
         return self.L.relp_stream(self.h)
+
+    def debug_trace(self, n_ctas=148):
+        out = np.zeros((n_ctas, 16), np.uint64)
+        self._chk(self.L.relp_debug_trace(self.h, _p(out), n_ctas))
+        return out
 
     def close(self):
         if getattr(self, "h", None):

@@ -94,6 +94,7 @@ RELP_HD int ctz32(uint32_t x) {
 RELP_HD uint64_t gcd64(uint64_t a, uint64_t b) {
     if (a == 0) return b;
     if (b == 0) return a;
+    if (a == 1 || b == 1) return 1;
     int sh = ctz64(a | b);
     a >>= ctz64(a);
     do {
@@ -157,6 +158,9 @@ RELP_HD bool small_fma(const Val& x, const Val& a, const Val& b, int s, Val* out
 // out = x / y  (y != 0)      (sparse.rs:291-301 element_wise_divide, tableau/mod.rs:229 ratio)
 RELP_HD bool small_div(const Val& x, const Val& y, Val* out) {
     if (x.n == 0) { *out = val_zero(); return true; }
+    if (y.d == 1 && (y.n == 1 || y.n == -1)) {          // unit pivots (totally unimodular bases)
+        *out = make_small(y.n > 0 ? x.n : -x.n, x.d); return true;
+    }
     uint64_t xn = abs64(x.n), yn = abs64(y.n);
     uint64_t g1 = gcd64(xn, yn);
     uint64_t g2 = (x.d == 1 || y.d == 1) ? 1 : gcd64((uint64_t)x.d, (uint64_t)y.d);

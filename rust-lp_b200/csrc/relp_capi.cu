@@ -87,11 +87,11 @@ struct relp_ctx {
     // device buffers
     DBuf<DState> st; DBuf<uint32_t> heap;
     DBuf<int64_t> xn, xd, zn, zd, an_d, ad_d, cn_d, cd_d, rhsn_d, rhsd_d, dn, dd, pnd, tmpn, tmpd, sell_an, sell_ad;
-    DBuf<long long> col_ptr_d, sell_ptr; DBuf<int> row_idx_d, sell_row, basis, art_row, tlist, slist, cost_rows, scratch_i;
+    DBuf<long long> col_ptr_d, sell_ptr; DBuf<uint32_t> zbits; DBuf<int> row_idx_d, sell_row, basis, art_row, tlist, slist, cost_rows, scratch_i;
     DBuf<unsigned char> in_basis;
-    DBuf<int2> worklist; DBuf<Cand> cand, cand2, gather; DBuf<LogEntry> log;
+    DBuf<int2> worklist; DBuf<Cand> cand, cand2, gather; DBuf<LogEntry> log; DBuf<unsigned long long> trace;
     int n_slices = 0, a_int = 1, coop_blocks = 0, last_ratio_blocks = 1;
-    bool use_persistent = true;
+    bool use_persistent = true, smem_opt_in = false;
     DState* h_st = nullptr;       // pinned mirror
     Dev D;
     bool loaded = false, carry_ready = false;
@@ -109,7 +109,10 @@ struct relp_ctx {
 
 #ifdef RELP_EMUL
 #define LAUNCH(c, kern, grid, block, ...) do { kern(__VA_ARGS__); (c)->launches++; } while (0)
+#define LAUNCH_SMEM(c, kern, grid, block, smem, ...) do { kern(__VA_ARGS__); (c)->launches++; } while (0)
 #else
+#define LAUNCH_SMEM(c, kern, grid, block, smem, ...)                                        \
+    do { kern<<<(grid), (block), (smem), (c)->stream>>>(__VA_ARGS__); (c)->launches++; } while (0)
 #define LAUNCH(c, kern, grid, block, ...)                                                   \
     do { kern<<<(grid), (block), 0, (c)->stream>>>(__VA_ARGS__); (c)->launches++; } while (0)
 #endif
@@ -290,7 +293,7 @@ static void wire_dev(relp_ctx* c) {
     D.art_row = c->art_row.p; D.dn = c->dn.p; D.dd = c->dd.p;
     D.pn = c->pnd.p; D.pd = c->pnd.p + (c->m + 1);
     D.tlist = c->tlist.p; D.slist = c->slist.p; D.worklist = c->worklist.p; D.cand = c->cand.p; D.cand2 = c->cand2.p;
-    D.gather = c->gather.p; D.log = c->log.p; D.log_cap = (long long)c->log.n;
+    D.gather = c->gather.p; D.log = c->log.p; D.log_cap = (long long)c->log.n; D.trace = c->trace.p; D.zbits = c->zbits.p;
 }
 
 static const int MAX_PARTIAL_BLOCKS = 2048;
@@ -300,7 +303,7 @@ static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
     c->ld = std::max(16, (c->mloc + 15) / 16 * 16);
     size_t plane = (size_t)(m + 1) * c->ld;
     if (c->xn.alloc(plane) || c->xd.alloc(plane) || c->zn.alloc(m + 1) || c->zd.alloc(m + 1)) return RELP_ERR_CUDA;
-    if (c->in_basis.alloc(ncols_max)) return RELP_ERR_CUDA;
+    if (c->in_basis.alloc(ncols_max) || c->zbits.alloc((m + 31) / 32 + 1)) return RELP_ERR_CUDA;
     if (c->dn.alloc(c->mloc + 1) || c->dd.alloc(c->mloc + 1) || c->tmpn.alloc(m + 2) || c->tmpd.alloc(m + 2)) return RELP_ERR_CUDA;
     if (c->pnd.alloc(2 * (size_t)(m + 1))) return RELP_ERR_CUDA;
     if (c->basis.alloc(m) || c->art_row.alloc(m) || c->tlist.alloc(c->mloc + 1) || c->slist.alloc(m + 1)) return RELP_ERR_CUDA;
@@ -338,6 +341,12 @@ __global__ void k_set_pivot(DState* st, int j, int r, int set_zero_rc) {
 }
 __global__ void k_reset_transient(DState* st) { st->tr_top = st->tr_base; }
 
+// shared-memory words for the -pi bitmap (0: too large, kernels test the global bitmap)
+static int zbits_smem_words(relp_ctx* c) {
+    int w = (c->m + 31) / 32;
+    return (size_t)w * 4 <= 160 * 1024 ? w : 0;
+}
+
 static int nccl_check(int rc, const char* what) {
     if (rc == 0) return 0;
     set_error(std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "nccl error"));
@@ -358,7 +367,9 @@ static int enqueue_price(relp_ctx* c, int rule) {
     DState* hs = c->h_st;
     long long lanes = (long long)(hs->sl_hi - hs->sl_lo) * 32 + (hs->art_hi - hs->art_lo);
     int gb = grid_for(c, std::max<long long>(lanes, 1));
-    LAUNCH(c, k_price, gb, RELP_THREADS, c->D, mode);
+    int sw = zbits_smem_words(c);
+    if ((size_t)sw * 4 > 40 * 1024) sw = 0;      // stage wrapper: stay within the default shared-memory limit
+    LAUNCH_SMEM(c, k_price, gb, RELP_THREADS, (size_t)sw * 4, c->D, mode, sw);
     return enqueue_select(c, mode, gb, rule);
 }
 static int enqueue_column_and_ratio(relp_ctx* c, bool select_row) {
@@ -399,7 +410,7 @@ static int check_cuda(relp_ctx* c) {
 
 static int launch_persistent(relp_ctx* c, int rule, int max_iters) {
 #ifdef RELP_EMUL
-    k_simplex_loop(c->D, rule, max_iters);
+    k_simplex_loop(c->D, rule, max_iters, 0);
     c->launches++;
     return 0;
 #else
@@ -409,8 +420,15 @@ static int launch_persistent(relp_ctx* c, int rule, int max_iters) {
         if (per_sm < 1) { set_error("persistent kernel does not fit on an SM"); return RELP_ERR_CUDA; }
         c->coop_blocks = c->sm_count;        // one CTA per SM
     }
-    void* args[] = { (void*)&c->D, (void*)&rule, (void*)&max_iters };
-    CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_simplex_loop, dim3(c->coop_blocks), dim3(RELP_PTHREADS), args, 0, c->stream));
+    int sw = zbits_smem_words(c);
+    size_t smem = (size_t)sw * 4;
+    if (smem > 40 * 1024 && !c->smem_opt_in) {
+        CUDA_TRY(cudaFuncSetAttribute(k_simplex_loop, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        CUDA_TRY(cudaFuncSetAttribute(k_price, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        c->smem_opt_in = true;
+    }
+    void* args[] = { (void*)&c->D, (void*)&rule, (void*)&max_iters, (void*)&sw };
+    CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_simplex_loop, dim3(c->coop_blocks), dim3(RELP_PTHREADS), args, smem, c->stream));
     c->launches++;
     return 0;
 #endif
@@ -479,6 +497,7 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     wire_dev(c);
     LAUNCH(c, k_init_planes, c->sm_count * 8, RELP_THREADS, c->D, c->rhsn_d.p, c->rhsd_d.p);
     LAUNCH(c, k_init_cost_row_artificial, 1, 1, c->D, c->rhsn_d.p, c->rhsd_d.p);
+    LAUNCH(c, k_build_zbits, grid_for(c, (m + 31) / 32), RELP_THREADS, c->D);
     if (check_cuda(c)) return RELP_ERR_CUDA;
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0;
@@ -532,6 +551,7 @@ static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbe
         LAUNCH(c, k_sum_partials, grid_for(c, cnt, 2), RELP_THREADS, c->D, all.p, c->world, cnt, c->zn.p, c->zd.p);
         CUDA_TRY(cudaStreamSynchronize(c->stream));
     }
+    LAUNCH(c, k_build_zbits, grid_for(c, (m + 31) / 32), RELP_THREADS, c->D);
     if (check_cuda(c)) return RELP_ERR_CUDA;
     if (sync_state(c)) return RELP_ERR_CUDA;
     if (c->h_st->err) return err_status(c->h_st);
@@ -898,8 +918,19 @@ int relp_rows_removed(relp_ctx* c, int32_t* out, int32_t cap) {
 int relp_set_option(relp_ctx* c, const char* name, int64_t value) {
     if (!c || !name) return RELP_ERR_ARGUMENT;
     if (!strcmp(name, "persistent")) { c->use_persistent = value != 0; return RELP_OK; }
+    if (!strcmp(name, "trace")) {      // debug: per-CTA barrier arrival times of the last iteration
+        if (value) { if (c->trace.alloc(16 * 4096)) return RELP_ERR_CUDA; cudaMemset(c->trace.p, 0, 16 * 4096 * 8); }
+        else c->trace.release();
+        c->D.trace = c->trace.p;
+        return RELP_OK;
+    }
     return RELP_ERR_ARGUMENT;
 }
 void* relp_stream(relp_ctx* c) { return c ? (void*)c->stream : nullptr; }
+int relp_debug_trace(relp_ctx* c, uint64_t* out, int32_t n_ctas) {
+    if (!c || !c->trace.p || n_ctas > 4096) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaMemcpy(out, c->trace.p, (size_t)n_ctas * 16 * 8, cudaMemcpyDeviceToHost));
+    return RELP_OK;
+}
 
 }  // extern "C"

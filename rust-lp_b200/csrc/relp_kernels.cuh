@@ -89,18 +89,36 @@ struct Dev {
     Cand* cand2;                              // per-block partial argmin: ratio test
     Cand* gather;                             // world candidates (multi-GPU all-gather buffer)
     LogEntry* log; long long log_cap;
+    uint32_t* zbits;                          // bit i set <=> -pi_i != 0 (maintained with the cost row)
+    unsigned long long* trace;                // debug: per-CTA arrival time at each barrier (16 slots per CTA)
 };
 
 #define RELP_THREADS 256          // stage wrappers
-#define RELP_PTHREADS 1024        // persistent kernel: one CTA of 1024 threads per SM
+#ifndef RELP_PTHREADS
+#define RELP_PTHREADS 512         // persistent kernel: one CTA per SM; 512 threads leave 128 registers each
+#endif
+#ifndef RELP_CHP
+#define RELP_CHP 8                // pricing: row indices / -pi gathers in flight per lane
+#endif
+#ifndef RELP_CHG
+#define RELP_CHG 8                // column generation: B^-1 column reads in flight per row
+#endif
 #define RELP_MAXWARPS 32
 
 struct Grid { int tid, nth, bid, nb; };
+// loop invariants of DState, read once per kernel (every barrier invalidates L1, so re-reading
+// them from global memory in every stage costs an L2 round trip each time)
+struct Inv { int m, mloc, row_lo, ld, n, nr_art, phase, ncols, sl_lo, sl_hi, art_lo, art_hi, a_int; };
 __device__ __forceinline__ Grid this_grid_dims() {
     Grid g; g.tid = blockIdx.x * blockDim.x + threadIdx.x; g.nth = gridDim.x * blockDim.x;
     g.bid = blockIdx.x; g.nb = gridDim.x; return g;
 }
 
+__device__ __forceinline__ Inv load_inv(const DState* st) {
+    Inv I; I.m = st->m; I.mloc = st->mloc; I.row_lo = st->row_lo; I.ld = st->ld; I.n = st->n; I.nr_art = st->nr_art;
+    I.phase = st->phase; I.ncols = st->ncols; I.sl_lo = st->sl_lo; I.sl_hi = st->sl_hi; I.art_lo = st->art_lo;
+    I.art_hi = st->art_hi; I.a_int = st->a_int; return I;
+}
 __device__ __forceinline__ Arena transient(const Dev& D) {
     Arena a; a.top = &D.st->tr_top; a.limit = D.st->tr_limit; a.err = &D.st->err; return a;
 }
@@ -225,17 +243,33 @@ __device__ __forceinline__ void price_consider(const Dev& D, Val rc, int j, int 
     if (cand_better(c, best, mode, D.heap)) best = c;
 }
 
-__device__ void stage_price(const Dev& D, const Grid& g, int mode) {
+#ifndef RELP_EMUL
+extern __shared__ uint32_t relp_dyn_smem[];
+#endif
+
+// `smem_words` > 0: the CTA first copies the "-pi_i != 0" bitmap into shared memory, so that the
+// per-entry test is a shared-memory lookup (a 32-lane gather from global memory costs 32 L1
+// wavefronts; measured, that was the whole pricing time).  -pi itself is read only where the bit
+// is set.  smem_words == 0 (bitmap too large, or the CPU stand-in): test the global bitmap.
+__device__ void stage_price(const Dev& D, const Grid& g, const Inv& I, int mode, int smem_words) {
     const DState* st = D.st;
     Arena ar = transient(D);
-    const int phase = st->phase, nr_art = st->nr_art, ncols = st->ncols, n = st->n;
+    const int phase = I.phase, nr_art = I.nr_art, ncols = I.ncols, n = I.n;
     const int start = (mode == ARG_FIRST && st->last_selected >= 0) ? st->last_selected : 0;
     const int off = phase == 1 ? nr_art : 0;
-    const int64_t* __restrict__ zn = D.zn + 1; const int64_t* __restrict__ zd = D.zd + 1;
+    const int64_t* zn = D.zn + 1; const int64_t* zd = D.zd + 1;   // mutable between stages: no __restrict__
+    const uint32_t* zb = D.zbits;
+#ifndef RELP_EMUL
+    if (smem_words > 0) {
+        for (int w = threadIdx.x; w < smem_words; w += blockDim.x) relp_dyn_smem[w] = D.zbits[w];
+        __syncthreads();
+        zb = relp_dyn_smem;
+    }
+#endif
     Cand best = cand_none();
     if (phase == 1) {
         Val one = make_small(1, 1);
-        for (int a = st->art_lo + g.tid; a < st->art_hi; a += g.nth) {
+        for (int a = I.art_lo + g.tid; a < I.art_hi; a += g.nth) {
             if (D.in_basis[a]) continue;
             Val rc = val_fma(ld_val(zn, zd, D.art_row[a]), one, one, 1, D.heap, ar);
             price_consider(D, rc, a, mode, start, ncols, best);
@@ -245,29 +279,49 @@ __device__ void stage_price(const Dev& D, const Grid& g, int mode) {
     const int gw = 0, nw = 1;        // sequential stand-in: one thread plays every lane in turn
     for (int lane = 0; lane < 32; lane++)
 #else
-    const int lane = g.tid & 31, gw = g.tid >> 5, nw = g.nth >> 5;
+    // slices are dealt round-robin over the CTAs so that every SM's load/store unit shares the work
+    const int lane = threadIdx.x & 31, gw = (threadIdx.x >> 5) * g.nb + g.bid, nw = g.nth >> 5;
 #endif
-    for (int s = st->sl_lo + gw; s < st->sl_hi; s += nw) {
-        const int a_int = st->a_int;
+    for (int s = I.sl_lo + gw; s < I.sl_hi; s += nw) {
+        const int a_int = I.a_int;
         int jj = s * 32 + lane;
         long long base = D.sell_ptr[s];
         int width = (int)((D.sell_ptr[s + 1] - base) >> 5);
         bool live = jj < n && !D.in_basis[off + jj];
         Val acc = (phase == 2 && live) ? make_small(D.cn[jj], D.cd[jj]) : val_zero();
         const int* __restrict__ rows = D.sell_row + base + lane;
-        for (int t = 0; t < width; t += 4) {
-            int rr[4]; int64_t zz[4];
+        // Pass 1 (streaming): test every entry's row against the bitmap and remember the hits of
+        // this lane as a bit mask; the row indices of the next chunk are requested before this
+        // chunk is consumed.  Pass 2: the lanes walk their own hits in lockstep, two at a time, so
+        // a warp pays (max hits per lane)/2 dependent round trips instead of one per hit position.
+        for (int seg = 0; seg < width; seg += 64) {
+            const int wseg = width - seg < 64 ? width - seg : 64;
+            unsigned long long hits = 0;
+            int rr[RELP_CHP], nx[RELP_CHP];
 #pragma unroll
-            for (int u = 0; u < 4; u++) rr[u] = (live && t + u < width) ? rows[(size_t)(t + u) * 32] : -1;
+            for (int u = 0; u < RELP_CHP; u++) rr[u] = (live && u < wseg) ? rows[(size_t)(seg + u) * 32] : -1;
+            for (int t = 0; t < wseg; t += RELP_CHP) {
 #pragma unroll
-            for (int u = 0; u < 4; u++) zz[u] = rr[u] >= 0 ? zn[rr[u]] : 0;
+                for (int u = 0; u < RELP_CHP; u++) nx[u] = (live && t + RELP_CHP + u < wseg) ? rows[(size_t)(seg + t + RELP_CHP + u) * 32] : -1;
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-                if (zz[u] == 0) continue;
-                size_t e = (size_t)base + (size_t)(t + u) * 32 + lane;
-                Val zv; zv.n = zz[u]; zv.d = zd[rr[u]];
-                Val av = make_small(D.sell_an[e], a_int ? 1 : D.sell_ad[e]);
-                acc = val_fma(acc, zv, av, 1, D.heap, ar);
+                for (int u = 0; u < RELP_CHP; u++) {
+                    int row = rr[u];
+                    if (row >= 0 && ((zb[row >> 5] >> (row & 31)) & 1u)) hits |= 1ull << (t + u);
+                }
+#pragma unroll
+                for (int u = 0; u < RELP_CHP; u++) rr[u] = nx[u];
+            }
+            while (hits) {
+                int ta = ctz64(hits); hits &= hits - 1;
+                int tb = hits ? ctz64(hits) : -1; if (tb >= 0) hits &= hits - 1;
+                size_t ea = (size_t)base + (size_t)(seg + ta) * 32 + lane;
+                size_t eb = tb >= 0 ? (size_t)base + (size_t)(seg + tb) * 32 + lane : ea;
+                int ra = D.sell_row[ea], rb = D.sell_row[eb];
+                Val za = ld_val(zn, zd, ra), zb2 = ld_val(zn, zd, rb);
+                Val aa = make_small(D.sell_an[ea], a_int ? 1 : D.sell_ad[ea]);
+                Val ab = make_small(D.sell_an[eb], a_int ? 1 : D.sell_ad[eb]);
+                acc = val_fma(acc, za, aa, 1, D.heap, ar);
+                if (tb >= 0) acc = val_fma(acc, zb2, ab, 1, D.heap, ar);
             }
         }
         if (live) price_consider(D, acc, off + jj, mode, start, ncols, best);
@@ -280,38 +334,50 @@ __device__ void stage_price(const Dev& D, const Grid& g, int mode) {
 // Stage C -- K2 + K4: d_i = sum_k Binv[i][k] a_kj for every local row, the list of rows with
 // d_i != 0, and the exact argmin of b_i / d_i over rows with d_i > 0 (block level).
 // ---------------------------------------------------------------------------------------------
-__device__ void stage_gen_column(const Dev& D, const Grid& g, int j) {
+__device__ void stage_gen_column(const Dev& D, const Grid& g, const Inv& I, int j) {
     DState* st = D.st;
     Arena ar = transient(D);
     int unit_row = -1; long long t0 = 0, t1 = 0;
-    if (st->phase == 1 && j < st->nr_art) unit_row = D.art_row[j];
-    else { int jj = st->phase == 1 ? j - st->nr_art : j; t0 = D.col_ptr[jj]; t1 = D.col_ptr[jj + 1]; }
-    const int mloc = st->mloc; const size_t ld = st->ld;
-    const int64_t* __restrict__ xn = D.xn + ld;     // column 1 + k at xn + k * ld
-    const int64_t* __restrict__ xd = D.xd + ld;
+    if (I.phase == 1 && j < I.nr_art) unit_row = D.art_row[j];
+    else { int jj = I.phase == 1 ? j - I.nr_art : j; t0 = D.col_ptr[jj]; t1 = D.col_ptr[jj + 1]; }
+    const int mloc = I.mloc; const size_t ld = I.ld;
+    const int64_t* xn = D.xn + ld;     // column 1 + k at xn + k * ld
+    const int64_t* xd = D.xd + ld;
     Cand best = cand_none();
     for (int li = g.tid; li < mloc; li += g.nth) {
+        // b_i and the row's basis column are requested up front: they are needed only by rows
+        // with d_i > 0, but issuing them now takes two round trips off that critical path
+        Val bv = ld_val(D.xn, D.xd, li);
+        int bkey = D.basis[I.row_lo + li];
         Val acc = val_zero();
         if (unit_row >= 0) acc = copy_val(ld_val(xn, xd, (size_t)unit_row * ld + li), D.heap, ar);
-        else for (long long t = t0; t < t1; t += 4) {
-            int kk[4]; int64_t xx[4];
+        else for (long long seg = t0; seg < t1; seg += 64) {
+            // Pass 1 (streaming, coalesced over rows): which entries of this row are nonzero?
+            // Pass 2: the rows of a warp walk their own hits in lockstep (operands come back from
+            // L1), so a warp pays max-hits-per-row round trips, not one per distinct hit column.
+            const int wseg = t1 - seg < 64 ? (int)(t1 - seg) : 64;
+            unsigned long long hits = 0;
+            for (int t = 0; t < wseg; t += RELP_CHG) {
+                int kk[RELP_CHG]; int64_t xx[RELP_CHG];
 #pragma unroll
-            for (int u = 0; u < 4; u++) kk[u] = t + u < t1 ? D.row_idx[t + u] : -1;
+                for (int u = 0; u < RELP_CHG; u++) kk[u] = t + u < wseg ? D.row_idx[seg + t + u] : -1;
 #pragma unroll
-            for (int u = 0; u < 4; u++) xx[u] = kk[u] >= 0 ? xn[(size_t)kk[u] * ld + li] : 0;
+                for (int u = 0; u < RELP_CHG; u++) xx[u] = kk[u] >= 0 ? xn[(size_t)kk[u] * ld + li] : 0;
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-                if (xx[u] == 0) continue;
-                Val xv; xv.n = xx[u]; xv.d = xd[(size_t)kk[u] * ld + li];
-                acc = val_fma(acc, xv, make_small(D.an[t + u], D.ad[t + u]), 1, D.heap, ar);
+                for (int u = 0; u < RELP_CHG; u++) if (xx[u] != 0) hits |= 1ull << (t + u);
+            }
+            while (hits) {
+                int t = ctz64(hits); hits &= hits - 1;
+                size_t e = (size_t)D.row_idx[seg + t] * ld + li;
+                acc = val_fma(acc, ld_val(xn, xd, e), make_small(D.an[seg + t], D.ad[seg + t]), 1, D.heap, ar);
             }
         }
         st_val(D.dn, D.dd, li, acc);
         if (acc.n != 0) {
             int p = list_append(&st->T); D.tlist[p] = li;
             if (val_sign(acc, D.heap) > 0) {
-                Cand c; c.v = val_div(ld_val(D.xn, D.xd, li), acc, D.heap, ar);
-                c.idx = st->row_lo + li; c.key = D.basis[c.idx];
+                Cand c; c.v = val_div(bv, acc, D.heap, ar);
+                c.idx = I.row_lo + li; c.key = bkey;
                 if (cand_better(c, best, ARG_RATIO, D.heap)) best = c;
             }
         }
@@ -324,19 +390,19 @@ __device__ void stage_gen_column(const Dev& D, const Grid& g, int j) {
 // Stage D -- K1a (owner of row r): p_k = X[r][k] / d_r for k = 0..m, written back to row r and
 // staged in the pivot-row buffer; list of columns with p_k != 0.
 // ---------------------------------------------------------------------------------------------
-__device__ void stage_pivot_row(const Dev& D, const Grid& g, int r, int multi) {
+__device__ void stage_pivot_row(const Dev& D, const Grid& g, const Inv& I, int r, int multi) {
     DState* st = D.st;
-    int lr = r - st->row_lo;
-    bool owner = lr >= 0 && lr < st->mloc;
+    int lr = r - I.row_lo;
+    bool owner = lr >= 0 && lr < I.mloc;
     if (!owner) {   // multi-GPU: contribute zeros to the sum all-reduce that replicates the row
-        for (int k = g.tid; k <= st->m; k += g.nth) { D.pn[k] = 0; D.pd[k] = 0; }
+        for (int k = g.tid; k <= I.m; k += g.nth) { D.pn[k] = 0; D.pd[k] = 0; }
         return;
     }
     Val pivot = ld_val(D.dn, D.dd, lr);
     if (pivot.n == 0) { if (g.tid == 0) atomicOr(&st->err, ERR_ZERO_PIVOT); return; }
     Arena ar = persistent(D);
-    const size_t ld = st->ld;
-    for (int k = g.tid; k <= st->m; k += g.nth) {
+    const size_t ld = I.ld;
+    for (int k = g.tid; k <= I.m; k += g.nth) {
         size_t e = (size_t)k * ld + lr;
         int64_t x = D.xn[e];
         if (x == 0) { if (multi) { D.pn[k] = 0; D.pd[k] = 1; } continue; }
@@ -350,9 +416,9 @@ __device__ void stage_pivot_row(const Dev& D, const Grid& g, int r, int multi) {
 }
 
 // multi-GPU: every rank derives the column list from the replicated pivot row
-__device__ void stage_build_slist(const Dev& D, const Grid& g) {
+__device__ void stage_build_slist(const Dev& D, const Grid& g, const Inv& I) {
     DState* st = D.st;
-    for (int k = g.tid; k <= st->m; k += g.nth)
+    for (int k = g.tid; k <= I.m; k += g.nth)
         if (D.pn[k] != 0) { int s = list_append(&st->S); D.slist[s] = k; }
 }
 
@@ -361,10 +427,10 @@ __device__ void stage_build_slist(const Dev& D, const Grid& g) {
 // row.  Fixed-width tier in place; elements whose operands or result leave int64/int64 are queued
 // for the multi-limb stage.  One thread does the basis bookkeeping (tableau/mod.rs:72-84).
 // ---------------------------------------------------------------------------------------------
-__device__ void stage_update(const Dev& D, const Grid& g, int j, int r, Val rc) {
+__device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, int r, Val rc) {
     DState* st = D.st;
-    const int T = st->T, S = st->S; const size_t ld = st->ld;
-    const int lr = r - st->row_lo;
+    const int T = st->T, S = st->S; const size_t ld = I.ld;
+    const int lr = r - I.row_lo;
     const long long total = (long long)T * S;
     for (long long w = g.tid; w < total; w += g.nth) {
         int s = (int)(w / T), t = (int)(w - (long long)s * T);
@@ -385,6 +451,10 @@ __device__ void stage_update(const Dev& D, const Grid& g, int j, int r, Val rc) 
             int k = D.slist[s];
             Val z = val_fma(ld_val(D.zn, D.zd, k), rc, ld_val(D.pn, D.pd, k), -1, D.heap, ar);
             st_val(D.zn, D.zd, k, z);
+            if (k > 0) {
+                uint32_t bit = 1u << ((k - 1) & 31);
+                if (z.n != 0) atomicOr(&D.zbits[(k - 1) >> 5], bit); else atomicAnd(&D.zbits[(k - 1) >> 5], ~bit);
+            }
         }
     }
     if (g.tid == 0) {
@@ -392,7 +462,7 @@ __device__ void stage_update(const Dev& D, const Grid& g, int j, int r, Val rc) 
         D.basis[r] = j;
         D.in_basis[leaving] = 0; D.in_basis[j] = 1;
         st->leaving = leaving; st->j = j; st->r = r;
-        int b_nz = (lr >= 0 && lr < st->mloc) ? (D.xn[lr] != 0) : (D.pn[0] != 0);   // p_0 = b_r / pivot
+        int b_nz = (lr >= 0 && lr < I.mloc) ? (D.xn[lr] != 0) : (D.pn[0] != 0);   // p_0 = b_r / pivot
         int Tl = T - 1;                       // reference's col.len() - 1 (rows eliminated) on this rank
         int Sl = S - b_nz + 1;                // nnz(B^-1 row r) + 1
         if ((long long)st->iter < D.log_cap) {
@@ -405,9 +475,9 @@ __device__ void stage_update(const Dev& D, const Grid& g, int j, int r, Val rc) 
 }
 
 // Stage F -- K1c: the queued elements in the multi-limb tier.
-__device__ void stage_update_big(const Dev& D, const Grid& g) {
+__device__ void stage_update_big(const Dev& D, const Grid& g, const Inv& I) {
     DState* st = D.st;
-    const int n = st->wl_count; const size_t ld = st->ld;
+    const int n = st->wl_count; const size_t ld = I.ld;
     Arena ar = persistent(D);
     for (int w = g.tid; w < n; w += g.nth) {
         int2 it = D.worklist[w];
@@ -472,18 +542,21 @@ __device__ __forceinline__ unsigned long long gtime() {
     unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t;
 }
 #define GRID_SYNC() cooperative_groups::this_grid().sync()
+#define TRACE(k) do { if (threadIdx.x == 0 && D.trace) D.trace[(size_t)g.bid * 16 + (k)] = gtime(); } while (0)
 #else
 static inline unsigned long long gtime() { return 0; }
 #define GRID_SYNC() do {} while (0)
+#define TRACE(k) do {} while (0)
 #endif
 
 // ---------------------------------------------------------------------------------------------
 // The persistent loop: phase_one::primal / phase_two::primal (phase_one.rs:135-169,
 // phase_two.rs:32-50) entirely on the device.  Cooperative launch, one CTA per SM.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int rule, int max_iters) {
+__global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int rule, int max_iters, int smem_words) {
     DState* st = D.st;
     const Grid g = this_grid_dims();
+    const Inv I = load_inv(st);
     const int mode = rule == RULE_DANTZIG ? ARG_DANTZIG : ARG_FIRST;
     unsigned long long t0 = gtime();
     for (int it = 0; it < max_iters; it++) {
@@ -495,26 +568,37 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
             GRID_SYNC();
             if (g.tid == 0) st->compacting = 0;
         }
-        stage_price(D, g, mode);
+        TRACE(0);
+        stage_price(D, g, I, mode, smem_words);
+        TRACE(1);
         GRID_SYNC();
         unsigned long long t1 = gtime();
+        TRACE(2);
         Cand col = reduce_candidates(D.cand, g.nb, mode, D.heap);      // same winner in every CTA
         if (g.tid == 0) commit_column(st, col, rule);
         if (col.idx < 0) break;
-        stage_gen_column(D, g, col.idx);
+        TRACE(3);
+        stage_gen_column(D, g, I, col.idx);
+        TRACE(4);
         GRID_SYNC();
+        TRACE(5);
         unsigned long long t2 = gtime();
         Cand row = reduce_candidates(D.cand2, g.nb, ARG_RATIO, D.heap);
         if (g.tid == 0) commit_row(st, row);
         if (row.idx < 0) break;
-        stage_pivot_row(D, g, row.idx, 0);
+        TRACE(6);
+        stage_pivot_row(D, g, I, row.idx, 0);
+        TRACE(7);
         GRID_SYNC();
+        TRACE(8);
         unsigned long long t3 = gtime();
-        stage_update(D, g, col.idx, row.idx, col.v);
+        stage_update(D, g, I, col.idx, row.idx, col.v);
+        TRACE(9);
         GRID_SYNC();
         unsigned long long t4 = gtime();
+        TRACE(10);
         if (st->wl_count > 0) {                 // final after the barrier: uniform
-            stage_update_big(D, g);
+            stage_update_big(D, g, I);
             GRID_SYNC();
         }
         if (g.tid == 0) {
@@ -537,9 +621,9 @@ __global__ void k_begin(Dev D) {      // housekeeping that the persistent loop d
     if (st->compacting) stage_compact(D, this_grid_dims());
 }
 __global__ void k_begin2(Dev D) { if (!halted(D.st)) D.st->compacting = 0; }
-__global__ void k_price(Dev D, int mode) {
+__global__ void k_price(Dev D, int mode, int smem_words) {
     if (halted(D.st)) return;
-    stage_price(D, this_grid_dims(), mode);
+    stage_price(D, this_grid_dims(), load_inv(D.st), mode, smem_words);
 }
 // reduce `count` candidates (this rank's blocks, or the all-gather buffer) and either commit the
 // decision or post this rank's winner to gather[slot] (multi-GPU stage 1)
@@ -554,23 +638,23 @@ __global__ void k_select(Dev D, int mode, int count, int from_gather, int slot, 
 }
 __global__ void k_gen_column(Dev D) {
     if (halted(D.st)) return;
-    stage_gen_column(D, this_grid_dims(), D.st->j);
+    stage_gen_column(D, this_grid_dims(), load_inv(D.st), D.st->j);
 }
 __global__ void k_pivot_row(Dev D, int multi) {
     if (halted(D.st)) return;
-    stage_pivot_row(D, this_grid_dims(), D.st->r, multi);
+    stage_pivot_row(D, this_grid_dims(), load_inv(D.st), D.st->r, multi);
 }
 __global__ void k_build_slist(Dev D) {
     if (halted(D.st)) return;
-    stage_build_slist(D, this_grid_dims());
+    stage_build_slist(D, this_grid_dims(), load_inv(D.st));
 }
 __global__ void k_update(Dev D) {
     if (halted(D.st)) return;
-    stage_update(D, this_grid_dims(), D.st->j, D.st->r, D.st->rc);
+    stage_update(D, this_grid_dims(), load_inv(D.st), D.st->j, D.st->r, D.st->rc);
 }
 __global__ void k_update_big(Dev D) {
     if (halted(D.st)) return;
-    stage_update_big(D, this_grid_dims());
+    stage_update_big(D, this_grid_dims(), load_inv(D.st));
 }
 __global__ void k_iter_end(Dev D) {
     if (halted(D.st)) return;
@@ -610,6 +694,17 @@ __global__ void k_init_cost_row_artificial(Dev D, const int64_t* rhs_n, const in
         D.zn[1 + i] = -1; D.zd[1 + i] = 1;
     }
     st_val(D.zn, D.zd, 0, acc);
+}
+
+// bitmap of nonzero -pi entries, rebuilt whenever the cost row is replaced wholesale
+__global__ void k_build_zbits(Dev D) {
+    DState* st = D.st;
+    int nwords = (st->m + 31) >> 5;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += gridDim.x * blockDim.x) {
+        uint32_t bits = 0;
+        for (int b = 0; b < 32; b++) { int i = w * 32 + b; if (i < st->m && D.zn[1 + i] != 0) bits |= 1u << b; }
+        D.zbits[w] = bits;
+    }
 }
 
 // K5: z_k = -sum_i c_B(i) X[i][k] over this rank's rows, for k = 0..m (column 0 gives -obj).

@@ -4,10 +4,12 @@ from rust_lp_b200 import capi
 from rust_lp_b200.synth import synthetic_lp
 m, n = int(sys.argv[1]), int(sys.argv[2])
 variant = sys.argv[3] if len(sys.argv) > 3 else "tu"
+lib = sys.argv[4] if len(sys.argv) > 4 else None
+reps = int(sys.argv[5]) if len(sys.argv) > 5 else 3
 pa = synthetic_lp(m, n, 20, variant)
-for rep in range(3):
+for rep in range(reps):
     t0 = time.time()
-    c = capi.Carry(pa, heap_words=1 << 26)
+    c = capi.Carry(pa, heap_words=1 << 26, lib_path=lib)
     t1 = time.time()
     st = c.solve_relaxation()
     t2 = time.time()

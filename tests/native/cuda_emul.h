@@ -6,6 +6,7 @@
 // The product library (librelp_b200.so) is never built with RELP_EMUL and has no CPU path.
 #pragma once
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <cstdint>
 
@@ -25,6 +26,8 @@ static inline int2 make_int2(int x, int y) { int2 r; r.x = x; r.y = y; return r;
 
 template <typename T> static inline T atomicAdd(T* p, T v) { T o = *p; *p += v; return o; }
 static inline int atomicOr(int* p, int v) { int o = *p; *p |= v; return o; }
+static inline unsigned atomicOr(unsigned* p, unsigned v) { unsigned o = *p; *p |= v; return o; }
+static inline unsigned atomicAnd(unsigned* p, unsigned v) { unsigned o = *p; *p &= v; return o; }
 static inline int atomicMin(int* p, int v) { int o = *p; if (v < o) *p = v; return o; }
 template <typename T> static inline T __shfl_down_sync(unsigned, T v, int) { return v; }
 static inline void __syncthreads() {}
@@ -44,6 +47,7 @@ static inline cudaError_t cudaMalloc(void** p, size_t n) { *p = calloc(1, n); re
 static inline cudaError_t cudaFree(void* p) { free(p); return 0; }
 static inline cudaError_t cudaMallocHost(void** p, size_t n) { *p = calloc(1, n); return *p ? 0 : 2; }
 static inline cudaError_t cudaFreeHost(void* p) { free(p); return 0; }
+static inline cudaError_t cudaMemset(void* d, int v, size_t n) { memset(d, v, n); return 0; }
 static inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, cudaMemcpyKind) { memmove(d, s, n); return 0; }
 static inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, cudaMemcpyKind, cudaStream_t) { memmove(d, s, n); return 0; }
 static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t* s, int) { *s = (void*)1; return 0; }
