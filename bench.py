@@ -1,0 +1,260 @@
+#!/usr/bin/env python
+"""Headline benchmark: exact simplex pivots/sec and time-to-optimal on the synthetic sparse LP of
+BASELINE.json (config 5a: m = 20 000 rows, n = 200 000 structural columns, 20 nonzeros per column,
+totally unimodular, `A x <= b`), solved exactly (rational arithmetic) from the artificial tableau
+to the optimum.
+
+A "step" is one complete exact solve of that LP through the C ABI (include/relp_b200.h):
+relp_solve_relaxation = Carry initialisation + phase 1 + hand-over + phase 2 on the GPU.
+
+  value   pivots/sec, device time (CUDA events on the library's stream), LP already resident in HBM
+  e2e     the same metric through the public API with HOST buffers: relp_load_matrix (pinned host
+          -> device), solve, read-back of objective + basic solution, wall clock around the calls
+  roofline  the persistent loop kernel k_simplex_loop; algorithmic bytes per SURVEY.md 8(d)
+  cpu_baseline  the oracle (CPU restatement of the reference path, 1 core) on a bounded sample
+
+`--impl reference` times the oracle alone (the reference's Rust toolchain does not exist here).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "exact_simplex_pivots_per_sec"
+UNIT = "pivots/s"
+W_BYTES = 16            # bytes per rational in the int64/int64 tier
+
+
+def workload(args):
+    from rust_lp_b200.synth import synthetic_lp
+    return synthetic_lp(args.m, args.n, args.nnz_col, args.variant)
+
+
+def config(args, n_gpus):
+    return {"workload": f"synthetic sparse LP 5a ({args.variant}): m={args.m} n={args.n} nnz/col={args.nnz_col} "
+                        f"(+{args.m} slack columns), exact solve to optimality, FirstProfitableWithMemory/SteepestDescent",
+            "m": args.m, "n": args.n, "nnz_per_col": args.nnz_col, "seed": 20260101,
+            "parallelism": "1 GPU" if n_gpus == 1 else f"rows/columns sharded over {n_gpus} GPUs",
+            "l2": "every step re-initialises the Carry planes (2 x 8 x (m+1) x m bytes = "
+                  f"{2 * 8 * (args.m + 1) * args.m / 1e9:.1f} GB written), which flushes the 126 MB L2 between timed steps"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": int(self.rows[0][1]) if self.rows and self.rows[0][1].isdigit() else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def pin(pa):
+    """Back every input array with pinned host memory (the e2e copy source)."""
+    import torch
+    for name in ("col_ptr", "row_idx", "val_num", "val_den", "cost_num", "cost_den", "rhs_num", "rhs_den",
+                 "piv_rows", "piv_cols"):
+        a = getattr(pa, name)
+        t = torch.from_numpy(a).pin_memory()
+        setattr(pa, name, t.numpy())
+        pa.__dict__.setdefault("_pinned", []).append(t)
+    return pa
+
+
+def algorithmic_bytes(pa, stats):
+    """SURVEY.md 8(d) figures, summed over the pivots of one solve (w = 16 bytes per rational):
+    K3 (w+4) nnz(A) + w n + 4 n ; K2 w (m nnz_j + nnz_j + m) ; K4 2 w m + 4 m ; K1 w (2 T S + S + T)."""
+    w, m, n, nnz = W_BYTES, pa.m, pa.n, pa.nnz
+    pivots = stats.pivots
+    k3 = (w + 4) * nnz + w * n + 4 * n
+    nnz_j = nnz / n
+    k2 = w * (m * nnz_j + nnz_j + m)
+    k4 = 2 * w * m + 4 * m
+    k1 = w * (2 * stats.sum_TS + stats.sum_S + stats.sum_T)
+    # one extra pricing pass per loop detects termination
+    return (k3 + k2 + k4) * pivots + 2 * k3 + k1, {"K3_price": k3, "K2_column": k2, "K4_ratio": k4,
+                                                   "K1_update_mean": k1 / max(pivots, 1)}
+
+
+def cpu_sample(pa, pivots):
+    """Oracle (single thread) on the first `pivots` pivots of the same LP."""
+    from oracle import coracle
+    o = coracle.COracle(pa)
+    o.begin(1, 2)
+    t0 = time.perf_counter()
+    o.advance(pivots)
+    dt = time.perf_counter() - t0
+    done = o.nr_pivots
+    return done / dt if dt > 0 else 0.0, done, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    pa = workload(args)
+    sample = args.cpu_pivots
+    for _ in range(args.warmup):
+        cpu_sample(pa, max(2, sample // 8))
+    tot_p, tot_t = 0, 0.0
+    for _ in range(args.steps):
+        _, done, dt = cpu_sample(pa, sample)
+        tot_p += done; tot_t += dt
+    v = tot_p / tot_t
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "exact rational (arbitrary-precision integers)", "data": "synthetic",
+            "config": config(args, args.gpus),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+                             "sample": f"first {sample} pivots of the same LP per step (oracle/simplex.cpp, single thread: "
+                                       "the reference is single-threaded Rust and cannot be built here)"},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_single(args):
+    import torch
+    from rust_lp_b200 import capi
+    import __graft_entry__ as entry
+    entry.build_library()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (the product has no CPU path); use --impl reference for the CPU arm")
+    torch.cuda.set_device(0)
+    pa = pin(workload(args))
+    c = capi.Carry(pa, heap_words=1 << 24)
+    stream = torch.cuda.ExternalStream(c.stream())
+
+    def solve():
+        st = c.solve_relaxation()
+        assert st == capi.OPTIMAL, st
+        return c.stats()
+
+    for _ in range(max(args.warmup, 3)):
+        s = solve()
+    # ---- value: LP resident in HBM, device time -------------------------------------------------
+    clocks = ClockSampler()
+    clocks.start()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = s.kernel_launches
+    e0.record(stream)
+    pivots, loop_ms, stage_ns = 0, 0.0, [0] * 8
+    for _ in range(args.steps):
+        s = solve()
+        pivots += s.pivots; loop_ms += s.loop_ms
+        stage_ns = [a + b for a, b in zip(stage_ns, s.stage_ns)]
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    launches = s.kernel_launches - launches0
+    clk = clocks.stop()
+    objective = c.get_objective_function_value()
+    # ---- e2e: host buffers in, result out, wall clock ----------------------------------------------
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    d2h = 0
+    for _ in range(args.steps):
+        c.load_matrix(pa)
+        st = c.solve_relaxation()
+        obj = c.get_objective_function_value()
+        bfs = c.current_bfs()
+        d2h += 16 + 16 * pa.m + 4 * pa.m
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    assert obj == objective
+    h2d = 8 * (pa.n + 1) + 20 * pa.nnz + 16 * pa.n + 16 * pa.m
+    # ---- roofline of the dominant kernel (the persistent loop) -------------------------------------
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = peaks.get("hbm_gbs", 6650.0)
+    abytes, per_kernel = algorithmic_bytes(pa, s)
+    loop_ms_step = loop_ms / args.steps
+    achieved = abytes / (loop_ms_step * 1e-3) / 1e9
+    traffic = None
+    tfile = os.path.join(ROOT, "profiles", "traffic_r01.json")
+    if os.path.exists(tfile):
+        traffic = json.load(open(tfile)).get("dram_bytes_per_launch")
+    # ---- CPU baseline (oracle, 1 core, bounded sample) ----------------------------------------------
+    cpu_v, cpu_done, cpu_dt = cpu_sample(pa, args.cpu_pivots)
+    line = {"metric": METRIC, "value": pivots / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "exact rational, int64/int64 tier (multi-limb escalation armed, 0 elements escalated)"
+            if s.escalated == 0 else "exact rational, int64/int64 + multi-limb", "data": "synthetic",
+            "config": config(args, 1),
+            "time_to_optimal_ms": ms / args.steps, "pivots_per_solve": int(s.pivots), "objective": str(objective),
+            "e2e": {"value": pivots / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h // args.steps,
+                    "ms_per_step": 1e3 * e2e_s / args.steps},
+            "gpu_launches": int(launches),
+            "clocks": clk,
+            "roofline": {"bound": "hbm", "kernel": "k_simplex_loop (persistent cooperative loop: price + column + ratio + update)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650",
+                         "traffic": traffic, "algorithmic_bytes_per_launch": abytes,
+                         "algorithmic_bytes_per_pivot": per_kernel, "kernel_ms_per_launch": loop_ms_step,
+                         "stage_us_per_pivot": {k: v / 1e3 / max(pivots, 1) for k, v in
+                                                zip(("price", "column_ratio", "pivot_row", "update", "housekeeping"), stage_ns)}},
+            "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": 1, "kind": "port",
+                             "sample": f"first {cpu_done} pivots of the same LP, {cpu_dt:.1f} s (oracle/simplex.cpp, single "
+                                       "thread like the reference)"}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--m", type=int, default=20000)
+    ap.add_argument("--n", type=int, default=200000)
+    ap.add_argument("--nnz-col", type=int, default=20)
+    ap.add_argument("--variant", default="tu")
+    ap.add_argument("--cpu-pivots", type=int, default=150, help="oracle sample: pivots per CPU step")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    if args.gpus > 1 or int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        from rust_lp_b200 import multi
+        return multi.bench(args, METRIC, UNIT, config, ClockSampler, workload)
+    run_single(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -63,15 +63,16 @@ static int load_nccl(const char* path) {
 enum { NCCL_INT8 = 0, NCCL_INT64 = 4, NCCL_SUM = 0 };
 
 template <typename T> struct DBuf {
-    T* p = nullptr; size_t n = 0;
-    int alloc(size_t count) {
-        release();
+    T* p = nullptr; size_t n = 0, cap = 0;
+    int alloc(size_t count) {      // grow-only: solves of the same shape reuse their buffers
         if (count == 0) count = 1;
+        if (p && cap >= count) { n = count; return 0; }
+        release();
         cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
         if (e != cudaSuccess) { set_error(std::string("cudaMalloc: ") + cudaGetErrorString(e)); p = nullptr; return RELP_ERR_CUDA; }
-        n = count; return 0;
+        n = count; cap = count; return 0;
     }
-    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; cap = 0; }
     ~DBuf() { release(); }
 };
 
@@ -100,7 +101,7 @@ struct relp_ctx {
     // resumable solve
     int stage = 0, rule1 = 1, rule2 = 2, final_status = RELP_OK;
     bool stop_at_handover = false;
-    uint64_t launches = 0;
+    uint64_t launches = 0, h2d_bytes = 0;
     double loop_ms = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int max_limbs = 0;
@@ -138,36 +139,45 @@ static int err_status(const DState* s) {
 }
 
 // SELL-32 copy of A for pricing: slice s = columns 32s .. 32s+31, width = longest column of the
-// slice, entry t of lane l at sell_ptr[s] + 32 t + l; padding has row -1.
-static int build_sell(relp_ctx* c) {
+// slice, entry t of lane l at sell_ptr[s] + 32 t + l; padding has row -1.  The slice offsets come
+// from col_ptr on the host (O(n)); the entries are scattered on the device from the CSC copy.
+__global__ void k_fill_sell(int n, const long long* col_ptr, const int* row_idx, const int64_t* an, const int64_t* ad,
+                            const long long* sell_ptr, int* srow, int64_t* san, int64_t* sad, int* a_int) {
+    int not_int = 0;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < ((n + 31) & ~31); j += gridDim.x * blockDim.x) {
+        int s = j >> 5, l = j & 31;
+        long long base = sell_ptr[s];
+        int width = (int)((sell_ptr[s + 1] - base) >> 5);
+        long long t0 = 0; int len = 0;
+        if (j < n) { t0 = col_ptr[j]; len = (int)(col_ptr[j + 1] - t0); }
+        for (int t = 0; t < width; t++) {
+            size_t e = (size_t)base + (size_t)t * 32 + l;
+            if (t < len) { srow[e] = row_idx[t0 + t]; san[e] = an[t0 + t]; int64_t d = ad[t0 + t]; sad[e] = d; if (d != 1) not_int = 1; }
+            else { srow[e] = -1; san[e] = 0; sad[e] = 1; }
+        }
+    }
+    if (not_int) *a_int = 0;
+}
+
+static int build_sell(relp_ctx* c, const long long* col_ptr) {
     int n = c->n;
     int ns = (n + 31) / 32;
     std::vector<long long> sp(ns + 1, 0);
     for (int s = 0; s < ns; s++) {
         long long w = 0;
-        for (int j = s * 32; j < std::min(n, s * 32 + 32); j++) w = std::max(w, c->col_ptr[j + 1] - c->col_ptr[j]);
+        for (int j = s * 32; j < std::min(n, s * 32 + 32); j++) w = std::max(w, col_ptr[j + 1] - col_ptr[j]);
         sp[s + 1] = sp[s] + 32 * w;
     }
     size_t total = (size_t)sp[ns];
-    std::vector<int> sr(std::max<size_t>(total, 1), -1);
-    std::vector<int64_t> sa(std::max<size_t>(total, 1), 0), sd(std::max<size_t>(total, 1), 1);
-    int a_int = 1;
-    for (int j = 0; j < n; j++) {
-        int s = j >> 5, l = j & 31;
-        long long t0 = c->col_ptr[j], len = c->col_ptr[j + 1] - t0;
-        for (long long t = 0; t < len; t++) {
-            size_t e = (size_t)(sp[s] + 32 * t + l);
-            sr[e] = c->row_idx[t0 + t]; sa[e] = c->an[t0 + t]; sd[e] = c->ad[t0 + t];
-            if (sd[e] != 1) a_int = 0;
-        }
-    }
-    c->n_slices = ns; c->a_int = a_int;
-    if (c->sell_ptr.alloc(ns + 1) || c->sell_row.alloc(total) || c->sell_an.alloc(total) || c->sell_ad.alloc(total)) return RELP_ERR_CUDA;
+    c->n_slices = ns;
+    if (c->sell_ptr.alloc(ns + 1) || c->sell_row.alloc(total) || c->sell_an.alloc(total) || c->sell_ad.alloc(total) || c->scratch_i.alloc(4)) return RELP_ERR_CUDA;
     cudaStream_t st = c->stream;
+    int one = 1;
     CUDA_TRY(cudaMemcpyAsync(c->sell_ptr.p, sp.data(), (ns + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(c->sell_row.p, sr.data(), sr.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(c->sell_an.p, sa.data(), sa.size() * 8, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(c->sell_ad.p, sd.data(), sd.size() * 8, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(c->scratch_i.p, &one, sizeof(int), cudaMemcpyHostToDevice, st));
+    LAUNCH(c, k_fill_sell, clampi((n + 255) / 256, 1, c->sm_count * 8), 256, n, c->col_ptr_d.p, c->row_idx_d.p, c->an_d.p, c->ad_d.p,
+           c->sell_ptr.p, c->sell_row.p, c->sell_an.p, c->sell_ad.p, c->scratch_i.p);
+    CUDA_TRY(cudaMemcpyAsync(&c->a_int, c->scratch_i.p, sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     return 0;
 }
@@ -242,8 +252,7 @@ int relp_load_matrix(relp_ctx* c, int32_t m, int32_t n, const int64_t* col_ptr, 
     long long nnz = col_ptr[n];
     c->m = m; c->n = n;
     c->col_ptr.assign(col_ptr, col_ptr + n + 1);
-    c->row_idx.assign(row_idx, row_idx + nnz);
-    c->an.assign(val_num, val_num + nnz); c->ad.assign(val_den, val_den + nnz);
+    c->row_idx.clear(); c->an.clear(); c->ad.clear();     // fetched back from the device only if rows get removed
     c->cn.assign(cost_num, cost_num + n); c->cd.assign(cost_den, cost_den + n);
     c->rhsn.assign(rhs_num, rhs_num + m); c->rhsd.assign(rhs_den, rhs_den + m);
     if (c->col_ptr_d.alloc(n + 1) || c->row_idx_d.alloc(nnz) || c->an_d.alloc(nnz) || c->ad_d.alloc(nnz) ||
@@ -258,8 +267,9 @@ int relp_load_matrix(relp_ctx* c, int32_t m, int32_t n, const int64_t* col_ptr, 
     CUDA_TRY(cudaMemcpyAsync(c->rhsn_d.p, rhs_num, m * 8, cudaMemcpyHostToDevice, s));
     CUDA_TRY(cudaMemcpyAsync(c->rhsd_d.p, rhs_den, m * 8, cudaMemcpyHostToDevice, s));
     CUDA_TRY(cudaStreamSynchronize(s));
-    int rc = build_sell(c);
+    int rc = build_sell(c, c->col_ptr.data());
     if (rc) return rc;
+    c->h2d_bytes = (uint64_t)(n + 1) * 8 + (uint64_t)nnz * 20 + (uint64_t)n * 16 + (uint64_t)m * 16;
     c->loaded = true; c->carry_ready = false; c->stage = 0;
     return RELP_OK;
 }
@@ -596,6 +606,14 @@ static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* r
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     std::swap(c->xn.p, nxn.p); std::swap(c->xn.n, nxn.n); std::swap(c->xd.p, nxd.p); std::swap(c->xd.n, nxd.n);
     // provider without the removed rows (filter/generic_wrapper.rs:224-300)
+    if (c->row_idx.empty() && c->col_ptr[n] > 0) {
+        size_t nnz = (size_t)c->col_ptr[n];
+        c->row_idx.resize(nnz); c->an.resize(nnz); c->ad.resize(nnz);
+        CUDA_TRY(cudaMemcpyAsync(c->row_idx.data(), c->row_idx_d.p, nnz * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaMemcpyAsync(c->an.data(), c->an_d.p, nnz * 8, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaMemcpyAsync(c->ad.data(), c->ad_d.p, nnz * 8, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+    }
     std::vector<long long> cp(n + 1, 0); std::vector<int> ri; std::vector<int64_t> an, ad;
     for (int j = 0; j < n; j++) {
         for (long long t = c->col_ptr[j]; t < c->col_ptr[j + 1]; t++) {
@@ -615,7 +633,7 @@ static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* r
         CUDA_TRY(cudaMemcpyAsync(c->ad_d.p, ad.data(), ad.size() * 8, cudaMemcpyHostToDevice, c->stream));
     }
     CUDA_TRY(cudaStreamSynchronize(c->stream));
-    int rc = build_sell(c);
+    int rc = build_sell(c, c->col_ptr.data());
     if (rc) return rc;
     c->m = m2; shard_rows(c, m2); c->ld = ld2;
     basis = b2;
