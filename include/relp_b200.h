@@ -95,6 +95,12 @@ int relp_debug_trace(relp_ctx*, uint64_t* out /* n_ctas x 16 */, int32_t n_ctas)
  * candidate all-gathers.  `nccl_lib` is the dlopen path of libnccl (NULL = "libnccl.so.2"). */
 int relp_comm_unique_id(void* id128, const char* nccl_lib);
 int relp_attach_comm(relp_ctx*, const void* id128, const char* nccl_lib);
+/* Alternative transport: host-staged callbacks (e.g. torch.distributed over gloo).  `send`/`recv`/`buf`
+ * are HOST buffers; all-gather concatenates `bytes` from every rank in rank order; all-reduce sums
+ * int64 in place.  Return 0 on success.  Used by the world_size-2 CPU tests. */
+typedef int (*relp_allgather_fn)(void* user, const void* send, void* recv, size_t bytes);
+typedef int (*relp_allreduce_fn)(void* user, int64_t* buf, size_t count);
+int relp_attach_comm_callbacks(relp_ctx*, relp_allgather_fn, relp_allreduce_fn, void* user);
 
 /* ---- input: MatrixProvider (matrix_provider/mod.rs:37-136) ---------------------------------- */
 /* CSC of ALL provider columns, virtual slack columns materialised (matrix_data.rs:308-348),

@@ -22,7 +22,7 @@ FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
 # every symbol include/relp_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_comm_unique_id",
-    "relp_attach_comm", "relp_load_matrix", "relp_carry_create_partially_artificial",
+    "relp_attach_comm", "relp_attach_comm_callbacks", "relp_load_matrix", "relp_carry_create_partially_artificial",
     "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_price",
     "relp_generate_column", "relp_ratio_test", "relp_change_basis", "relp_generate_element",
     "relp_iterate", "relp_solve_relaxation", "relp_solve_continue", "relp_solve_to_handover",
@@ -51,6 +51,9 @@ class Stats(C.Structure):
                 ("loop_ms", C.c_double), ("stage_ns", C.c_uint64 * 8)]
 
 
+ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_int64), C.c_size_t)
+
 _libs = {}
 
 
@@ -74,6 +77,7 @@ def load_library(path=None):
     L.relp_debug_trace.argtypes = [vp, vp, i32]
     L.relp_comm_unique_id.argtypes = [vp, C.c_char_p]
     L.relp_attach_comm.argtypes = [vp, vp, C.c_char_p]
+    L.relp_attach_comm_callbacks.argtypes = [vp, ALLGATHER_FN, ALLREDUCE_FN, vp]
     L.relp_load_matrix.argtypes = [vp, i32, i32] + [vp] * 8
     L.relp_carry_create_partially_artificial.argtypes = [vp, i32, vp, vp]
     L.relp_carry_from_artificial.argtypes = [vp]
@@ -145,6 +149,20 @@ class Carry:
 
     def stream(self):
         return self.L.relp_stream(self.h)
+
+    # ---- multi-GPU plumbing -------------------------------------------------------------------
+    def comm_unique_id(self, nccl_lib=None):
+        buf = (C.c_char * 128)()
+        self._chk(self.L.relp_comm_unique_id(buf, nccl_lib.encode() if nccl_lib else None))
+        return bytes(buf)
+
+    def attach_comm(self, unique_id, nccl_lib=None):
+        buf = (C.c_char * 128).from_buffer_copy(unique_id)
+        self._chk(self.L.relp_attach_comm(self.h, buf, nccl_lib.encode() if nccl_lib else None))
+
+    def attach_comm_callbacks(self, allgather, allreduce):
+        self._cb = (ALLGATHER_FN(allgather), ALLREDUCE_FN(allreduce))     # keep alive
+        self._chk(self.L.relp_attach_comm_callbacks(self.h, self._cb[0], self._cb[1], None))
 
     def debug_trace(self, n_ctas=148):
         out = np.zeros((n_ctas, 16), np.uint64)

@@ -80,6 +80,8 @@ struct relp_ctx {
     int device = 0, rank = 0, world = 1;
     cudaStream_t stream = nullptr;
     ncclComm_t comm = nullptr;
+    relp_allgather_fn cb_allgather = nullptr; relp_allreduce_fn cb_allreduce = nullptr; void* cb_user = nullptr;
+    std::vector<char> stage_a, stage_b;   // host staging for the callback transport
     uint64_t heap_words = 0;
     // host copy of the provider (needed for row removal and set-up)
     int m = 0, n = 0;
@@ -244,6 +246,12 @@ int relp_attach_comm(relp_ctx* c, const void* id128, const char* nccl_lib) {
     return RELP_OK;
 }
 
+int relp_attach_comm_callbacks(relp_ctx* c, relp_allgather_fn ag, relp_allreduce_fn ar, void* user) {
+    if (!c || !ag || !ar) return RELP_ERR_ARGUMENT;
+    c->cb_allgather = ag; c->cb_allreduce = ar; c->cb_user = user;
+    return RELP_OK;
+}
+
 int relp_load_matrix(relp_ctx* c, int32_t m, int32_t n, const int64_t* col_ptr, const int32_t* row_idx,
                      const int64_t* val_num, const int64_t* val_den, const int64_t* cost_num, const int64_t* cost_den,
                      const int64_t* rhs_num, const int64_t* rhs_den) {
@@ -320,7 +328,7 @@ static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
     if (c->cost_rows.alloc(c->mloc + 1) || c->scratch_i.alloc(2 * (size_t)(m + 2))) return RELP_ERR_CUDA;
     // worklist: worst case every element of the local block is escalated
     if (c->worklist.alloc((size_t)(m + 1) * std::max(c->mloc, 1))) return RELP_ERR_CUDA;
-    if (c->cand.alloc(MAX_PARTIAL_BLOCKS) || c->cand2.alloc(MAX_PARTIAL_BLOCKS) || c->gather.alloc(std::max(c->world, 1))) return RELP_ERR_CUDA;
+    if (c->cand.alloc(MAX_PARTIAL_BLOCKS) || c->cand2.alloc(MAX_PARTIAL_BLOCKS) || c->gather.alloc(c->world + 1)) return RELP_ERR_CUDA;
     if (!c->log.p && c->log.alloc(1 << 20)) return RELP_ERR_CUDA;
     return 0;
 }
@@ -363,12 +371,42 @@ static int nccl_check(int rc, const char* what) {
     return RELP_ERR_COMM;
 }
 
+// Collectives: NCCL on the context's stream (stream ordered, no host round trip), or -- when the
+// caller attached callbacks (torch.distributed over gloo in the CPU tests) -- staged through the host.
+static int comm_allgather(relp_ctx* c, const void* send, void* recv, size_t bytes) {
+    if (c->cb_allgather) {
+        c->stage_a.resize(bytes); c->stage_b.resize(bytes * c->world);
+        CUDA_TRY(cudaMemcpyAsync(c->stage_a.data(), send, bytes, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        if (c->cb_allgather(c->cb_user, c->stage_a.data(), c->stage_b.data(), bytes)) { set_error("all-gather callback failed"); return RELP_ERR_COMM; }
+        CUDA_TRY(cudaMemcpyAsync(recv, c->stage_b.data(), bytes * c->world, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    if (!c->comm) { set_error("multi-GPU context without a communicator: call relp_attach_comm"); return RELP_ERR_COMM; }
+    return nccl_check(g_nccl.AllGather(send, recv, bytes, NCCL_INT8, c->comm, c->stream), "ncclAllGather");
+}
+static int comm_allreduce_i64(relp_ctx* c, int64_t* buf, size_t count) {
+    if (c->cb_allreduce) {
+        c->stage_a.resize(count * 8);
+        CUDA_TRY(cudaMemcpyAsync(c->stage_a.data(), buf, count * 8, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        if (c->cb_allreduce(c->cb_user, (int64_t*)c->stage_a.data(), count)) { set_error("all-reduce callback failed"); return RELP_ERR_COMM; }
+        CUDA_TRY(cudaMemcpyAsync(buf, c->stage_a.data(), count * 8, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    if (!c->comm) { set_error("multi-GPU context without a communicator: call relp_attach_comm"); return RELP_ERR_COMM; }
+    return nccl_check(g_nccl.AllReduce(buf, buf, count, NCCL_INT64, NCCL_SUM, c->comm, c->stream), "ncclAllReduce");
+}
+
 // select: reduce this rank's block candidates; multi-GPU: all-gather the per-rank winners and
 // reduce again, identically on every rank ("gather-then-reduce-identically")
 static int enqueue_select(relp_ctx* c, int mode, int nblocks, int rule) {
     if (c->world == 1) { LAUNCH(c, k_select, 1, RELP_THREADS, c->D, mode, nblocks, 0, -1, rule); return 0; }
-    LAUNCH(c, k_select, 1, RELP_THREADS, c->D, mode, nblocks, 0, c->rank, rule);
-    if (nccl_check(g_nccl.AllGather(c->gather.p + c->rank, c->gather.p, sizeof(Cand), NCCL_INT8, c->comm, c->stream), "ncclAllGather")) return RELP_ERR_COMM;
+    LAUNCH(c, k_select, 1, RELP_THREADS, c->D, mode, nblocks, 0, c->world, rule);
+    // not in place: every rank posts its winner to `mine` and gathers all of them
+    if (comm_allgather(c, c->gather.p + c->world, c->gather.p, sizeof(Cand))) return RELP_ERR_COMM;
     LAUNCH(c, k_select, 1, RELP_THREADS, c->D, mode, c->world, 1, -1, rule);
     return 0;
 }
@@ -392,7 +430,7 @@ static int enqueue_column_and_ratio(relp_ctx* c, bool select_row) {
 static int enqueue_change_basis(relp_ctx* c) {
     LAUNCH(c, k_pivot_row, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D, c->world > 1 ? 1 : 0);
     if (c->world > 1) {
-        if (nccl_check(g_nccl.AllReduce(c->pnd.p, c->pnd.p, 2 * (size_t)(c->m + 1), NCCL_INT64, NCCL_SUM, c->comm, c->stream), "ncclAllReduce")) return RELP_ERR_COMM;
+        if (comm_allreduce_i64(c, c->pnd.p, 2 * (size_t)(c->m + 1))) return RELP_ERR_COMM;
         LAUNCH(c, k_build_slist, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D);
     }
     LAUNCH(c, k_update, c->sm_count * 8, RELP_THREADS, c->D);
@@ -557,7 +595,7 @@ static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbe
         DBuf<int64_t> all;
         if (all.alloc((size_t)c->world * 2 * cnt)) return RELP_ERR_CUDA;
         LAUNCH(c, k_recompute_cost_row, grid_for(c, cnt, 2), RELP_THREADS, c->D, c->cost_rows.p, (int)cost_rows.size(), c->D.pn, c->D.pd);
-        if (nccl_check(g_nccl.AllGather(c->pnd.p, all.p, 2 * (size_t)cnt * 8, NCCL_INT8, c->comm, c->stream), "ncclAllGather")) return RELP_ERR_COMM;
+        if (comm_allgather(c, c->pnd.p, all.p, 2 * (size_t)cnt * 8)) return RELP_ERR_COMM;
         LAUNCH(c, k_sum_partials, grid_for(c, cnt, 2), RELP_THREADS, c->D, all.p, c->world, cnt, c->zn.p, c->zd.p);
         CUDA_TRY(cudaStreamSynchronize(c->stream));
     }

@@ -1,0 +1,173 @@
+"""One process per GPU: row-sharded Carry, column-sharded pricing.
+
+torch.distributed is the plumbing only (rendezvous, exchanging the NCCL unique id, gathering the
+per-rank pieces of the answer); the per-pivot collectives are issued by librelp_b200.so itself on
+its own stream (NCCL), or -- in the CPU tests -- through host callbacks over a gloo group.
+"""
+import ctypes as C
+import glob
+import json
+import os
+import time
+
+import numpy as np
+
+from . import capi
+
+
+def find_nccl():
+    """The libnccl torch itself loaded (so that there is one NCCL in the process)."""
+    try:
+        import torch
+        base = os.path.dirname(os.path.dirname(torch.__file__))
+        for pat in ("nvidia/nccl/lib/libnccl.so*", "torch/lib/libnccl.so*"):
+            hits = sorted(glob.glob(os.path.join(base, pat)))
+            if hits:
+                return hits[0]
+    except Exception:
+        pass
+    return None
+
+
+def gloo_callbacks(group=None):
+    """Host-staged all-gather / all-reduce over torch.distributed (any backend with CPU tensors)."""
+    import torch
+    import torch.distributed as dist
+
+    def allgather(_user, send, recv, nbytes):
+        world = dist.get_world_size(group)
+        src = torch.from_numpy(np.ctypeslib.as_array(C.cast(send, C.POINTER(C.c_uint8)), shape=(nbytes,)).copy())
+        outs = [torch.empty(nbytes, dtype=torch.uint8) for _ in range(world)]
+        dist.all_gather(outs, src, group=group)
+        dst = np.ctypeslib.as_array(C.cast(recv, C.POINTER(C.c_uint8)), shape=(nbytes * world,))
+        dst[:] = torch.cat(outs).numpy()
+        return 0
+
+    def allreduce(_user, buf, count):
+        arr = np.ctypeslib.as_array(buf, shape=(count,))
+        t = torch.from_numpy(arr.copy())
+        dist.all_reduce(t, group=group)
+        arr[:] = t.numpy()
+        return 0
+
+    return allgather, allreduce
+
+
+class ShardedCarry:
+    """The same interface as capi.Carry for the calls a sharded solve needs; every rank calls every
+    method (they are collective)."""
+
+    def __init__(self, provider, device=None, heap_words=0, lib_path=None, transport="nccl"):
+        import torch.distributed as dist
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        dev = device if device is not None else int(os.environ.get("LOCAL_RANK", self.rank))
+        self.c = capi.Carry(provider, device=dev, rank=self.rank, world=self.world, heap_words=heap_words,
+                            lib_path=lib_path)
+        self.c.set_option("persistent", 0)
+        if self.world > 1:
+            if transport == "nccl":
+                lib = find_nccl()
+                box = [self.c.comm_unique_id(lib) if self.rank == 0 else None]
+                dist.broadcast_object_list(box, src=0)
+                self.c.attach_comm(box[0], lib)
+            else:
+                self.c.attach_comm_callbacks(*gloo_callbacks())
+
+    def solve_relaxation(self, *a, **k):
+        return self.c.solve_relaxation(*a, **k)
+
+    def log(self):
+        return self.c.log()
+
+    def stats(self):
+        return self.c.stats()
+
+    def get_objective_function_value(self):
+        return self.c.get_objective_function_value()
+
+    def current_bfs(self):
+        """all ranks get the full basic solution"""
+        import torch.distributed as dist
+        parts = [None] * self.world
+        dist.all_gather_object(parts, self.c.current_bfs())
+        out = [x for p in parts for x in p]
+        out.sort(key=lambda x: x[0])
+        return out
+
+    def b(self):
+        import torch.distributed as dist
+        parts = [None] * self.world
+        dist.all_gather_object(parts, self.c.b())
+        return [x for p in parts for x in p]
+
+    def close(self):
+        self.c.close()
+
+
+def bench(args, metric, unit, config, ClockSampler, workload):
+    """`bench.py --gpus N` under torchrun: ONE LP solved cooperatively by N GPUs (strong scaling)."""
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pa = workload(args)
+    sc = ShardedCarry(pa, device=local, heap_words=1 << 24)
+    stream = torch.cuda.ExternalStream(sc.c.stream())
+
+    def solve():
+        st = sc.solve_relaxation()
+        assert st == capi.OPTIMAL, st
+        return sc.stats()
+
+    for _ in range(max(args.warmup, 3)):
+        s = solve()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    dist.barrier(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = s.kernel_launches
+    e0.record(stream)
+    pivots = 0
+    for _ in range(args.steps):
+        s = solve()
+        pivots += s.pivots
+    e1.record(stream)
+    torch.cuda.synchronize(); dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    launches = s.kernel_launches - launches0
+    obj = sc.get_objective_function_value()
+    # e2e: host buffers in, answer out, wall clock, max over ranks
+    dist.barrier(); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        sc.c.load_matrix(pa)
+        sc.solve_relaxation()
+        sc.get_objective_function_value()
+        sc.current_bfs()
+    torch.cuda.synchronize(); dist.barrier()
+    e2e = torch.tensor([time.perf_counter() - t0], device="cuda")
+    dist.all_reduce(e2e, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e.item())
+    if rank == 0:
+        clk = clocks.stop()
+        h2d = 8 * (pa.n + 1) + 20 * pa.nnz + 16 * pa.n + 16 * pa.m
+        line = {"metric": metric, "value": pivots / (ms * 1e-3), "unit": unit, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None,
+                "dtype": "exact rational, int64/int64 tier (multi-limb escalation armed)", "data": "synthetic",
+                "config": config(args, world), "time_to_optimal_ms": ms / args.steps,
+                "pivots_per_solve": int(s.pivots), "objective": str(obj),
+                "e2e": {"value": pivots / e2e_s, "unit": unit, "h2d_bytes_per_step": h2d * world,
+                        "d2h_bytes_per_step": 16 + 20 * pa.m, "ms_per_step": 1e3 * e2e_s / args.steps},
+                "gpu_launches": int(launches), "clocks": clk,
+                "note": "one LP solved cooperatively: Carry rows and pricing columns sharded, 2 all-gathers + 1 all-reduce "
+                        "per pivot (NCCL); this LP is latency-bound (DESIGN.md section 4), so more GPUs add collective "
+                        "latency without removing much work"}
+        print(json.dumps(line), flush=True)
+    sc.close()
+    dist.destroy_process_group()
