@@ -1,0 +1,51 @@
+"""Sharded solve on real GPUs (one process per GPU, NCCL issued by the library): identical pivot
+sequence and answer as the oracle.  Skipped with fewer than 2 GPUs."""
+import os
+import subprocess
+import sys
+import textwrap
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = textwrap.dedent('''
+    import os, sys
+    sys.path.insert(0, %r); sys.path.insert(0, os.path.join(%r, "tests"))
+    import torch, torch.distributed as dist
+    from rust_lp_b200 import capi, multi
+    from rust_lp_b200.synth import synthetic_lp
+    from oracle import coracle
+    import parity
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    for (m, n, k) in [(60, 400, 6), (203, 2000, 20), (2000, 20000, 20)]:
+        pa = synthetic_lp(m, n, k, "tu")
+        o = coracle.COracle(pa); st_o = o.solve(1, 2)
+        sc = multi.ShardedCarry(pa, device=local, heap_words=1 << 22)
+        st = sc.solve_relaxation()
+        assert st == parity.STATUS[st_o], (st, st_o)
+        assert [x[:4] for x in sc.log()] == [x[:4] for x in parity.oracle_log(o)]
+        assert sc.get_objective_function_value() == o.objective()
+        assert sc.current_bfs() == o.current_bfs()
+        sc.close(); del o
+    print("rank", dist.get_rank(), "ok", flush=True)
+    dist.barrier(); dist.destroy_process_group(); os._exit(0)
+''') % (ROOT, ROOT)
+
+
+def test_sharded_solve_nccl(tmp_path):
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    n = 2 if n < 4 else 4
+    w = tmp_path / "worker.py"
+    w.write_text(WORKER)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29621", str(w)],
+                       capture_output=True, text=True, timeout=900, env=dict(os.environ, MASTER_ADDR="127.0.0.1"))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("ok") >= n
