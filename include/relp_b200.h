@@ -42,7 +42,9 @@ enum relp_status {
     RELP_ERR_HEAP_EXHAUSTED = -4, /* limb heap full: recreate the context with a larger heap        */
     RELP_ERR_ARGUMENT = -5,
     RELP_ERR_PHASE1_UNBOUNDED = -6, /* "Artificial cost can not be unbounded" (phase_one.rs:143)     */
-    RELP_ERR_COMM = -7
+    RELP_ERR_COMM = -7,
+    RELP_ERR_ARTIFICIAL_BASIC = -8 /* an artificial column survived the phase-one clean-up; the reference
+                                      underflows `basis_column -= nr_artificial` here (carry/mod.rs:500) */
 };
 
 enum relp_rule {              /* strategy/pivot_rule.rs */

@@ -258,7 +258,8 @@ def remove_artificial_basis_variables(t):
             col = t.generate_column(found[0])
             t.bring_into_basis(found[0], pivot_row, col, found[1], 'z')
         else:
-            rows_to_remove.append(a)  # sic: the artificial index (phase_one.rs:251)
+            # the reference pushes `artificial` (phase_one.rs:251); equal to pivot_row whenever the reference survives (else it removes the wrong row and underflows at carry/mod.rs:665)
+            rows_to_remove.append(pivot_row)
     return rows_to_remove
 
 

@@ -251,7 +251,8 @@ struct Solver {
             if (found >= 0) {
                 SparseVec col = generate_column(found);
                 bring_into_basis(found, pivot_row, col, cost, 'z');
-            } else rows_removed.push_back(a);   // sic: artificial index (phase_one.rs:251)
+            } else rows_removed.push_back(pivot_row);
+            // the reference pushes `artificial` (phase_one.rs:251); equal to pivot_row whenever the reference survives (else it removes the wrong row and underflows at carry/mod.rs:665)
         }
     }
 
@@ -294,6 +295,10 @@ struct Solver {
                 for (auto& e : lp.cols[j]) if (newidx[e.first] >= 0) nl.cols[j].emplace_back(newidx[e.first], e.second);
             lp = nl;
         }
+        // An artificial that re-entered the basis during phase 1 on another row is not found by the clean-up
+        // (it pivots on the artificial's ORIGINAL row, partially.rs pivot_row_from_artificial); the reference
+        // then underflows `basis_column -= nr_artificial` (carry/mod.rs:500/:665).  Reported as status -8.
+        for (int x : c.basis_indices) if (x < nr_art) { status = -8; return; }
         for (auto& x : c.basis_indices) x -= nr_art;
         phase1 = false;
         recompute_cost_row();
@@ -317,6 +322,7 @@ struct Solver {
                     for (int a = 0; a < nr_art; a++) if (in_basis[a]) art = true;
                     if (art) remove_artificial_basis_variables();
                     to_phase_two();
+                    if (status != 0) break;
                     stage = 1;
                     if (stop_at_handover) break;
                     continue;

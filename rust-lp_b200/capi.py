@@ -15,8 +15,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librelp_b200.so")
 
 OK, OPTIMAL, UNBOUNDED, INFEASIBLE = 0, 1, 2, 3
-ERR_CUDA, ERR_ZERO_PIVOT, ERR_LIMB_CAPACITY, ERR_HEAP_EXHAUSTED, ERR_ARGUMENT, ERR_PHASE1_UNBOUNDED, ERR_COMM = \
-    -1, -2, -3, -4, -5, -6, -7
+ERR_CUDA, ERR_ZERO_PIVOT, ERR_LIMB_CAPACITY, ERR_HEAP_EXHAUSTED, ERR_ARGUMENT, ERR_PHASE1_UNBOUNDED, ERR_COMM, \
+    ERR_ARTIFICIAL_BASIC = -1, -2, -3, -4, -5, -6, -7, -8
 FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
 
 # every symbol include/relp_b200.h declares (tests check the library exports all of them)

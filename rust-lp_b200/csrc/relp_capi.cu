@@ -572,6 +572,9 @@ __global__ void k_sum_partials(Dev D, const int64_t* allp, int world, int count,
 static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbering of phase 1, size m */) {
     int m = c->m, n = c->n;
     for (auto& b : basis) b -= c->nr_art;
+    // The reference underflows here (carry/mod.rs:500, :665) when an artificial column that re-entered the
+    // basis on another row survived the clean-up (which pivots on the artificial's ORIGINAL row).
+    for (int b : basis) if (b < 0) { set_error("an artificial column is still basic after phase one"); return RELP_ERR_ARTIFICIAL_BASIC; }
     std::vector<unsigned char> inb(n, 0);
     for (int b : basis) if (b >= 0 && b < n) inb[b] = 1;
     std::vector<int> cost_rows;
@@ -631,6 +634,7 @@ static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* r
     std::vector<int> newidx(m, -1), keep;
     { size_t q = 0; for (int i = 0; i < m; i++) { if (q < (size_t)n_rows && rows[q] == i) { q++; continue; } newidx[i] = (int)keep.size(); keep.push_back(i); } }
     int m2 = (int)keep.size();
+    for (int i : keep) if (basis[i] < c->nr_art) { set_error("an artificial column is still basic after phase one"); return RELP_ERR_ARTIFICIAL_BASIC; }
     // planes: kept rows; columns 0 and 1 + kept
     std::vector<int> keep_col(m2 + 1);
     keep_col[0] = 0; for (int k = 0; k < m2; k++) keep_col[1 + k] = 1 + keep[k];
@@ -697,7 +701,8 @@ static int remove_artificial_basis_variables(relp_ctx* c) {
         CUDA_TRY(cudaMemcpyAsync(&best, d_best, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
         CUDA_TRY(cudaStreamSynchronize(c->stream));
         if (c->world > 1) { set_error("artificial clean-up is single-GPU only"); return RELP_ERR_COMM; }
-        if (best == INT_MAX) { c->rows_removed.push_back(a); continue; }   // sic: the artificial's index (phase_one.rs:251)
+        // the reference pushes `artificial` (phase_one.rs:251); equal to pivot_row whenever the reference survives (else it removes the wrong row and underflows at carry/mod.rs:665)
+        if (best == INT_MAX) { c->rows_removed.push_back(pivot_row); continue; }
         LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'z', 1, 1);
         enqueue_begin(c);
         LAUNCH(c, k_set_pivot, 1, 1, c->st.p, best, pivot_row, 1);

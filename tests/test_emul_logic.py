@@ -101,3 +101,31 @@ def test_heap_exhaustion_is_an_error_not_garbage(lib):
     with pytest.raises(capi.RelpError) as e:
         c.solve_relaxation()
     assert e.value.status == capi.ERR_HEAP_EXHAUSTED
+
+
+def _mps_names():
+    from test_mps_golden import NAMES
+    return [n for n in NAMES if n != "netlib_SCORPION"]
+
+
+@pytest.mark.parametrize("name", _mps_names())
+def test_mps_fixtures(lib, name):
+    """Problems read by the MPS reader (tests/golden/mps): bound rows, range rows, free variables, and
+    redundant rows whose artificial index differs from its row (VTP-BASE, degenerate_redundant)."""
+    from test_mps_golden import load_fixture, BY_NAME
+    pa, _ = load_fixture(name)
+    s, o = parity.check_full_solve(pa, lib)
+    assert pa.m - o.m == BY_NAME[name]["rows_removed"]
+
+
+def test_artificial_left_in_basis_is_an_error(lib):
+    """netlib SCORPION without presolve: an artificial column re-enters the basis in phase one on another
+    row and survives the clean-up; the reference underflows there (carry/mod.rs:500).  Status -8 here."""
+    from test_mps_golden import load_fixture
+    from rust_lp_b200 import capi
+    pa, _ = load_fixture("netlib_SCORPION")
+    c = capi.Carry(pa, heap_words=1 << 22, lib_path=lib)
+    with pytest.raises(capi.RelpError) as ei:
+        c.solve_relaxation(1, 2)
+    assert ei.value.status == capi.ERR_ARTIFICIAL_BASIC
+    c.close()
