@@ -92,6 +92,8 @@ struct relp_ctx {
     DBuf<int64_t> xn, xd, zn, zd, an_d, ad_d, cn_d, cd_d, rhsn_d, rhsd_d, dn, dd, pnd, tmpn, tmpd, sell_an, sell_ad;
     DBuf<long long> col_ptr_d, sell_ptr; DBuf<uint32_t> zbits; DBuf<int> row_idx_d, sell_row, basis, art_row, tlist, slist, cost_rows, scratch_i;
     DBuf<unsigned char> in_basis;
+    DBuf<int64_t> rn, rd; DBuf<long long> row_ptr_d; DBuf<int> csr_col, row_art; DBuf<uint32_t> colbits, rowbits;   // reduced-cost row, nonzero pattern
+    size_t wl_cap = 0;
     DBuf<int2> worklist; DBuf<Cand> cand, cand2, gather; DBuf<LogEntry> log; DBuf<unsigned long long> trace;
     int n_slices = 0, a_int = 1, coop_blocks = 0, last_ratio_blocks = 1;
     bool use_persistent = true, smem_opt_in = false;
@@ -161,6 +163,38 @@ __global__ void k_fill_sell(int n, const long long* col_ptr, const int* row_idx,
     if (not_int) *a_int = 0;
 }
 
+// CSR pattern of A (column indices only; order within a row is irrelevant): the reduced-cost update
+// enumerates the columns that have an entry in a given row.
+__global__ void k_csr_count(int n, const long long* col_ptr, const int* row_idx, long long* row_ptr) {
+    long long nnz = col_ptr[n];
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < nnz; t += (long long)gridDim.x * blockDim.x)
+        atomicAdd((unsigned long long*)&row_ptr[row_idx[t] + 1], 1ull);
+}
+__global__ void k_csr_scan(int m, long long* row_ptr, long long* cursor) {      // m is small next to nnz: one thread
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    long long acc = 0;
+    for (int i = 0; i <= m; i++) { acc += row_ptr[i]; row_ptr[i] = acc; if (i < m) cursor[i] = acc; }
+}
+__global__ void k_csr_fill(int n, const long long* col_ptr, const int* row_idx, long long* cursor, int* csr_col) {
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
+        for (long long t = col_ptr[j]; t < col_ptr[j + 1]; t++) {
+            long long q = (long long)atomicAdd((unsigned long long*)&cursor[row_idx[t]], 1ull);
+            csr_col[q] = j;
+        }
+}
+
+static int build_csr(relp_ctx* c, long long nnz) {
+    int m = c->m, n = c->n;
+    DBuf<long long> cursor;
+    if (c->row_ptr_d.alloc(m + 1) || c->csr_col.alloc(nnz) || cursor.alloc(m + 1)) return RELP_ERR_CUDA;
+    CUDA_TRY(cudaMemsetAsync(c->row_ptr_d.p, 0, (size_t)(m + 1) * sizeof(long long), c->stream));
+    LAUNCH(c, k_csr_count, clampi((nnz + 255) / 256, 1, c->sm_count * 8), 256, n, c->col_ptr_d.p, c->row_idx_d.p, c->row_ptr_d.p);
+    LAUNCH(c, k_csr_scan, 1, 1, m, c->row_ptr_d.p, cursor.p);
+    LAUNCH(c, k_csr_fill, clampi((n + 255) / 256, 1, c->sm_count * 8), 256, n, c->col_ptr_d.p, c->row_idx_d.p, cursor.p, c->csr_col.p);
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
 static int build_sell(relp_ctx* c, const long long* col_ptr) {
     int n = c->n;
     int ns = (n + 31) / 32;
@@ -181,7 +215,7 @@ static int build_sell(relp_ctx* c, const long long* col_ptr) {
            c->sell_ptr.p, c->sell_row.p, c->sell_an.p, c->sell_ad.p, c->scratch_i.p);
     CUDA_TRY(cudaMemcpyAsync(&c->a_int, c->scratch_i.p, sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
-    return 0;
+    return build_csr(c, col_ptr[n]);
 }
 
 extern "C" {
@@ -311,6 +345,8 @@ static void wire_dev(relp_ctx* c) {
     D.art_row = c->art_row.p; D.dn = c->dn.p; D.dd = c->dd.p;
     D.pn = c->pnd.p; D.pd = c->pnd.p + (c->m + 1);
     D.tlist = c->tlist.p; D.slist = c->slist.p; D.worklist = c->worklist.p; D.cand = c->cand.p; D.cand2 = c->cand2.p;
+    D.rn = c->rn.p; D.rd = c->rd.p; D.row_ptr = c->row_ptr_d.p; D.csr_col = c->csr_col.p;
+    D.colbits = c->colbits.p; D.rowbits = c->rowbits.p; D.row_art = c->row_art.p;
     D.gather = c->gather.p; D.log = c->log.p; D.log_cap = (long long)c->log.n; D.trace = c->trace.p; D.zbits = c->zbits.p;
 }
 
@@ -318,7 +354,7 @@ static const int MAX_PARTIAL_BLOCKS = 2048;
 
 static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
     shard_rows(c, m);
-    c->ld = std::max(16, (c->mloc + 15) / 16 * 16);
+    c->ld = std::max(32, (c->mloc + 31) / 32 * 32);      // a warp's 32 rows share one word of colbits
     size_t plane = (size_t)(m + 1) * c->ld;
     if (c->xn.alloc(plane) || c->xd.alloc(plane) || c->zn.alloc(m + 1) || c->zd.alloc(m + 1)) return RELP_ERR_CUDA;
     if (c->in_basis.alloc(ncols_max) || c->zbits.alloc((m + 31) / 32 + 1)) return RELP_ERR_CUDA;
@@ -326,8 +362,12 @@ static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
     if (c->pnd.alloc(2 * (size_t)(m + 1))) return RELP_ERR_CUDA;
     if (c->basis.alloc(m) || c->art_row.alloc(m) || c->tlist.alloc(c->mloc + 1) || c->slist.alloc(m + 1)) return RELP_ERR_CUDA;
     if (c->cost_rows.alloc(c->mloc + 1) || c->scratch_i.alloc(2 * (size_t)(m + 2))) return RELP_ERR_CUDA;
-    // worklist: worst case every element of the local block is escalated
-    if (c->worklist.alloc((size_t)(m + 1) * std::max(c->mloc, 1))) return RELP_ERR_CUDA;
+    if (c->rn.alloc(ncols_max) || c->rd.alloc(ncols_max) || c->row_art.alloc(m) ||
+        c->colbits.alloc((size_t)(m + 1) * (c->ld / 32) + 2) || c->rowbits.alloc((size_t)c->ld * ((m + 32) / 32) + 4)) return RELP_ERR_CUDA;
+    // worklist: worst case every element of the local block is escalated; capped at 128 MB (a larger
+    // block of multi-limb entries reports RELP_ERR_HEAP_EXHAUSTED instead of reserving gigabytes up front)
+    c->wl_cap = std::min<size_t>((size_t)(m + 1) * std::max(c->mloc, 1), (size_t)1 << 24);
+    if (c->worklist.alloc(c->wl_cap)) return RELP_ERR_CUDA;
     if (c->cand.alloc(MAX_PARTIAL_BLOCKS) || c->cand2.alloc(MAX_PARTIAL_BLOCKS) || c->gather.alloc(c->world + 1)) return RELP_ERR_CUDA;
     if (!c->log.p && c->log.alloc(1 << 20)) return RELP_ERR_CUDA;
     return 0;
@@ -361,7 +401,7 @@ __global__ void k_reset_transient(DState* st) { st->tr_top = st->tr_base; }
 
 // shared-memory words for the -pi bitmap (0: too large, kernels test the global bitmap)
 static int zbits_smem_words(relp_ctx* c) {
-    int w = (c->m + 31) / 32;
+    int w = (c->m + 32) / 32 + 1;          // covers the -pi bitmap (m bits) and the pivot-row bitmap (m + 1 bits)
     return (size_t)w * 4 <= 160 * 1024 ? w : 0;
 }
 
@@ -539,11 +579,18 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld; s->n = n; s->nr_art = nr_art;
     s->phase = 1; s->ncols = nr_art + n; shard_cols(c, s); s->a_int = c->a_int;
     s->status = ST_RUNNING; s->last_selected = -1; s->iter = 0; s->iter_limit = ~0ull; s->tag = '1'; s->go = 1;
-    s->rc = make_small(0, 1);
+    s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap;
     init_heap_regions(c, s);
     if (push_state(c)) return RELP_ERR_CUDA;
+    {   // row -> artificial column
+        std::vector<int> ra(m, -1);
+        for (int a = 0; a < nr_art; a++) ra[c->art_rows_h[a]] = a;
+        CUDA_TRY(cudaMemcpyAsync(c->row_art.p, ra.data(), m * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+    }
     wire_dev(c);
     LAUNCH(c, k_init_planes, c->sm_count * 8, RELP_THREADS, c->D, c->rhsn_d.p, c->rhsd_d.p);
+    LAUNCH(c, k_build_pattern, c->sm_count * 8, RELP_THREADS, c->D);
     LAUNCH(c, k_init_cost_row_artificial, 1, 1, c->D, c->rhsn_d.p, c->rhsd_d.p);
     LAUNCH(c, k_build_zbits, grid_for(c, (m + 31) / 32), RELP_THREADS, c->D);
     if (check_cuda(c)) return RELP_ERR_CUDA;
@@ -569,7 +616,7 @@ __global__ void k_sum_partials(Dev D, const int64_t* allp, int world, int count,
 }
 
 // K5 + index shift; `m` may already have shrunk (row removal).
-static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbering of phase 1, size m */) {
+static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbering of phase 1, size m */, bool planes_replaced = false) {
     int m = c->m, n = c->n;
     for (auto& b : basis) b -= c->nr_art;
     // The reference underflows here (carry/mod.rs:500, :665) when an artificial column that re-entered the
@@ -586,10 +633,11 @@ static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbe
     DState* s = c->h_st;
     s->phase = 2; s->ncols = n; shard_cols(c, s); s->last_selected = -1; s->status = ST_RUNNING;
     s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld;
-    s->tr_top = s->tr_base; s->T = 0; s->S = 0; s->wl_count = 0;
+    s->tr_top = s->tr_base; s->T = 0; s->S = 0; s->wl_count = 0; s->W = 0; s->rc_valid = 0;
     if (push_state(c)) return RELP_ERR_CUDA;
     c->phase = 2;
     wire_dev(c);
+    if (planes_replaced) LAUNCH(c, k_build_pattern, c->sm_count * 8, RELP_THREADS, c->D);
     if (c->world == 1) {
         LAUNCH(c, k_recompute_cost_row, grid_for(c, m + 1, 2), RELP_THREADS, c->D, c->cost_rows.p, (int)cost_rows.size(), c->zn.p, c->zd.p);
     } else {
@@ -638,7 +686,7 @@ static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* r
     // planes: kept rows; columns 0 and 1 + kept
     std::vector<int> keep_col(m2 + 1);
     keep_col[0] = 0; for (int k = 0; k < m2; k++) keep_col[1 + k] = 1 + keep[k];
-    int ld2 = std::max(16, (m2 + 15) / 16 * 16);
+    int ld2 = std::max(32, (m2 + 31) / 32 * 32);
     DBuf<int64_t> nxn, nxd;
     if (nxn.alloc((size_t)(m2 + 1) * ld2) || nxd.alloc((size_t)(m2 + 1) * ld2)) return RELP_ERR_CUDA;
     int* kr = c->scratch_i.p; int* kc = c->scratch_i.p + (m + 2);
@@ -675,11 +723,11 @@ static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* r
         CUDA_TRY(cudaMemcpyAsync(c->ad_d.p, ad.data(), ad.size() * 8, cudaMemcpyHostToDevice, c->stream));
     }
     CUDA_TRY(cudaStreamSynchronize(c->stream));
+    c->m = m2; shard_rows(c, m2); c->ld = ld2;
     int rc = build_sell(c, c->col_ptr.data());
     if (rc) return rc;
-    c->m = m2; shard_rows(c, m2); c->ld = ld2;
     basis = b2;
-    return handover_common(c, basis);
+    return handover_common(c, basis, true);
 }
 
 // phase_one.rs:223-260

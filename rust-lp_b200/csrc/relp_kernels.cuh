@@ -57,6 +57,9 @@ struct DState {
     int compacting;
     int a_int;                     // every A value has denominator 1
     int go;                        // persistent loop: continue? (written by one thread between barriers)
+    int rc_valid;                  // the stored reduced-cost row (Dev::rn, rd) is current
+    int W;                         // sum of the CSR row lengths over the pivot row's nonzero columns
+    int wl_cap;                    // capacity of the escalation worklist
     unsigned long long iter, iter_limit;
     unsigned long long pool_top, pool_limit, pool_base;   // active persistent region of the limb heap
     unsigned long long alt_base, alt_limit;               // the other persistent region (compaction target)
@@ -90,6 +93,15 @@ struct Dev {
     Cand* gather;                             // world candidates (multi-GPU all-gather buffer)
     LogEntry* log; long long log_cap;
     uint32_t* zbits;                          // bit i set <=> -pi_i != 0 (maintained with the cost row)
+    // Reduced-cost row, kept by the persistent loop (see stage_update_rc): one rational per tableau column
+    int64_t* rn; int64_t* rd;
+    const long long* row_ptr; const int* csr_col;   // CSR pattern of A: which columns does a row touch
+    // Nonzero pattern of the Carry block, kept with it (stage_update): colbits word (k, li / 32) has bit
+    // li % 32 set <=> X[li][k] != 0 (column generation tests 32 rows of a B^-1 column with one word);
+    // rowbits word (li, k / 32) is the transpose (the pivot row's nonzero columns come from one
+    // contiguous read, and that row of rowbits IS the bitmap "p_k != 0" of the reduced-cost update).
+    uint32_t* colbits; uint32_t* rowbits;
+    const int* row_art;                       // row -> its artificial column, or -1
     unsigned long long* trace;                // debug: per-CTA arrival time at each barrier (16 slots per CTA)
 };
 
@@ -106,9 +118,15 @@ struct Dev {
 #define RELP_MAXWARPS 32
 
 struct Grid { int tid, nth, bid, nb; };
+#if !defined(RELP_EMUL) && defined(RELP_WTRACE)
+__device__ __forceinline__ unsigned long long gtime0() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define WTRACE(k) do { if (D.trace) atomicMax(&D.trace[(size_t)g.bid * 16 + (k)], gtime0()); } while (0)
+#else
+#define WTRACE(k) do {} while (0)
+#endif
 // loop invariants of DState, read once per kernel (every barrier invalidates L1, so re-reading
 // them from global memory in every stage costs an L2 round trip each time)
-struct Inv { int m, mloc, row_lo, ld, n, nr_art, phase, ncols, sl_lo, sl_hi, art_lo, art_hi, a_int; };
+struct Inv { int m, mloc, row_lo, ld, n, nr_art, phase, ncols, sl_lo, sl_hi, art_lo, art_hi, a_int, wpc, wpr; };
 __device__ __forceinline__ Grid this_grid_dims() {
     Grid g; g.tid = blockIdx.x * blockDim.x + threadIdx.x; g.nth = gridDim.x * blockDim.x;
     g.bid = blockIdx.x; g.nb = gridDim.x; return g;
@@ -117,7 +135,9 @@ __device__ __forceinline__ Grid this_grid_dims() {
 __device__ __forceinline__ Inv load_inv(const DState* st) {
     Inv I; I.m = st->m; I.mloc = st->mloc; I.row_lo = st->row_lo; I.ld = st->ld; I.n = st->n; I.nr_art = st->nr_art;
     I.phase = st->phase; I.ncols = st->ncols; I.sl_lo = st->sl_lo; I.sl_hi = st->sl_hi; I.art_lo = st->art_lo;
-    I.art_hi = st->art_hi; I.a_int = st->a_int; return I;
+    I.art_hi = st->art_hi; I.a_int = st->a_int;
+    I.wpc = st->ld >> 5; I.wpr = (st->m + 32) >> 5;   // words per column of colbits / per row of rowbits
+    return I;
 }
 __device__ __forceinline__ Arena transient(const Dev& D) {
     Arena a; a.top = &D.st->tr_top; a.limit = D.st->tr_limit; a.err = &D.st->err; return a;
@@ -211,6 +231,14 @@ __device__ Cand reduce_candidates(const Cand* src, int count, int mode, const ui
     return block_argmin(best, mode, heap);
 }
 
+// element (li, k) of the Carry block changed between zero and nonzero
+__device__ __forceinline__ void pattern_set(const Dev& D, const Inv& I, int li, int k, bool nonzero) {
+    uint32_t* c = D.colbits + (size_t)k * I.wpc + (li >> 5);
+    uint32_t* r = D.rowbits + (size_t)li * I.wpr + (k >> 5);
+    if (nonzero) { atomicOr(c, 1u << (li & 31)); atomicOr(r, 1u << (k & 31)); }
+    else { atomicAnd(c, ~(1u << (li & 31))); atomicAnd(r, ~(1u << (k & 31))); }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Stage A -- K3 pricing: rc_j = c_j + sum_i (-pi_i) A_ij for every non-basic tableau column of
 // this rank, fused with the argmin (no reduced-cost vector is ever stored).
@@ -247,34 +275,19 @@ __device__ __forceinline__ void price_consider(const Dev& D, Val rc, int j, int 
 extern __shared__ uint32_t relp_dyn_smem[];
 #endif
 
-// `smem_words` > 0: the CTA first copies the "-pi_i != 0" bitmap into shared memory, so that the
-// per-entry test is a shared-memory lookup (a 32-lane gather from global memory costs 32 L1
-// wavefronts; measured, that was the whole pricing time).  -pi itself is read only where the bit
-// is set.  smem_words == 0 (bitmap too large, or the CPU stand-in): test the global bitmap.
-__device__ void stage_price(const Dev& D, const Grid& g, const Inv& I, int mode, int smem_words) {
-    const DState* st = D.st;
-    Arena ar = transient(D);
-    const int phase = I.phase, nr_art = I.nr_art, ncols = I.ncols, n = I.n;
-    const int start = (mode == ARG_FIRST && st->last_selected >= 0) ? st->last_selected : 0;
-    const int off = phase == 1 ? nr_art : 0;
-    const int64_t* zn = D.zn + 1; const int64_t* zd = D.zd + 1;   // mutable between stages: no __restrict__
-    const uint32_t* zb = D.zbits;
-#ifndef RELP_EMUL
-    if (smem_words > 0) {
-        for (int w = threadIdx.x; w < smem_words; w += blockDim.x) relp_dyn_smem[w] = D.zbits[w];
-        __syncthreads();
-        zb = relp_dyn_smem;
-    }
-#endif
-    Cand best = cand_none();
-    if (phase == 1) {
-        Val one = make_small(1, 1);
-        for (int a = I.art_lo + g.tid; a < I.art_hi; a += g.nth) {
-            if (D.in_basis[a]) continue;
-            Val rc = val_fma(ld_val(zn, zd, D.art_row[a]), one, one, 1, D.heap, ar);
-            price_consider(D, rc, a, mode, start, ncols, best);
-        }
-    }
+// One pass over this rank's SELL slices, one lane per column jj.  `init(jj, acc)` says whether the
+// column takes part and seeds the sum; the sum then collects v[row + voff] * a over the entries
+// whose bit (row + voff) is set in `bits`; `done(jj, acc)` receives it.
+// Pass 1 (streaming): every entry's row is tested against the bitmap and the hits of a lane are
+// remembered as a bit mask; the row indices of the next chunk are requested before this chunk is
+// consumed.  Pass 2: the lanes walk their own hits in lockstep, two at a time, so a warp pays
+// (max hits per lane)/2 dependent round trips instead of one per hit position.  (A 32-lane
+// gather from global memory costs 32 L1 wavefronts; measured, testing -pi itself instead of a
+// shared-memory bitmap was the whole pricing time.)
+template <class Init, class Done>
+__device__ __forceinline__ void sell_scan(const Dev& D, const Grid& g, const Inv& I, const uint32_t* bits, int voff,
+                                          const int64_t* vn, const int64_t* vd, const Arena& ar, Init init, Done done) {
+    const int n = I.n;
 #ifdef RELP_EMUL
     const int gw = 0, nw = 1;        // sequential stand-in: one thread plays every lane in turn
     for (int lane = 0; lane < 32; lane++)
@@ -287,13 +300,9 @@ __device__ void stage_price(const Dev& D, const Grid& g, const Inv& I, int mode,
         int jj = s * 32 + lane;
         long long base = D.sell_ptr[s];
         int width = (int)((D.sell_ptr[s + 1] - base) >> 5);
-        bool live = jj < n && !D.in_basis[off + jj];
-        Val acc = (phase == 2 && live) ? make_small(D.cn[jj], D.cd[jj]) : val_zero();
+        Val acc = val_zero();
+        bool live = jj < n && init(jj, acc);
         const int* __restrict__ rows = D.sell_row + base + lane;
-        // Pass 1 (streaming): test every entry's row against the bitmap and remember the hits of
-        // this lane as a bit mask; the row indices of the next chunk are requested before this
-        // chunk is consumed.  Pass 2: the lanes walk their own hits in lockstep, two at a time, so
-        // a warp pays (max hits per lane)/2 dependent round trips instead of one per hit position.
         for (int seg = 0; seg < width; seg += 64) {
             const int wseg = width - seg < 64 ? width - seg : 64;
             unsigned long long hits = 0;
@@ -305,8 +314,8 @@ __device__ void stage_price(const Dev& D, const Grid& g, const Inv& I, int mode,
                 for (int u = 0; u < RELP_CHP; u++) nx[u] = (live && t + RELP_CHP + u < wseg) ? rows[(size_t)(seg + t + RELP_CHP + u) * 32] : -1;
 #pragma unroll
                 for (int u = 0; u < RELP_CHP; u++) {
-                    int row = rr[u];
-                    if (row >= 0 && ((zb[row >> 5] >> (row & 31)) & 1u)) hits |= 1ull << (t + u);
+                    int row = rr[u] + voff;
+                    if (rr[u] >= 0 && ((bits[row >> 5] >> (row & 31)) & 1u)) hits |= 1ull << (t + u);
                 }
 #pragma unroll
                 for (int u = 0; u < RELP_CHP; u++) rr[u] = nx[u];
@@ -316,18 +325,172 @@ __device__ void stage_price(const Dev& D, const Grid& g, const Inv& I, int mode,
                 int tb = hits ? ctz64(hits) : -1; if (tb >= 0) hits &= hits - 1;
                 size_t ea = (size_t)base + (size_t)(seg + ta) * 32 + lane;
                 size_t eb = tb >= 0 ? (size_t)base + (size_t)(seg + tb) * 32 + lane : ea;
-                int ra = D.sell_row[ea], rb = D.sell_row[eb];
-                Val za = ld_val(zn, zd, ra), zb2 = ld_val(zn, zd, rb);
+                int ra = D.sell_row[ea] + voff, rb = D.sell_row[eb] + voff;
+                Val za = ld_val(vn, vd, ra), zb2 = ld_val(vn, vd, rb);
                 Val aa = make_small(D.sell_an[ea], a_int ? 1 : D.sell_ad[ea]);
                 Val ab = make_small(D.sell_an[eb], a_int ? 1 : D.sell_ad[eb]);
                 acc = val_fma(acc, za, aa, 1, D.heap, ar);
                 if (tb >= 0) acc = val_fma(acc, zb2, ab, 1, D.heap, ar);
             }
         }
-        if (live) price_consider(D, acc, off + jj, mode, start, ncols, best);
+        if (jj < n) done(jj, live, acc);
+    }
+}
+
+// copy a bitmap into the CTA's dynamic shared memory (smem_words == 0: too large, or the CPU
+// stand-in -- the kernels then test the global bitmap)
+__device__ __forceinline__ const uint32_t* stage_bits(const uint32_t* global_bits, int smem_words) {
+#ifndef RELP_EMUL
+    if (smem_words > 0) {
+        __syncthreads();
+        for (int w = threadIdx.x; w < smem_words; w += blockDim.x) relp_dyn_smem[w] = global_bits[w];
+        __syncthreads();
+        return relp_dyn_smem;
+    }
+#endif
+    return global_bits;
+}
+
+// Full pricing pass.  `fill`: also store every reduced cost (0 for basic columns) in the
+// reduced-cost row, from where the persistent loop keeps it current (stage_update_rc).
+__device__ void stage_price(const Dev& D, const Grid& g, const Inv& I, int mode, int smem_words, int fill) {
+    const DState* st = D.st;
+    Arena ar = fill ? persistent(D) : transient(D);
+    const int phase = I.phase, nr_art = I.nr_art, ncols = I.ncols;
+    const int start = (mode == ARG_FIRST && st->last_selected >= 0) ? st->last_selected : 0;
+    const int off = phase == 1 ? nr_art : 0;
+    const int64_t* zn = D.zn + 1; const int64_t* zd = D.zd + 1;   // mutable between stages: no __restrict__
+    const uint32_t* zb = stage_bits(D.zbits, smem_words);
+    Cand best = cand_none();
+    if (phase == 1) {
+        Val one = make_small(1, 1);
+        for (int a = I.art_lo + g.tid; a < I.art_hi; a += g.nth) {
+            bool basic = D.in_basis[a];
+            Val rc = basic ? val_zero() : val_fma(ld_val(zn, zd, D.art_row[a]), one, one, 1, D.heap, ar);
+            if (fill) st_val(D.rn, D.rd, a, rc);
+            if (!basic) price_consider(D, rc, a, mode, start, ncols, best);
+        }
+    }
+    sell_scan(D, g, I, zb, 0, zn, zd, ar,
+              [&](int jj, Val& acc) {
+                  if (D.in_basis[off + jj]) return false;
+                  if (phase == 2) acc = make_small(D.cn[jj], D.cd[jj]);
+                  return true;
+              },
+              [&](int jj, bool live, const Val& acc) {
+                  if (fill) st_val(D.rn, D.rd, off + jj, live ? acc : val_zero());
+                  if (live) price_consider(D, acc, off + jj, mode, start, ncols, best);
+              });
+    best = block_argmin(best, mode, D.heap);
+    if (threadIdx.x == 0) D.cand[g.bid] = best;
+}
+
+// Stage A of the persistent loop: the entering column from the stored reduced-cost row.  Basic
+// columns hold exactly 0 there, so "rc_j < 0" alone is the reference's filter (pivot_rule.rs:38-127).
+__device__ void stage_select_rc(const Dev& D, const Grid& g, const Inv& I, int mode) {
+    const DState* st = D.st;
+    const int start = (mode == ARG_FIRST && st->last_selected >= 0) ? st->last_selected : 0;
+    Cand best = cand_none();
+    for (int j = g.tid; j < I.ncols; j += g.nth) {
+        Val rc = ld_val(D.rn, D.rd, j);
+        if (rc.n == 0) continue;
+        price_consider(D, rc, j, mode, start, I.ncols, best);
     }
     best = block_argmin(best, mode, D.heap);
     if (threadIdx.x == 0) D.cand[g.bid] = best;
+}
+
+// Reduced-cost row after a pivot.  -pi' = -pi - rc_e p (carry/mod.rs:326-333) gives, for EVERY
+// column, rc_j' = rc_j - rc_e (p . A_j) with p the normalised pivot row of B^-1: exact arithmetic
+// makes this the same reduced rational the reference recomputes from scratch (tableau/mod.rs:
+// 102-108), basic columns included (p . A_j is 0 for them, 1 for the entering column, so it drops
+// to exactly 0).  Only columns with an entry in a row where p != 0 change.  Sparse pivot row: those
+// columns are enumerated from the CSR pattern of A; otherwise one
+// SELL pass with the pivot row's bitmap.  Runs in the same barrier interval as the Carry update,
+// from the other end of the grid.
+// one column k = slist[s] of the pivot row, i.e. row k - 1 of A: one thread of the CTA per entry
+__device__ __forceinline__ void rc_sparse_row(const Dev& D, const Inv& I, int s, const Val& rc, int off, const uint32_t* pbits, const Arena& ar) {
+    const int k = D.slist[s];
+    if (k == 0) return;
+    if (threadIdx.x == 0 && I.phase == 1) {      // artificial column e_i (cost one): p . e_i = p_k
+        int a = D.row_art[k - 1];
+        if (a >= 0) st_val(D.rn, D.rd, a, val_fma(ld_val(D.rn, D.rd, a), rc, ld_val(D.pn, D.pd, k), -1, D.heap, ar));
+    }
+    const long long lo = D.row_ptr[k - 1], hi = D.row_ptr[k];
+    for (long long e = lo + threadIdx.x; e < hi; e += blockDim.x) {
+        const int jj = D.csr_col[e];
+        Val old = ld_val(D.rn, D.rd, off + jj);            // requested early, used last
+        const long long t0 = D.col_ptr[jj], t1 = D.col_ptr[jj + 1];
+        Val alpha = val_zero();
+        int first = 0x7fffffff;
+        for (long long seg = t0; seg < t1; seg += 32) {
+            const int wseg = t1 - seg < 32 ? (int)(t1 - seg) : 32;
+            unsigned hits = 0;
+            for (int t = 0; t < wseg; t += RELP_CHG) {
+                int kk[RELP_CHG]; uint32_t ww[RELP_CHG];
+#pragma unroll
+                for (int u = 0; u < RELP_CHG; u++) kk[u] = t + u < wseg ? D.row_idx[seg + t + u] + 1 : -1;
+#pragma unroll
+                for (int u = 0; u < RELP_CHG; u++) ww[u] = kk[u] >= 0 ? pbits[kk[u] >> 5] : 0u;
+#pragma unroll
+                for (int u = 0; u < RELP_CHG; u++) if (kk[u] >= 0 && ((ww[u] >> (kk[u] & 31)) & 1u)) {
+                    hits |= 1u << (t + u);
+                    if (kk[u] < first) first = kk[u];
+                }
+            }
+            while (hits) {
+                int t = ctz32(hits); hits &= hits - 1;
+                int kk = D.row_idx[seg + t] + 1;
+                alpha = val_fma(alpha, ld_val(D.pn, D.pd, kk), make_small(D.an[seg + t], D.ad[seg + t]), 1, D.heap, ar);
+            }
+        }
+        if (first == k && alpha.n != 0)
+            st_val(D.rn, D.rd, off + jj, val_fma(old, rc, alpha, -1, D.heap, ar));
+    }
+}
+
+#ifndef RELP_RC_SPARSE_S
+#define RELP_RC_SPARSE_S 32
+#endif
+__device__ void stage_update_rc(const Dev& D, const Grid& g, const Inv& I, int r, Val rc, int smem_words) {
+    const DState* st = D.st;
+    if (rc.n == 0) return;
+    const int S = st->S, W = st->W;
+    const int off = I.phase == 1 ? I.nr_art : 0;
+    Arena ar = persistent(D);
+    const uint32_t* pbits = D.rowbits + (size_t)(r - I.row_lo) * I.wpr;     // p_k != 0 <=> X[r][k] != 0
+    long long nnz = D.col_ptr[I.n];
+    if (S <= RELP_RC_SPARSE_S && (long long)W * 32 <= nnz + 1024
+#ifndef RELP_EMUL
+        && S <= g.nb
+#endif
+        ) {
+        // CTA (counted from the far end of the grid) s takes column k = slist[s] of the pivot row,
+        // i.e. row k - 1 of A, one thread per entry of that row.  A column with entries in several
+        // such rows is updated by the thread that came from its smallest one: no atomics, and every
+        // load chain is slist -> row_ptr -> csr_col -> col_ptr -> row_idx -> pbits -> p.
+#ifdef RELP_EMUL
+        for (int s = 0; s < S; s++) rc_sparse_row(D, I, s, rc, off, pbits, ar);
+#else
+        const int s = g.nb - 1 - g.bid;
+        if (s < S) rc_sparse_row(D, I, s, rc, off, pbits, ar);
+#endif
+        return;
+    }
+    if (I.phase == 1) {
+        for (int s = g.tid; s < S; s += g.nth) {
+            int k = D.slist[s];
+            int a = k > 0 ? D.row_art[k - 1] : -1;
+            if (a >= 0) st_val(D.rn, D.rd, a, val_fma(ld_val(D.rn, D.rd, a), rc, ld_val(D.pn, D.pd, k), -1, D.heap, ar));
+        }
+    }
+    const uint32_t* pb = stage_bits(pbits, smem_words);
+    sell_scan(D, g, I, pb, 1, D.pn, D.pd, ar,
+              [&](int, Val&) { return true; },
+              [&](int jj, bool, const Val& alpha) {
+                  if (alpha.n != 0)
+                      st_val(D.rn, D.rd, off + jj, val_fma(ld_val(D.rn, D.rd, off + jj), rc, alpha, -1, D.heap, ar));
+              });
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -343,45 +506,75 @@ __device__ void stage_gen_column(const Dev& D, const Grid& g, const Inv& I, int 
     const int mloc = I.mloc; const size_t ld = I.ld;
     const int64_t* xn = D.xn + ld;     // column 1 + k at xn + k * ld
     const int64_t* xd = D.xd + ld;
+    const uint32_t* cb = D.colbits + I.wpc;          // column 1 + k at cb + k * wpc
     Cand best = cand_none();
-    for (int li = g.tid; li < mloc; li += g.nth) {
-        // b_i and the row's basis column are requested up front: they are needed only by rows
-        // with d_i > 0, but issuing them now takes two round trips off that critical path
-        Val bv = ld_val(D.xn, D.xd, li);
-        int bkey = D.basis[I.row_lo + li];
+#ifdef RELP_EMUL
+    for (int li = 0; li < mloc; li++) {
         Val acc = val_zero();
-        if (unit_row >= 0) acc = copy_val(ld_val(xn, xd, (size_t)unit_row * ld + li), D.heap, ar);
-        else for (long long seg = t0; seg < t1; seg += 64) {
-            // Pass 1 (streaming, coalesced over rows): which entries of this row are nonzero?
-            // Pass 2: the rows of a warp walk their own hits in lockstep (operands come back from
-            // L1), so a warp pays max-hits-per-row round trips, not one per distinct hit column.
-            const int wseg = t1 - seg < 64 ? (int)(t1 - seg) : 64;
-            unsigned long long hits = 0;
-            for (int t = 0; t < wseg; t += RELP_CHG) {
-                int kk[RELP_CHG]; int64_t xx[RELP_CHG];
-#pragma unroll
-                for (int u = 0; u < RELP_CHG; u++) kk[u] = t + u < wseg ? D.row_idx[seg + t + u] : -1;
-#pragma unroll
-                for (int u = 0; u < RELP_CHG; u++) xx[u] = kk[u] >= 0 ? xn[(size_t)kk[u] * ld + li] : 0;
-#pragma unroll
-                for (int u = 0; u < RELP_CHG; u++) if (xx[u] != 0) hits |= 1ull << (t + u);
+        if (unit_row >= 0) {
+            if ((cb[(size_t)unit_row * I.wpc + (li >> 5)] >> (li & 31)) & 1u)
+                acc = copy_val(ld_val(xn, xd, (size_t)unit_row * ld + li), D.heap, ar);
+        } else for (long long t = t0; t < t1; t++) {
+            int kk = D.row_idx[t];
+            if ((cb[(size_t)kk * I.wpc + (li >> 5)] >> (li & 31)) & 1u)
+                acc = val_fma(acc, ld_val(xn, xd, (size_t)kk * ld + li), make_small(D.an[t], D.ad[t]), 1, D.heap, ar);
+        }
+#else
+    // A warp owns 32 consecutive rows.  Lane u fetches entry u of a_j and the ONE word of colbits that
+    // says which of the warp's 32 rows are nonzero in that column of B^-1; the words are passed round
+    // by shuffle, so a block of rows that the column does not touch costs col_ptr -> row_idx ->
+    // colbits and no read of B^-1 at all.  Entries that do hit are visited by the whole warp together
+    // (coalesced over the rows).
+    const int lane = threadIdx.x & 31, gw = (threadIdx.x >> 5) * g.nb + g.bid, nw = g.nth >> 5;
+    for (int rb = gw; rb * 32 < mloc; rb += nw) {
+        const int li = rb * 32 + lane;
+        Val acc = val_zero();
+        if (unit_row >= 0) {
+            uint32_t word = cb[(size_t)unit_row * I.wpc + rb];
+            if ((word >> lane) & 1u) acc = copy_val(ld_val(xn, xd, (size_t)unit_row * ld + li), D.heap, ar);
+        } else for (long long seg = t0; seg < t1; seg += 32) {
+            const int cnt = t1 - seg < 32 ? (int)(t1 - seg) : 32;
+            const int kk = lane < cnt ? D.row_idx[seg + lane] : -1;
+            const uint32_t word = kk >= 0 ? cb[(size_t)kk * I.wpc + rb] : 0u;
+            unsigned act = __ballot_sync(0xffffffffu, word != 0u);
+            if (act) WTRACE(11);
+            unsigned mine = 0;                      // entries of this segment that hit MY row
+            while (act) {
+                const int u = ctz32(act); act &= act - 1;
+                const uint32_t w = __shfl_sync(0xffffffffu, word, u);
+                if ((w >> lane) & 1u) mine |= 1u << u;
             }
-            while (hits) {
-                int t = ctz64(hits); hits &= hits - 1;
-                size_t e = (size_t)D.row_idx[seg + t] * ld + li;
-                acc = val_fma(acc, ld_val(xn, xd, e), make_small(D.an[seg + t], D.ad[seg + t]), 1, D.heap, ar);
+            // four hits at a time: all operands are requested before the first is used (one round trip
+            // to B^-1 per four hits of a row, however many entries of a_j touch this block of rows)
+            while (mine) {
+                int uu[4]; Val xx[4], aa[4];
+#pragma unroll
+                for (int q = 0; q < 4; q++) { uu[q] = mine ? ctz32(mine) : -1; if (mine) mine &= mine - 1; }
+#pragma unroll
+                for (int q = 0; q < 4; q++) if (uu[q] >= 0) {
+                    xx[q] = ld_val(xn, xd, (size_t)D.row_idx[seg + uu[q]] * ld + li);
+                    aa[q] = make_small(D.an[seg + uu[q]], D.ad[seg + uu[q]]);
+                }
+#pragma unroll
+                for (int q = 0; q < 4; q++) if (uu[q] >= 0) acc = val_fma(acc, xx[q], aa[q], 1, D.heap, ar);
             }
         }
+        if (li >= mloc) continue;
+        if (acc.n != 0) WTRACE(12);
+#endif
         st_val(D.dn, D.dd, li, acc);
         if (acc.n != 0) {
             int p = list_append(&st->T); D.tlist[p] = li;
+            WTRACE(13);
             if (val_sign(acc, D.heap) > 0) {
-                Cand c; c.v = val_div(bv, acc, D.heap, ar);
-                c.idx = I.row_lo + li; c.key = bkey;
+                Cand c; c.v = val_div(ld_val(D.xn, D.xd, li), acc, D.heap, ar);
+                c.idx = I.row_lo + li; c.key = D.basis[I.row_lo + li];
                 if (cand_better(c, best, ARG_RATIO, D.heap)) best = c;
+                WTRACE(14);
             }
         }
     }
+    WTRACE(15);
     best = block_argmin(best, ARG_RATIO, D.heap);
     if (threadIdx.x == 0) D.cand2[g.bid] = best;
 }
@@ -402,17 +595,35 @@ __device__ void stage_pivot_row(const Dev& D, const Grid& g, const Inv& I, int r
     if (pivot.n == 0) { if (g.tid == 0) atomicOr(&st->err, ERR_ZERO_PIVOT); return; }
     Arena ar = persistent(D);
     const size_t ld = I.ld;
-    for (int k = g.tid; k <= I.m; k += g.nth) {
-        size_t e = (size_t)k * ld + lr;
-        int64_t x = D.xn[e];
-        if (x == 0) { if (multi) { D.pn[k] = 0; D.pd[k] = 1; } continue; }
-        Val xv; xv.n = x; xv.d = D.xd[e];
-        Val p = val_div(xv, pivot, D.heap, ar);
-        st_val(D.xn, D.xd, e, p);
-        st_val(D.pn, D.pd, k, p);
-        if (!multi) { int s = list_append(&st->S); D.slist[s] = k; }
-        else if (p.d == 0) atomicOr(&st->err, ERR_LIMB_CAPACITY);   // escalated pivot rows do not cross GPUs yet
+    if (multi) {    // the all-reduce needs p densely
+        for (int k = g.tid; k <= I.m; k += g.nth) {
+            size_t e = (size_t)k * ld + lr;
+            int64_t x = D.xn[e];
+            if (x == 0) { D.pn[k] = 0; D.pd[k] = 1; continue; }
+            Val xv; xv.n = x; xv.d = D.xd[e];
+            Val p = val_div(xv, pivot, D.heap, ar);
+            st_val(D.xn, D.xd, e, p);
+            st_val(D.pn, D.pd, k, p);
+            if (p.d == 0) atomicOr(&st->err, ERR_LIMB_CAPACITY);   // escalated pivot rows do not cross GPUs yet
+        }
+        return;
     }
+    // the row's nonzero columns come from its row of rowbits: (m + 1) / 32 contiguous words
+    const uint32_t* rb = D.rowbits + (size_t)lr * I.wpr;
+    int len = 0;
+    for (int w = g.tid; w < I.wpr; w += g.nth) {
+        uint32_t bits = rb[w];
+        while (bits) {
+            int k = w * 32 + ctz32(bits); bits &= bits - 1;
+            size_t e = (size_t)k * ld + lr;
+            Val p = val_div(ld_val(D.xn, D.xd, e), pivot, D.heap, ar);
+            st_val(D.xn, D.xd, e, p);
+            st_val(D.pn, D.pd, k, p);
+            int s = list_append(&st->S); D.slist[s] = k;
+            if (k > 0) len += (int)(D.row_ptr[k] - D.row_ptr[k - 1]);
+        }
+    }
+    if (len) atomicAdd(&st->W, len);
 }
 
 // multi-GPU: every rank derives the column list from the replicated pivot row
@@ -427,7 +638,7 @@ __device__ void stage_build_slist(const Dev& D, const Grid& g, const Inv& I) {
 // row.  Fixed-width tier in place; elements whose operands or result leave int64/int64 are queued
 // for the multi-limb stage.  One thread does the basis bookkeeping (tableau/mod.rs:72-84).
 // ---------------------------------------------------------------------------------------------
-__device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, int r, Val rc) {
+__device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, int r, Val rc, int keeps_rc) {
     DState* st = D.st;
     const int T = st->T, S = st->S; const size_t ld = I.ld;
     const int lr = r - I.row_lo;
@@ -442,8 +653,14 @@ __device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, i
         Val dv = ld_val(D.dn, D.dd, li);
         Val p = ld_val(D.pn, D.pd, k);
         Val out;
-        if (x.d > 0 && dv.d > 0 && p.d > 0 && small_fma(x, dv, p, -1, &out)) st_val(D.xn, D.xd, e, out);
-        else { int q = atomicAdd(&st->wl_count, 1); D.worklist[q] = make_int2(li, k); }
+        if (x.d > 0 && dv.d > 0 && p.d > 0 && small_fma(x, dv, p, -1, &out)) {
+            st_val(D.xn, D.xd, e, out);
+            if ((x.n != 0) != (out.n != 0)) pattern_set(D, I, li, k, out.n != 0);
+        }
+        else {
+            int q = atomicAdd(&st->wl_count, 1);
+            if (q < st->wl_cap) D.worklist[q] = make_int2(li, k); else atomicOr(&st->err, ERR_HEAP_EXHAUSTED);
+        }
     }
     if (rc.n != 0) {   // carry/mod.rs:326-333; rc == 0 only for the zero-cost clean-up pivots
         Arena ar = persistent(D);
@@ -462,6 +679,7 @@ __device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, i
         D.basis[r] = j;
         D.in_basis[leaving] = 0; D.in_basis[j] = 1;
         st->leaving = leaving; st->j = j; st->r = r;
+        if (!keeps_rc) st->rc_valid = 0;     // step-wise / multi-GPU drivers price from scratch
         int b_nz = (lr >= 0 && lr < I.mloc) ? (D.xn[lr] != 0) : (D.pn[0] != 0);   // p_0 = b_r / pivot
         int Tl = T - 1;                       // reference's col.len() - 1 (rows eliminated) on this rank
         int Sl = S - b_nz + 1;                // nnz(B^-1 row r) + 1
@@ -477,7 +695,7 @@ __device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, i
 // Stage F -- K1c: the queued elements in the multi-limb tier.
 __device__ void stage_update_big(const Dev& D, const Grid& g, const Inv& I) {
     DState* st = D.st;
-    const int n = st->wl_count; const size_t ld = I.ld;
+    const int n = st->wl_count < st->wl_cap ? st->wl_count : st->wl_cap; const size_t ld = I.ld;
     Arena ar = persistent(D);
     for (int w = g.tid; w < n; w += g.nth) {
         int2 it = D.worklist[w];
@@ -485,6 +703,7 @@ __device__ void stage_update_big(const Dev& D, const Grid& g, const Inv& I) {
         Val x = ld_val(D.xn, D.xd, e);
         Val out = big_fma(x, ld_val(D.dn, D.dd, it.x), ld_val(D.pn, D.pd, it.y), -1, D.heap, ar);
         st_val(D.xn, D.xd, e, out);
+        if ((x.n != 0) != (out.n != 0)) pattern_set(D, I, it.x, it.y, out.n != 0);
     }
 }
 
@@ -495,7 +714,7 @@ __device__ void end_of_iteration(const Dev& D) {
     st->iter++;
     st->go = !halted(st);
     st->tr_top = st->tr_base;
-    st->T = 0; st->S = 0; st->wl_count = 0;
+    st->T = 0; st->S = 0; st->wl_count = 0; st->W = 0;
     unsigned long long used = st->pool_top - st->pool_base;
     if (used > st->pool_peak) st->pool_peak = used;
     if (used > (st->pool_limit - st->pool_base) / 2) {
@@ -524,6 +743,13 @@ __device__ void stage_compact(const Dev& D, const Grid& g) {
             Val v; v.n = D.zn[k]; v.d = 0;
             Val c = copy_val(v, D.heap, ar);
             D.zn[k] = c.n; D.zd[k] = c.d;
+        }
+    }
+    if (st->rc_valid) for (int j = g.tid; j < st->ncols; j += g.nth) {
+        if (D.rd[j] == 0) {
+            Val v; v.n = D.rn[j]; v.d = 0;
+            Val c = copy_val(v, D.heap, ar);
+            D.rn[j] = c.n; D.rd[j] = c.d;
         }
     }
 }
@@ -558,27 +784,41 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
     const Grid g = this_grid_dims();
     const Inv I = load_inv(st);
     const int mode = rule == RULE_DANTZIG ? ARG_DANTZIG : ARG_FIRST;
+    // The reduced-cost row is computed once (full pricing pass) and then kept current by every
+    // pivot; `rc_valid` is cleared by whatever replaces the cost row or the basis from outside.
+    if (!st->rc_valid) {
+        stage_price(D, g, I, mode, smem_words, 1);
+        GRID_SYNC();
+        if (g.tid == 0) st->rc_valid = 1;
+    }
     unsigned long long t0 = gtime();
     for (int it = 0; it < max_iters; it++) {
-        // `go` and `compacting` are written by one thread between the last two barriers of an
-        // iteration (or by the host before the launch): every thread reads the same value here
+        TRACE(0);
+        // Selection reads only the reduced-cost row; the previous iteration's bookkeeping (one
+        // thread: end_of_iteration) overlaps it and is published by the same barrier.
+        stage_select_rc(D, g, I, mode);
+        TRACE(1);
+        GRID_SYNC();
+        // `go` and `compacting` were written by one thread before that barrier (or by the host
+        // before the launch): every thread reads the same value here
         if (!st->go) break;
         if (st->compacting) {
             stage_compact(D, g);
             GRID_SYNC();
             if (g.tid == 0) st->compacting = 0;
         }
-        TRACE(0);
-        stage_price(D, g, I, mode, smem_words);
-        TRACE(1);
-        GRID_SYNC();
         unsigned long long t1 = gtime();
         TRACE(2);
         Cand col = reduce_candidates(D.cand, g.nb, mode, D.heap);      // same winner in every CTA
         if (g.tid == 0) commit_column(st, col, rule);
         if (col.idx < 0) break;
         TRACE(3);
+        unsigned long long w1 = gtime();
         stage_gen_column(D, g, I, col.idx);
+        unsigned long long w2 = gtime();
+#ifdef RELP_WTRACE
+        if (threadIdx.x == 0 && D.trace && st->iter < 7000) atomicMax(&D.trace[160 * 16 + 7000 * 8 + st->iter], ((w2 - w1) << 8) | (unsigned long long)g.bid);
+#endif
         TRACE(4);
         GRID_SYNC();
         TRACE(5);
@@ -587,12 +827,15 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
         if (g.tid == 0) commit_row(st, row);
         if (row.idx < 0) break;
         TRACE(6);
+        unsigned long long w3 = gtime();
         stage_pivot_row(D, g, I, row.idx, 0);
+        unsigned long long w4 = gtime();
         TRACE(7);
         GRID_SYNC();
         TRACE(8);
         unsigned long long t3 = gtime();
-        stage_update(D, g, I, col.idx, row.idx, col.v);
+        stage_update(D, g, I, col.idx, row.idx, col.v, 1);
+        stage_update_rc(D, g, I, row.idx, col.v, smem_words);
         TRACE(9);
         GRID_SYNC();
         unsigned long long t4 = gtime();
@@ -602,13 +845,19 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
             GRID_SYNC();
         }
         if (g.tid == 0) {
+#ifdef RELP_WTRACE
+            if (D.trace && st->iter < 7000) {      // per-iteration stage times behind the per-CTA slots
+                unsigned long long* q = D.trace + 160 * 16 + st->iter * 8;
+                q[0] = t1 - t0; q[1] = t2 - t1; q[2] = t3 - t2; q[3] = t4 - t3;
+                q[4] = w1 - t1; q[5] = w2 - t1; q[6] = w3 - t2; q[7] = w4 - t2;
+            }
+#endif
             end_of_iteration(D);
             unsigned long long t5 = gtime();
             st->stage_ns[0] += t1 - t0; st->stage_ns[1] += t2 - t1; st->stage_ns[2] += t3 - t2;
             st->stage_ns[3] += t4 - t3; st->stage_ns[4] += t5 - t4;
             t0 = t5;
         }
-        GRID_SYNC();
     }
 }
 
@@ -623,7 +872,7 @@ __global__ void k_begin(Dev D) {      // housekeeping that the persistent loop d
 __global__ void k_begin2(Dev D) { if (!halted(D.st)) D.st->compacting = 0; }
 __global__ void k_price(Dev D, int mode, int smem_words) {
     if (halted(D.st)) return;
-    stage_price(D, this_grid_dims(), load_inv(D.st), mode, smem_words);
+    stage_price(D, this_grid_dims(), load_inv(D.st), mode, smem_words, 0);
 }
 // reduce `count` candidates (this rank's blocks, or the all-gather buffer) and either commit the
 // decision or post this rank's winner to gather[slot] (multi-GPU stage 1)
@@ -650,7 +899,7 @@ __global__ void k_build_slist(Dev D) {
 }
 __global__ void k_update(Dev D) {
     if (halted(D.st)) return;
-    stage_update(D, this_grid_dims(), load_inv(D.st), D.st->j, D.st->r, D.st->rc);
+    stage_update(D, this_grid_dims(), load_inv(D.st), D.st->j, D.st->r, D.st->rc, 0);
 }
 __global__ void k_update_big(Dev D) {
     if (halted(D.st)) return;
@@ -677,6 +926,25 @@ __global__ void k_init_planes(Dev D, const int64_t* rhs_n, const int64_t* rhs_d)
             else if (k == i + 1) n = 1;
         }
         D.xn[e] = n; D.xd[e] = d;
+    }
+}
+
+// Nonzero pattern of the planes, rebuilt whenever they are written wholesale (set-up, row removal).
+__global__ void k_build_pattern(Dev D) {
+    DState* st = D.st;
+    const size_t ld = st->ld; const int wpc = st->ld >> 5, wpr = (st->m + 32) >> 5, m = st->m;
+    size_t nthreads = (size_t)gridDim.x * blockDim.x, tid = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    for (size_t w = tid; w < (size_t)(m + 1) * wpc; w += nthreads) {
+        int k = (int)(w / wpc), wb = (int)(w - (size_t)k * wpc);
+        uint32_t bits = 0;
+        for (int b = 0; b < 32; b++) if (D.xn[(size_t)k * ld + wb * 32 + b] != 0) bits |= 1u << b;
+        D.colbits[w] = bits;
+    }
+    for (size_t w = tid; w < (size_t)ld * wpr; w += nthreads) {
+        int kw = (int)(w / ld), li = (int)(w - (size_t)kw * ld);      // consecutive threads: consecutive rows
+        uint32_t bits = 0;
+        for (int b = 0; b < 32; b++) { int k = kw * 32 + b; if (k <= m && D.xn[(size_t)k * ld + li] != 0) bits |= 1u << b; }
+        D.rowbits[(size_t)li * wpr + kw] = bits;
     }
 }
 

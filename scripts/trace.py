@@ -23,3 +23,10 @@ d = tr[:, 7] - tr[:, 6]
 print("pivot_row duration per CTA (first 48):", d[:48])
 d = tr[:, 1] - tr[:, 0]
 print("price duration per CTA (first 64):", d[:64])
+print("select duration per CTA (first 32):", (tr[:, 1] - tr[:, 0])[:32])
+print("reduce1 (2->3) per CTA (first 32):", (tr[:, 3] - tr[:, 2])[:32])
+print("sync after gen (4->5) (first 32):", (tr[:, 5] - tr[:, 4])[:32])
+print("reduce2 (5->6) per CTA (first 32):", (tr[:, 6] - tr[:, 5])[:32])
+print("sync after pivot row (7->8) (first 32):", (tr[:, 8] - tr[:, 7])[:32])
+print("update (8->9) per CTA (first 32):", (tr[:, 9] - tr[:, 8])[:32], "last 8:", (tr[:, 9] - tr[:, 8])[-8:])
+print("sync after update (9->10) (first 32):", (tr[:, 10] - tr[:, 9])[:32])

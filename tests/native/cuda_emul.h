@@ -28,6 +28,7 @@ template <typename T> static inline T atomicAdd(T* p, T v) { T o = *p; *p += v; 
 static inline int atomicOr(int* p, int v) { int o = *p; *p |= v; return o; }
 static inline unsigned atomicOr(unsigned* p, unsigned v) { unsigned o = *p; *p |= v; return o; }
 static inline unsigned atomicAnd(unsigned* p, unsigned v) { unsigned o = *p; *p &= v; return o; }
+static inline int atomicExch(int* p, int v) { int o = *p; *p = v; return o; }
 static inline int atomicMin(int* p, int v) { int o = *p; if (v < o) *p = v; return o; }
 template <typename T> static inline T __shfl_down_sync(unsigned, T v, int) { return v; }
 static inline void __syncthreads() {}
@@ -48,6 +49,7 @@ static inline cudaError_t cudaFree(void* p) { free(p); return 0; }
 static inline cudaError_t cudaMallocHost(void** p, size_t n) { *p = calloc(1, n); return *p ? 0 : 2; }
 static inline cudaError_t cudaFreeHost(void* p) { free(p); return 0; }
 static inline cudaError_t cudaMemset(void* d, int v, size_t n) { memset(d, v, n); return 0; }
+static inline cudaError_t cudaMemsetAsync(void* d, int v, size_t n, cudaStream_t) { memset(d, v, n); return 0; }
 static inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, cudaMemcpyKind) { memmove(d, s, n); return 0; }
 static inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, cudaMemcpyKind, cudaStream_t) { memmove(d, s, n); return 0; }
 static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t* s, int) { *s = (void*)1; return 0; }
