@@ -73,7 +73,9 @@ typedef struct relp_stats {
     int32_t  max_limbs;         /* longest stored numerator/denominator seen at read-back    */
     int32_t  m, n, nr_artificial, phase;
     double   loop_ms;           /* device time (CUDA events) spent inside relp_iterate loops */
-    uint64_t stage_ns[8];       /* persistent loop, ns per stage: price, column+ratio, pivot row, update, multi-limb+housekeeping */
+    uint64_t stage_ns[8];       /* persistent loop, ns: [0] selection, [1] column+ratio, [2] pivot row, [3] update,
+                                   [4] multi-limb + housekeeping, [5] narrow iterations (CTA 0 alone, all stages) */
+    uint64_t narrow_pivots;     /* pivots done by one CTA alone (sparse B^-1), the rest by the whole grid   */
 } relp_stats;
 
 /* ---- life cycle ------------------------------------------------------------------------- */
@@ -85,7 +87,8 @@ void relp_destroy(relp_ctx*);
 const char* relp_last_error(void);
 int relp_abi_version(void);
 /* options: "persistent" = 1 (default) runs single-GPU loops as one cooperative kernel, 0 as one
- * launch per stage (the path multi-GPU solves use, with NCCL between the stages). */
+ * launch per stage (the path multi-GPU solves use, with NCCL between the stages); "narrow" = 1
+ * (default) lets CTA 0 of the persistent kernel do small pivots alone, 0 always uses the whole grid. */
 int relp_set_option(relp_ctx*, const char* name, int64_t value);
 /* the cudaStream_t all work of this context is enqueued on (for CUDA-event timing by the caller) */
 void* relp_stream(relp_ctx*);

@@ -48,7 +48,7 @@ class Stats(C.Structure):
                 ("sum_S", C.c_uint64), ("sum_TS", C.c_uint64), ("heap_peak_words", C.c_uint64),
                 ("compactions", C.c_uint64), ("kernel_launches", C.c_uint64), ("max_limbs", C.c_int32),
                 ("m", C.c_int32), ("n", C.c_int32), ("nr_artificial", C.c_int32), ("phase", C.c_int32),
-                ("loop_ms", C.c_double), ("stage_ns", C.c_uint64 * 8)]
+                ("loop_ms", C.c_double), ("stage_ns", C.c_uint64 * 8), ("narrow_pivots", C.c_uint64)]
 
 
 ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)

@@ -92,11 +92,11 @@ struct relp_ctx {
     DBuf<int64_t> xn, xd, zn, zd, an_d, ad_d, cn_d, cd_d, rhsn_d, rhsd_d, dn, dd, pnd, tmpn, tmpd, sell_an, sell_ad;
     DBuf<long long> col_ptr_d, sell_ptr; DBuf<uint32_t> zbits; DBuf<int> row_idx_d, sell_row, basis, art_row, tlist, slist, cost_rows, scratch_i;
     DBuf<unsigned char> in_basis;
-    DBuf<int64_t> rn, rd; DBuf<long long> row_ptr_d; DBuf<int> csr_col, row_art; DBuf<uint32_t> colbits, rowbits;   // reduced-cost row, nonzero pattern
+    DBuf<int64_t> rn, rd; DBuf<long long> row_ptr_d; DBuf<int> csr_col, row_art; DBuf<uint32_t> colbits, rowbits, colsum;   // reduced-cost row, nonzero pattern
     size_t wl_cap = 0;
     DBuf<int2> worklist; DBuf<Cand> cand, cand2, gather; DBuf<LogEntry> log; DBuf<unsigned long long> trace;
     int n_slices = 0, a_int = 1, coop_blocks = 0, last_ratio_blocks = 1;
-    bool use_persistent = true, smem_opt_in = false;
+    bool use_persistent = true, use_narrow = true, smem_opt_in = false;
     DState* h_st = nullptr;       // pinned mirror
     Dev D;
     bool loaded = false, carry_ready = false;
@@ -346,7 +346,7 @@ static void wire_dev(relp_ctx* c) {
     D.pn = c->pnd.p; D.pd = c->pnd.p + (c->m + 1);
     D.tlist = c->tlist.p; D.slist = c->slist.p; D.worklist = c->worklist.p; D.cand = c->cand.p; D.cand2 = c->cand2.p;
     D.rn = c->rn.p; D.rd = c->rd.p; D.row_ptr = c->row_ptr_d.p; D.csr_col = c->csr_col.p;
-    D.colbits = c->colbits.p; D.rowbits = c->rowbits.p; D.row_art = c->row_art.p;
+    D.colbits = c->colbits.p; D.rowbits = c->rowbits.p; D.colsum = c->colsum.p; D.row_art = c->row_art.p;
     D.gather = c->gather.p; D.log = c->log.p; D.log_cap = (long long)c->log.n; D.trace = c->trace.p; D.zbits = c->zbits.p;
 }
 
@@ -363,7 +363,8 @@ static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
     if (c->basis.alloc(m) || c->art_row.alloc(m) || c->tlist.alloc(c->mloc + 1) || c->slist.alloc(m + 1)) return RELP_ERR_CUDA;
     if (c->cost_rows.alloc(c->mloc + 1) || c->scratch_i.alloc(2 * (size_t)(m + 2))) return RELP_ERR_CUDA;
     if (c->rn.alloc(ncols_max) || c->rd.alloc(ncols_max) || c->row_art.alloc(m) ||
-        c->colbits.alloc((size_t)(m + 1) * (c->ld / 32) + 2) || c->rowbits.alloc((size_t)c->ld * ((m + 32) / 32) + 4)) return RELP_ERR_CUDA;
+        c->colbits.alloc((size_t)(m + 1) * (c->ld / 32) + 2) || c->rowbits.alloc((size_t)c->ld * ((m + 32) / 32) + 4) ||
+        c->colsum.alloc((size_t)(m + 1) * ((c->ld / 32 + 31) / 32) + 2)) return RELP_ERR_CUDA;
     // worklist: worst case every element of the local block is escalated; capped at 128 MB (a larger
     // block of multi-limb entries reports RELP_ERR_HEAP_EXHAUSTED instead of reserving gigabytes up front)
     c->wl_cap = std::min<size_t>((size_t)(m + 1) * std::max(c->mloc, 1), (size_t)1 << 24);
@@ -498,7 +499,7 @@ static int check_cuda(relp_ctx* c) {
 
 static int launch_persistent(relp_ctx* c, int rule, int max_iters) {
 #ifdef RELP_EMUL
-    k_simplex_loop(c->D, rule, max_iters, 0);
+    k_simplex_loop(c->D, rule, max_iters, 0, 0);
     c->launches++;
     return 0;
 #else
@@ -515,7 +516,8 @@ static int launch_persistent(relp_ctx* c, int rule, int max_iters) {
         CUDA_TRY(cudaFuncSetAttribute(k_price, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         c->smem_opt_in = true;
     }
-    void* args[] = { (void*)&c->D, (void*)&rule, (void*)&max_iters, (void*)&sw };
+    int narrow = c->use_narrow ? 1 : 0;
+    void* args[] = { (void*)&c->D, (void*)&rule, (void*)&max_iters, (void*)&sw, (void*)&narrow };
     CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_simplex_loop, dim3(c->coop_blocks), dim3(RELP_PTHREADS), args, smem, c->stream));
     c->launches++;
     return 0;
@@ -1015,6 +1017,7 @@ int relp_stats_get(relp_ctx* c, relp_stats* out) {
         out->pivots = s->iter; out->escalated = s->escalated; out->sum_T = s->sum_T; out->sum_S = s->sum_S;
         out->sum_TS = s->sum_TS; out->heap_peak_words = s->pool_peak; out->compactions = s->compactions;
         for (int k = 0; k < 8; k++) out->stage_ns[k] = s->stage_ns[k];
+        out->narrow_pivots = s->narrow_done;
     }
     return RELP_OK;
 }
@@ -1027,6 +1030,7 @@ int relp_rows_removed(relp_ctx* c, int32_t* out, int32_t cap) {
 int relp_set_option(relp_ctx* c, const char* name, int64_t value) {
     if (!c || !name) return RELP_ERR_ARGUMENT;
     if (!strcmp(name, "persistent")) { c->use_persistent = value != 0; return RELP_OK; }
+    if (!strcmp(name, "narrow")) { c->use_narrow = value != 0; return RELP_OK; }
     if (!strcmp(name, "trace")) {      // debug: per-CTA barrier arrival times of the last iteration
         if (value) { if (c->trace.alloc(16 * 4096)) return RELP_ERR_CUDA; cudaMemset(c->trace.p, 0, 16 * 4096 * 8); }
         else c->trace.release();

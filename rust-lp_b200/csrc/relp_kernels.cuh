@@ -60,6 +60,8 @@ struct DState {
     int rc_valid;                  // the stored reduced-cost row (Dev::rn, rd) is current
     int W;                         // sum of the CSR row lengths over the pivot row's nonzero columns
     int wl_cap;                    // capacity of the escalation worklist
+    int narrow_verdict;            // persistent loop: outcome of CTA 0's attempt at the current iteration
+    unsigned long long narrow_done;   // iterations completed by CTA 0 alone
     unsigned long long iter, iter_limit;
     unsigned long long pool_top, pool_limit, pool_base;   // active persistent region of the limb heap
     unsigned long long alt_base, alt_limit;               // the other persistent region (compaction target)
@@ -101,6 +103,7 @@ struct Dev {
     // rowbits word (li, k / 32) is the transpose (the pivot row's nonzero columns come from one
     // contiguous read, and that row of rowbits IS the bitmap "p_k != 0" of the reduced-cost update).
     uint32_t* colbits; uint32_t* rowbits;
+    uint32_t* colsum;                         // per column: which blocks of 32 rows MAY be nonzero (bits are only ever set)
     const int* row_art;                       // row -> its artificial column, or -1
     unsigned long long* trace;                // debug: per-CTA arrival time at each barrier (16 slots per CTA)
 };
@@ -126,7 +129,7 @@ __device__ __forceinline__ unsigned long long gtime0() { unsigned long long t; a
 #endif
 // loop invariants of DState, read once per kernel (every barrier invalidates L1, so re-reading
 // them from global memory in every stage costs an L2 round trip each time)
-struct Inv { int m, mloc, row_lo, ld, n, nr_art, phase, ncols, sl_lo, sl_hi, art_lo, art_hi, a_int, wpc, wpr; };
+struct Inv { int m, mloc, row_lo, ld, n, nr_art, phase, ncols, sl_lo, sl_hi, art_lo, art_hi, a_int, wpc, wpr, wsc; };
 __device__ __forceinline__ Grid this_grid_dims() {
     Grid g; g.tid = blockIdx.x * blockDim.x + threadIdx.x; g.nth = gridDim.x * blockDim.x;
     g.bid = blockIdx.x; g.nb = gridDim.x; return g;
@@ -137,6 +140,7 @@ __device__ __forceinline__ Inv load_inv(const DState* st) {
     I.phase = st->phase; I.ncols = st->ncols; I.sl_lo = st->sl_lo; I.sl_hi = st->sl_hi; I.art_lo = st->art_lo;
     I.art_hi = st->art_hi; I.a_int = st->a_int;
     I.wpc = st->ld >> 5; I.wpr = (st->m + 32) >> 5;   // words per column of colbits / per row of rowbits
+    I.wsc = (I.wpc + 31) >> 5;                        // words per column of colsum
     return I;
 }
 __device__ __forceinline__ Arena transient(const Dev& D) {
@@ -235,7 +239,10 @@ __device__ Cand reduce_candidates(const Cand* src, int count, int mode, const ui
 __device__ __forceinline__ void pattern_set(const Dev& D, const Inv& I, int li, int k, bool nonzero) {
     uint32_t* c = D.colbits + (size_t)k * I.wpc + (li >> 5);
     uint32_t* r = D.rowbits + (size_t)li * I.wpr + (k >> 5);
-    if (nonzero) { atomicOr(c, 1u << (li & 31)); atomicOr(r, 1u << (k & 31)); }
+    if (nonzero) {
+        atomicOr(c, 1u << (li & 31)); atomicOr(r, 1u << (k & 31));
+        atomicOr(D.colsum + (size_t)k * I.wsc + (li >> 10), 1u << ((li >> 5) & 31));
+    }
     else { atomicAnd(c, ~(1u << (li & 31))); atomicAnd(r, ~(1u << (k & 31))); }
 }
 
@@ -408,6 +415,39 @@ __device__ void stage_select_rc(const Dev& D, const Grid& g, const Inv& I, int m
 // columns are enumerated from the CSR pattern of A; otherwise one
 // SELL pass with the pivot row's bitmap.  Runs in the same barrier interval as the Carry update,
 // from the other end of the grid.
+// rc_jj -= rc * (p . A_jj), done by the caller that came from the SMALLEST row k with p_k != 0 in
+// column jj (`from_k`), so a column touched from several rows is updated exactly once, no atomics.
+__device__ __forceinline__ void rc_column_update(const Dev& D, int jj, int from_k, const Val& rc, int off, const uint32_t* pbits, const Arena& ar) {
+    Val old = ld_val(D.rn, D.rd, off + jj);            // requested early, used last
+    const long long t0 = D.col_ptr[jj], t1 = D.col_ptr[jj + 1];
+    Val alpha = val_zero();
+    int first = 0x7fffffff;
+    for (long long seg = t0; seg < t1; seg += 32) {
+        const int wseg = t1 - seg < 32 ? (int)(t1 - seg) : 32;
+        unsigned hits = 0;
+        for (int t = 0; t < wseg; t += RELP_CHG) {
+            int kk[RELP_CHG]; uint32_t ww[RELP_CHG];
+#pragma unroll
+            for (int u = 0; u < RELP_CHG; u++) kk[u] = t + u < wseg ? D.row_idx[seg + t + u] + 1 : -1;
+#pragma unroll
+            for (int u = 0; u < RELP_CHG; u++) ww[u] = kk[u] >= 0 ? pbits[kk[u] >> 5] : 0u;
+#pragma unroll
+            for (int u = 0; u < RELP_CHG; u++) if (kk[u] >= 0 && ((ww[u] >> (kk[u] & 31)) & 1u)) {
+                hits |= 1u << (t + u);
+                if (kk[u] < first) first = kk[u];
+            }
+        }
+        if (first < from_k) return;                    // another caller owns this column
+        while (hits) {
+            int t = ctz32(hits); hits &= hits - 1;
+            int kk = D.row_idx[seg + t] + 1;
+            alpha = val_fma(alpha, ld_val(D.pn, D.pd, kk), make_small(D.an[seg + t], D.ad[seg + t]), 1, D.heap, ar);
+        }
+    }
+    if (first == from_k && alpha.n != 0)
+        st_val(D.rn, D.rd, off + jj, val_fma(old, rc, alpha, -1, D.heap, ar));
+}
+
 // one column k = slist[s] of the pivot row, i.e. row k - 1 of A: one thread of the CTA per entry
 __device__ __forceinline__ void rc_sparse_row(const Dev& D, const Inv& I, int s, const Val& rc, int off, const uint32_t* pbits, const Arena& ar) {
     const int k = D.slist[s];
@@ -417,36 +457,7 @@ __device__ __forceinline__ void rc_sparse_row(const Dev& D, const Inv& I, int s,
         if (a >= 0) st_val(D.rn, D.rd, a, val_fma(ld_val(D.rn, D.rd, a), rc, ld_val(D.pn, D.pd, k), -1, D.heap, ar));
     }
     const long long lo = D.row_ptr[k - 1], hi = D.row_ptr[k];
-    for (long long e = lo + threadIdx.x; e < hi; e += blockDim.x) {
-        const int jj = D.csr_col[e];
-        Val old = ld_val(D.rn, D.rd, off + jj);            // requested early, used last
-        const long long t0 = D.col_ptr[jj], t1 = D.col_ptr[jj + 1];
-        Val alpha = val_zero();
-        int first = 0x7fffffff;
-        for (long long seg = t0; seg < t1; seg += 32) {
-            const int wseg = t1 - seg < 32 ? (int)(t1 - seg) : 32;
-            unsigned hits = 0;
-            for (int t = 0; t < wseg; t += RELP_CHG) {
-                int kk[RELP_CHG]; uint32_t ww[RELP_CHG];
-#pragma unroll
-                for (int u = 0; u < RELP_CHG; u++) kk[u] = t + u < wseg ? D.row_idx[seg + t + u] + 1 : -1;
-#pragma unroll
-                for (int u = 0; u < RELP_CHG; u++) ww[u] = kk[u] >= 0 ? pbits[kk[u] >> 5] : 0u;
-#pragma unroll
-                for (int u = 0; u < RELP_CHG; u++) if (kk[u] >= 0 && ((ww[u] >> (kk[u] & 31)) & 1u)) {
-                    hits |= 1u << (t + u);
-                    if (kk[u] < first) first = kk[u];
-                }
-            }
-            while (hits) {
-                int t = ctz32(hits); hits &= hits - 1;
-                int kk = D.row_idx[seg + t] + 1;
-                alpha = val_fma(alpha, ld_val(D.pn, D.pd, kk), make_small(D.an[seg + t], D.ad[seg + t]), 1, D.heap, ar);
-            }
-        }
-        if (first == k && alpha.n != 0)
-            st_val(D.rn, D.rd, off + jj, val_fma(old, rc, alpha, -1, D.heap, ar));
-    }
+    for (long long e = lo + threadIdx.x; e < hi; e += blockDim.x) rc_column_update(D, D.csr_col[e], k, rc, off, pbits, ar);
 }
 
 #ifndef RELP_RC_SPARSE_S
@@ -497,84 +508,101 @@ __device__ void stage_update_rc(const Dev& D, const Grid& g, const Inv& I, int r
 // Stage C -- K2 + K4: d_i = sum_k Binv[i][k] a_kj for every local row, the list of rows with
 // d_i != 0, and the exact argmin of b_i / d_i over rows with d_i > 0 (block level).
 // ---------------------------------------------------------------------------------------------
-__device__ void stage_gen_column(const Dev& D, const Grid& g, const Inv& I, int j) {
-    DState* st = D.st;
-    Arena ar = transient(D);
-    int unit_row = -1; long long t0 = 0, t1 = 0;
-    if (I.phase == 1 && j < I.nr_art) unit_row = D.art_row[j];
-    else { int jj = I.phase == 1 ? j - I.nr_art : j; t0 = D.col_ptr[jj]; t1 = D.col_ptr[jj + 1]; }
-    const int mloc = I.mloc; const size_t ld = I.ld;
+struct ColumnRef { int unit_row; long long t0, t1; };
+__device__ __forceinline__ ColumnRef column_ref(const Dev& D, const Inv& I, int j) {
+    ColumnRef c; c.unit_row = -1; c.t0 = 0; c.t1 = 0;
+    if (I.phase == 1 && j < I.nr_art) c.unit_row = D.art_row[j];
+    else { int jj = I.phase == 1 ? j - I.nr_art : j; c.t0 = D.col_ptr[jj]; c.t1 = D.col_ptr[jj + 1]; }
+    return c;
+}
+
+#ifndef RELP_EMUL
+// d_i for the 32 rows of row block `rb` (one warp, lane = row).  Lane u fetches entry u of a_j and the
+// ONE word of colbits that says which of the 32 rows are nonzero in that column of B^-1; the words
+// are passed round by shuffle, so a block of rows that the column does not touch costs col_ptr ->
+// row_idx -> colbits and no read of B^-1 at all.  A row's own hits are then fetched four at a time.
+__device__ __forceinline__ Val gen_rows_block(const Dev& D, const Inv& I, int unit_row, const int* ents, int nent,
+                                              const int64_t* an, const int64_t* ad, int rb, int lane, const Arena& ar) {
+    const size_t ld = I.ld;
     const int64_t* xn = D.xn + ld;     // column 1 + k at xn + k * ld
     const int64_t* xd = D.xd + ld;
     const uint32_t* cb = D.colbits + I.wpc;          // column 1 + k at cb + k * wpc
+    const int li = rb * 32 + lane;
+    Val acc = val_zero();
+    if (unit_row >= 0) {
+        uint32_t word = cb[(size_t)unit_row * I.wpc + rb];
+        if ((word >> lane) & 1u) acc = copy_val(ld_val(xn, xd, (size_t)unit_row * ld + li), D.heap, ar);
+        return acc;
+    }
+    for (int seg = 0; seg < nent; seg += 32) {
+        const int cnt = nent - seg < 32 ? nent - seg : 32;
+        const int kk = lane < cnt ? ents[seg + lane] : -1;
+        const uint32_t word = kk >= 0 ? cb[(size_t)kk * I.wpc + rb] : 0u;
+        unsigned act = __ballot_sync(0xffffffffu, word != 0u);
+        unsigned mine = 0;                      // entries of this segment that hit MY row
+        while (act) {
+            const int u = ctz32(act); act &= act - 1;
+            const uint32_t w = __shfl_sync(0xffffffffu, word, u);
+            if ((w >> lane) & 1u) mine |= 1u << u;
+        }
+        while (mine) {
+            int uu[4]; Val xx[4], aa[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) { uu[q] = mine ? ctz32(mine) : -1; if (mine) mine &= mine - 1; }
+#pragma unroll
+            for (int q = 0; q < 4; q++) if (uu[q] >= 0) {
+                xx[q] = ld_val(xn, xd, (size_t)ents[seg + uu[q]] * ld + li);
+                aa[q] = make_small(an[seg + uu[q]], ad[seg + uu[q]]);
+            }
+#pragma unroll
+            for (int q = 0; q < 4; q++) if (uu[q] >= 0) acc = val_fma(acc, xx[q], aa[q], 1, D.heap, ar);
+        }
+    }
+    return acc;
+}
+#endif
+
+// row li has d_i = acc: record it, and offer it to the ratio test when d_i > 0
+__device__ __forceinline__ void gen_row_done(const Dev& D, const Inv& I, int li, const Val& acc, int* t_counter, Cand& best, const Arena& ar) {
+    st_val(D.dn, D.dd, li, acc);
+    if (acc.n == 0) return;
+    int p = list_append(t_counter); D.tlist[p] = li;
+    if (val_sign(acc, D.heap) > 0) {
+        Cand c; c.v = val_div(ld_val(D.xn, D.xd, li), acc, D.heap, ar);
+        c.idx = I.row_lo + li; c.key = D.basis[I.row_lo + li];
+        if (cand_better(c, best, ARG_RATIO, D.heap)) best = c;
+    }
+}
+
+__device__ void stage_gen_column(const Dev& D, const Grid& g, const Inv& I, int j) {
+    DState* st = D.st;
+    Arena ar = transient(D);
+    const ColumnRef c = column_ref(D, I, j);
+    const int mloc = I.mloc;
     Cand best = cand_none();
 #ifdef RELP_EMUL
+    const size_t ld = I.ld;
+    const int64_t* xn = D.xn + ld; const int64_t* xd = D.xd + ld;
+    const uint32_t* cb = D.colbits + I.wpc;
     for (int li = 0; li < mloc; li++) {
         Val acc = val_zero();
-        if (unit_row >= 0) {
-            if ((cb[(size_t)unit_row * I.wpc + (li >> 5)] >> (li & 31)) & 1u)
-                acc = copy_val(ld_val(xn, xd, (size_t)unit_row * ld + li), D.heap, ar);
-        } else for (long long t = t0; t < t1; t++) {
+        if (c.unit_row >= 0) {
+            if ((cb[(size_t)c.unit_row * I.wpc + (li >> 5)] >> (li & 31)) & 1u)
+                acc = copy_val(ld_val(xn, xd, (size_t)c.unit_row * ld + li), D.heap, ar);
+        } else for (long long t = c.t0; t < c.t1; t++) {
             int kk = D.row_idx[t];
             if ((cb[(size_t)kk * I.wpc + (li >> 5)] >> (li & 31)) & 1u)
                 acc = val_fma(acc, ld_val(xn, xd, (size_t)kk * ld + li), make_small(D.an[t], D.ad[t]), 1, D.heap, ar);
         }
+        gen_row_done(D, I, li, acc, &st->T, best, ar);
+    }
 #else
-    // A warp owns 32 consecutive rows.  Lane u fetches entry u of a_j and the ONE word of colbits that
-    // says which of the warp's 32 rows are nonzero in that column of B^-1; the words are passed round
-    // by shuffle, so a block of rows that the column does not touch costs col_ptr -> row_idx ->
-    // colbits and no read of B^-1 at all.  Entries that do hit are visited by the whole warp together
-    // (coalesced over the rows).
     const int lane = threadIdx.x & 31, gw = (threadIdx.x >> 5) * g.nb + g.bid, nw = g.nth >> 5;
     for (int rb = gw; rb * 32 < mloc; rb += nw) {
-        const int li = rb * 32 + lane;
-        Val acc = val_zero();
-        if (unit_row >= 0) {
-            uint32_t word = cb[(size_t)unit_row * I.wpc + rb];
-            if ((word >> lane) & 1u) acc = copy_val(ld_val(xn, xd, (size_t)unit_row * ld + li), D.heap, ar);
-        } else for (long long seg = t0; seg < t1; seg += 32) {
-            const int cnt = t1 - seg < 32 ? (int)(t1 - seg) : 32;
-            const int kk = lane < cnt ? D.row_idx[seg + lane] : -1;
-            const uint32_t word = kk >= 0 ? cb[(size_t)kk * I.wpc + rb] : 0u;
-            unsigned act = __ballot_sync(0xffffffffu, word != 0u);
-            if (act) WTRACE(11);
-            unsigned mine = 0;                      // entries of this segment that hit MY row
-            while (act) {
-                const int u = ctz32(act); act &= act - 1;
-                const uint32_t w = __shfl_sync(0xffffffffu, word, u);
-                if ((w >> lane) & 1u) mine |= 1u << u;
-            }
-            // four hits at a time: all operands are requested before the first is used (one round trip
-            // to B^-1 per four hits of a row, however many entries of a_j touch this block of rows)
-            while (mine) {
-                int uu[4]; Val xx[4], aa[4];
-#pragma unroll
-                for (int q = 0; q < 4; q++) { uu[q] = mine ? ctz32(mine) : -1; if (mine) mine &= mine - 1; }
-#pragma unroll
-                for (int q = 0; q < 4; q++) if (uu[q] >= 0) {
-                    xx[q] = ld_val(xn, xd, (size_t)D.row_idx[seg + uu[q]] * ld + li);
-                    aa[q] = make_small(D.an[seg + uu[q]], D.ad[seg + uu[q]]);
-                }
-#pragma unroll
-                for (int q = 0; q < 4; q++) if (uu[q] >= 0) acc = val_fma(acc, xx[q], aa[q], 1, D.heap, ar);
-            }
-        }
-        if (li >= mloc) continue;
-        if (acc.n != 0) WTRACE(12);
-#endif
-        st_val(D.dn, D.dd, li, acc);
-        if (acc.n != 0) {
-            int p = list_append(&st->T); D.tlist[p] = li;
-            WTRACE(13);
-            if (val_sign(acc, D.heap) > 0) {
-                Cand c; c.v = val_div(ld_val(D.xn, D.xd, li), acc, D.heap, ar);
-                c.idx = I.row_lo + li; c.key = D.basis[I.row_lo + li];
-                if (cand_better(c, best, ARG_RATIO, D.heap)) best = c;
-                WTRACE(14);
-            }
-        }
+        Val acc = gen_rows_block(D, I, c.unit_row, D.row_idx + c.t0, (int)(c.t1 - c.t0), D.an + c.t0, D.ad + c.t0, rb, lane, ar);
+        if (rb * 32 + lane < mloc) gen_row_done(D, I, rb * 32 + lane, acc, &st->T, best, ar);
     }
-    WTRACE(15);
+#endif
     best = block_argmin(best, ARG_RATIO, D.heap);
     if (threadIdx.x == 0) D.cand2[g.bid] = best;
 }
@@ -638,9 +666,50 @@ __device__ void stage_build_slist(const Dev& D, const Grid& g, const Inv& I) {
 // row.  Fixed-width tier in place; elements whose operands or result leave int64/int64 are queued
 // for the multi-limb stage.  One thread does the basis bookkeeping (tableau/mod.rs:72-84).
 // ---------------------------------------------------------------------------------------------
+// x_ik -= d_i p_k for one element (fixed-width tier in place, else queued for the multi-limb stage)
+__device__ __forceinline__ void carry_elem_update(const Dev& D, const Inv& I, int li, int k, const Val& dv, const Val& p) {
+    DState* st = D.st;
+    size_t e = (size_t)k * I.ld + li;
+    Val x = ld_val(D.xn, D.xd, e);
+    Val out;
+    if (x.d > 0 && dv.d > 0 && p.d > 0 && small_fma(x, dv, p, -1, &out)) {
+        st_val(D.xn, D.xd, e, out);
+        if ((x.n != 0) != (out.n != 0)) pattern_set(D, I, li, k, out.n != 0);
+    } else {
+        int q = atomicAdd(&st->wl_count, 1);
+        if (q < st->wl_cap) D.worklist[q] = make_int2(li, k); else atomicOr(&st->err, ERR_HEAP_EXHAUSTED);
+    }
+}
+// z_k -= rc p_k on the cost row [-obj | -pi] and its bitmap      (carry/mod.rs:326-333)
+__device__ __forceinline__ void cost_row_update(const Dev& D, int k, const Val& rc, const Val& p, const Arena& ar) {
+    Val z = val_fma(ld_val(D.zn, D.zd, k), rc, p, -1, D.heap, ar);
+    st_val(D.zn, D.zd, k, z);
+    if (k > 0) {
+        uint32_t bit = 1u << ((k - 1) & 31);
+        if (z.n != 0) atomicOr(&D.zbits[(k - 1) >> 5], bit); else atomicAnd(&D.zbits[(k - 1) >> 5], ~bit);
+    }
+}
+// basis bookkeeping and the log entry of this pivot (tableau/mod.rs:72-84); one thread
+__device__ __forceinline__ void pivot_bookkeeping(const Dev& D, int j, int r, int T, int S, int b_nz, const Val& rc, int keeps_rc) {
+    DState* st = D.st;
+    int leaving = D.basis[r];
+    D.basis[r] = j;
+    D.in_basis[leaving] = 0; D.in_basis[j] = 1;
+    st->leaving = leaving; st->j = j; st->r = r;
+    if (!keeps_rc) st->rc_valid = 0;     // step-wise / multi-GPU drivers price from scratch
+    int Tl = T - 1;                       // reference's col.len() - 1 (rows eliminated) on this rank
+    int Sl = S - b_nz + 1;                // nnz(B^-1 row r) + 1
+    if ((long long)st->iter < D.log_cap) {
+        LogEntry e; e.tag = st->tag; e.j = j; e.r = r; e.leaving = leaving; e.T = Tl; e.S = Sl;
+        D.log[st->iter] = e;
+    }
+    unsigned long long rows = (unsigned long long)(T - 1 + (rc.n != 0));
+    st->sum_T += rows; st->sum_S += (unsigned long long)S; st->sum_TS += rows * (unsigned long long)S;
+}
+
 __device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, int r, Val rc, int keeps_rc) {
     DState* st = D.st;
-    const int T = st->T, S = st->S; const size_t ld = I.ld;
+    const int T = st->T, S = st->S;
     const int lr = r - I.row_lo;
     const long long total = (long long)T * S;
     for (long long w = g.tid; w < total; w += g.nth) {
@@ -648,47 +717,15 @@ __device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, i
         int li = D.tlist[t];
         if (li == lr) continue;
         int k = D.slist[s];
-        size_t e = (size_t)k * ld + li;
-        Val x = ld_val(D.xn, D.xd, e);
-        Val dv = ld_val(D.dn, D.dd, li);
-        Val p = ld_val(D.pn, D.pd, k);
-        Val out;
-        if (x.d > 0 && dv.d > 0 && p.d > 0 && small_fma(x, dv, p, -1, &out)) {
-            st_val(D.xn, D.xd, e, out);
-            if ((x.n != 0) != (out.n != 0)) pattern_set(D, I, li, k, out.n != 0);
-        }
-        else {
-            int q = atomicAdd(&st->wl_count, 1);
-            if (q < st->wl_cap) D.worklist[q] = make_int2(li, k); else atomicOr(&st->err, ERR_HEAP_EXHAUSTED);
-        }
+        carry_elem_update(D, I, li, k, ld_val(D.dn, D.dd, li), ld_val(D.pn, D.pd, k));
     }
-    if (rc.n != 0) {   // carry/mod.rs:326-333; rc == 0 only for the zero-cost clean-up pivots
+    if (rc.n != 0) {   // rc == 0 only for the zero-cost clean-up pivots
         Arena ar = persistent(D);
-        for (int s = g.tid; s < S; s += g.nth) {
-            int k = D.slist[s];
-            Val z = val_fma(ld_val(D.zn, D.zd, k), rc, ld_val(D.pn, D.pd, k), -1, D.heap, ar);
-            st_val(D.zn, D.zd, k, z);
-            if (k > 0) {
-                uint32_t bit = 1u << ((k - 1) & 31);
-                if (z.n != 0) atomicOr(&D.zbits[(k - 1) >> 5], bit); else atomicAnd(&D.zbits[(k - 1) >> 5], ~bit);
-            }
-        }
+        for (int s = g.tid; s < S; s += g.nth) { int k = D.slist[s]; cost_row_update(D, k, rc, ld_val(D.pn, D.pd, k), ar); }
     }
     if (g.tid == 0) {
-        int leaving = D.basis[r];
-        D.basis[r] = j;
-        D.in_basis[leaving] = 0; D.in_basis[j] = 1;
-        st->leaving = leaving; st->j = j; st->r = r;
-        if (!keeps_rc) st->rc_valid = 0;     // step-wise / multi-GPU drivers price from scratch
         int b_nz = (lr >= 0 && lr < I.mloc) ? (D.xn[lr] != 0) : (D.pn[0] != 0);   // p_0 = b_r / pivot
-        int Tl = T - 1;                       // reference's col.len() - 1 (rows eliminated) on this rank
-        int Sl = S - b_nz + 1;                // nnz(B^-1 row r) + 1
-        if ((long long)st->iter < D.log_cap) {
-            LogEntry e; e.tag = st->tag; e.j = j; e.r = r; e.leaving = leaving; e.T = Tl; e.S = Sl;
-            D.log[st->iter] = e;
-        }
-        unsigned long long rows = (unsigned long long)(T - 1 + (rc.n != 0));
-        st->sum_T += rows; st->sum_S += (unsigned long long)S; st->sum_TS += rows * (unsigned long long)S;
+        pivot_bookkeeping(D, j, r, T, S, b_nz, rc, keeps_rc);
     }
 }
 
@@ -775,11 +812,195 @@ static inline unsigned long long gtime() { return 0; }
 #define TRACE(k) do {} while (0)
 #endif
 
+#ifndef RELP_EMUL
+// ---------------------------------------------------------------------------------------------
+// Narrow iteration.  While B^-1 is sparse a pivot touches a few dozen Carry elements and a few
+// hundred reduced costs: spreading that over 148 CTAs buys nothing and costs a grid-wide barrier
+// after every stage.  CTA 0 therefore runs column generation, ratio test, pivot row, Carry update
+// and reduced-cost update ALONE, with block barriers in between; the rest of the grid only takes
+// part in the selection scan.  Every limit is checked before anything is modified: if the pivot
+// turns out to be too big for one CTA, the iteration is handed back (return 1) and redone by the
+// whole grid.  Returns 0 = done, 1 = redo wide, 2 = stop (no pivot row / error).
+// ---------------------------------------------------------------------------------------------
+#define RELP_NARROW_BLOCKS 64       // row blocks (of 32 rows) one CTA generates
+#define RELP_NARROW_ENT 1024        // entries of a_j held in shared memory
+#define RELP_NARROW_T 512           // rows with d_i != 0
+#define RELP_NARROW_S 64            // columns with p_k != 0
+#define RELP_NARROW_TS 4096         // Carry elements one CTA updates
+#define RELP_NARROW_W 8192          // reduced costs one CTA updates
+#define RELP_NARROW_SUMW 256        // words of the row-block summary held in shared memory
+#define RELP_NARROW_PBW 2048        // words of the pivot row's bitmap held in shared memory
+
+#if defined(RELP_WTRACE)
+#define NT(k) do { if (threadIdx.x == 0 && D.trace) { unsigned long long t_ = gtime0(); D.trace[150 * 16 + (k)] += t_ - tprev_; tprev_ = t_; } } while (0)
+#else
+#define NT(k) do {} while (0)
+#endif
+
+struct NarrowSmem {
+    uint32_t sum[RELP_NARROW_SUMW];
+    uint32_t pb[RELP_NARROW_PBW];            // p_k != 0 bitmap (copy of the pivot row's row of rowbits)
+    int ent[RELP_NARROW_ENT];                // rows of a_j
+    int blk[RELP_NARROW_BLOCKS];
+    int tl[RELP_NARROW_T]; Val dv[RELP_NARROW_T];       // rows with d_i != 0 and d_i
+    int sl[RELP_NARROW_S]; Val pv[RELP_NARROW_S];       // columns with p_k != 0 and p_k
+    long long plo[RELP_NARROW_S]; int pre[RELP_NARROW_S + 1];   // CSR row of A behind column k, prefix of lengths
+    int nblk, T, S, W, b_nz;
+    Val pivot;
+};
+
+__device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int smem_words) {
+    __shared__ NarrowSmem sm;
+#if defined(RELP_WTRACE)
+    unsigned long long tprev_ = gtime0();
+#endif
+    DState* st = D.st;
+    const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarps = nt >> 5;
+    Grid g0; g0.tid = tid; g0.nth = nt; g0.bid = 0; g0.nb = 1;
+    const int j = col.idx;
+    const Val rc = col.v;
+    const ColumnRef c = column_ref(D, I, j);
+    const int nent = c.unit_row >= 0 ? 1 : (int)(c.t1 - c.t0);
+    const int wsc = I.wsc;
+    if (wsc > RELP_NARROW_SUMW || nent > RELP_NARROW_ENT || I.wpr > RELP_NARROW_PBW) return 1;
+    // (a) which blocks of 32 rows can d = B^-1 a_j touch?   row_idx -> colsum, one entry per thread
+    for (int w = tid; w < wsc; w += nt) sm.sum[w] = 0;
+    if (tid == 0) { sm.T = 0; sm.S = 0; sm.W = 0; sm.b_nz = 0; }
+    __syncthreads();
+    for (int e = tid; e < nent; e += nt) sm.ent[e] = c.unit_row >= 0 ? c.unit_row : D.row_idx[c.t0 + e];
+    __syncthreads();
+    for (int it = tid; it < nent * wsc; it += nt) {
+        int e = it / wsc, w = it - e * wsc;
+        uint32_t word = D.colsum[(size_t)(1 + sm.ent[e]) * wsc + w];
+        if (word) atomicOr(&sm.sum[w], word);
+    }
+    __syncthreads();
+    if (warp == 0) {        // compact the set bits into a list of row blocks
+        int base = 0;
+        for (int w0 = 0; w0 < wsc; w0 += 32) {
+            uint32_t bits = w0 + lane < wsc ? sm.sum[w0 + lane] : 0u;
+            int cnt = __popc(bits), incl = cnt;
+            for (int d = 1; d < 32; d <<= 1) { int o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += o; }
+            int pos = base + incl - cnt;
+            while (bits) { int bb = ctz32(bits); bits &= bits - 1; if (pos < RELP_NARROW_BLOCKS) sm.blk[pos] = (w0 + lane) * 32 + bb; pos++; }
+            base += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (lane == 0) sm.nblk = base;
+    }
+    __syncthreads();
+    NT(1);
+    if (sm.nblk > RELP_NARROW_BLOCKS) return 1;
+    // (b) d, the rows with d_i != 0 and the ratio test; only scratch (dn, tlist) is written
+    Arena tr = transient(D);
+    Cand best = cand_none();
+    for (int q = warp; q < sm.nblk; q += nwarps) {
+        const int rb = sm.blk[q], li = rb * 32 + lane;
+        Val acc = gen_rows_block(D, I, c.unit_row, sm.ent, nent, D.an + c.t0, D.ad + c.t0, rb, lane, tr);
+        if (li < I.mloc && acc.n != 0) {
+            Val bv = ld_val(D.xn, D.xd, li); int key = D.basis[I.row_lo + li];
+            st_val(D.dn, D.dd, li, acc);
+            int t = list_append(&sm.T);
+            if (t < RELP_NARROW_T) { sm.tl[t] = li; sm.dv[t] = acc; D.tlist[t] = li; }
+            if (val_sign(acc, D.heap) > 0) {
+                Cand cd; cd.v = val_div(bv, acc, D.heap, tr); cd.idx = I.row_lo + li; cd.key = key;
+                if (cand_better(cd, best, ARG_RATIO, D.heap)) best = cd;
+            }
+        }
+    }
+    NT(2);
+    Cand row = block_argmin(best, ARG_RATIO, D.heap);       // (block barriers inside)
+    NT(3);
+    if (row.idx < 0) { if (tid == 0) commit_row(st, row); return 2; }
+    const int T = sm.T;
+    if (T > RELP_NARROW_T) return 1;
+    // (c) the pivot row into scratch: p_k = X[r][k] / d_r, its bitmap, and the CSR row of A behind each k
+    const int r = row.idx, lr = r - I.row_lo;
+    for (int t = tid; t < T; t += nt) if (sm.tl[t] == lr) sm.pivot = sm.dv[t];
+    __syncthreads();
+    const Val pivot = sm.pivot;
+    if (pivot.n == 0) { if (tid == 0) atomicOr(&st->err, ERR_ZERO_PIVOT); return 2; }
+    Arena ar = persistent(D);
+    const uint32_t* rbits = D.rowbits + (size_t)lr * I.wpr;
+    const size_t ld = I.ld;
+    for (int w = tid; w < I.wpr; w += nt) {
+        uint32_t bits = rbits[w];
+        sm.pb[w] = bits;
+        while (bits) {
+            int k = w * 32 + ctz32(bits); bits &= bits - 1;
+            Val x = ld_val(D.xn, D.xd, (size_t)k * ld + lr);
+            long long lo = k > 0 ? D.row_ptr[k - 1] : 0, hi = k > 0 ? D.row_ptr[k] : 0;
+            Val p = val_div(x, pivot, D.heap, ar);
+            int q = atomicAdd(&sm.S, 1);
+            if (q < RELP_NARROW_S) { sm.sl[q] = k; sm.pv[q] = p; sm.plo[q] = lo; sm.pre[q] = (int)(hi - lo); }
+            atomicAdd(&sm.W, (int)(hi - lo));
+            if (k == 0) sm.b_nz = 1;
+        }
+    }
+    __syncthreads();
+    const int S = sm.S, W = sm.W;
+    const long long nnz = D.col_ptr[I.n];
+    const bool rc_sparse = S <= RELP_RC_SPARSE_S && (long long)W * 32 <= nnz + 1024;
+    if (S > RELP_NARROW_S || (long long)T * S > RELP_NARROW_TS ||
+        (rc.n != 0 && (rc_sparse ? W > RELP_NARROW_W : (I.sl_hi - I.sl_lo) > 256))) return 1;
+    NT(4);
+    // (d) commit: row r in place and in the pivot-row buffer, then everything that depends on p
+    if (tid == 0) {
+        int acc = 0;
+        for (int q = 0; q < S; q++) { int len = sm.pre[q]; sm.pre[q] = acc; acc += len; }
+        sm.pre[S] = acc;
+        commit_row(st, row);
+        st->T = T; st->S = S; st->W = W;
+    }
+    for (int q = tid; q < S; q += nt) {
+        int k = sm.sl[q];
+        st_val(D.xn, D.xd, (size_t)k * ld + lr, sm.pv[q]);
+        st_val(D.pn, D.pd, k, sm.pv[q]);
+        D.slist[q] = k;
+    }
+    __syncthreads();
+    NT(5);
+    // one item space for the whole CTA: Carry elements, cost row, artificial and structural reduced costs
+    const int off = I.phase == 1 ? I.nr_art : 0;
+    const int n_carry = T * S, n_cost = rc.n != 0 ? S : 0, n_art = (rc.n != 0 && rc_sparse && I.phase == 1) ? S : 0;
+    const int n_rc = (rc.n != 0 && rc_sparse) ? W : 0;
+    const int total = n_carry + n_cost + n_art + n_rc;
+    for (int w = tid; w < total; w += nt) {
+        int it = w;
+        if (it < n_carry) {
+            int q = it / T, t = it - q * T;
+            if (sm.tl[t] != lr) carry_elem_update(D, I, sm.tl[t], sm.sl[q], sm.dv[t], sm.pv[q]);
+            continue;
+        }
+        it -= n_carry;
+        if (it < n_cost) { cost_row_update(D, sm.sl[it], rc, sm.pv[it], ar); continue; }
+        it -= n_cost;
+        if (it < n_art) {          // artificial column e_i (cost one): p . e_i = p_k
+            int k = sm.sl[it];
+            int a = k > 0 ? D.row_art[k - 1] : -1;
+            if (a >= 0) st_val(D.rn, D.rd, a, val_fma(ld_val(D.rn, D.rd, a), rc, sm.pv[it], -1, D.heap, ar));
+            continue;
+        }
+        it -= n_art;
+        int q = 0;
+        while (q + 1 < S && sm.pre[q + 1] <= it) q++;
+        rc_column_update(D, D.csr_col[sm.plo[q] + (it - sm.pre[q])], sm.sl[q], rc, off, sm.pb, ar);
+    }
+    if (tid == nt - 1) pivot_bookkeeping(D, j, r, T, S, sm.b_nz, rc, 1);
+    NT(6);
+    if (rc.n != 0 && !rc_sparse) stage_update_rc(D, g0, I, r, rc, smem_words);
+    __syncthreads();
+    NT(7);
+    if (st->wl_count > 0) { stage_update_big(D, g0, I); __syncthreads(); }
+    NT(8);
+    return 0;
+}
+#endif
+
 // ---------------------------------------------------------------------------------------------
 // The persistent loop: phase_one::primal / phase_two::primal (phase_one.rs:135-169,
 // phase_two.rs:32-50) entirely on the device.  Cooperative launch, one CTA per SM.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int rule, int max_iters, int smem_words) {
+__global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int rule, int max_iters, int smem_words, int use_narrow) {
     DState* st = D.st;
     const Grid g = this_grid_dims();
     const Inv I = load_inv(st);
@@ -812,46 +1033,58 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
         Cand col = reduce_candidates(D.cand, g.nb, mode, D.heap);      // same winner in every CTA
         if (g.tid == 0) commit_column(st, col, rule);
         if (col.idx < 0) break;
-        TRACE(3);
-        unsigned long long w1 = gtime();
-        stage_gen_column(D, g, I, col.idx);
-        unsigned long long w2 = gtime();
-#ifdef RELP_WTRACE
-        if (threadIdx.x == 0 && D.trace && st->iter < 7000) atomicMax(&D.trace[160 * 16 + 7000 * 8 + st->iter], ((w2 - w1) << 8) | (unsigned long long)g.bid);
+        unsigned long long t2 = t1, t3 = t1, t4 = t1;
+#ifndef RELP_EMUL
+        if (use_narrow) {
+            if (g.bid == 0) {
+                int verdict = narrow_iteration(D, I, col, smem_words);
+                if (threadIdx.x == 0) {
+                    st->narrow_verdict = verdict;
+                    if (verdict == 0) { t2 = t3 = t4 = gtime(); }
+                }
+            }
+            TRACE(4);
+            GRID_SYNC();
+            TRACE(5);
+            const int verdict = st->narrow_verdict;
+            if (verdict == 2) break;
+            if (verdict == 0) {
+                if (g.tid == 0) {
+                    st->narrow_done++;
+                    end_of_iteration(D);
+                    unsigned long long t5 = gtime();
+                    st->stage_ns[0] += t1 - t0; st->stage_ns[5] += t4 - t1; st->stage_ns[4] += t5 - t4;
+                    t0 = t5;
+                }
+                continue;
+            }
+            // verdict 1: nothing was modified; the whole grid redoes this iteration
+        }
 #endif
-        TRACE(4);
+        TRACE(3);
+        stage_gen_column(D, g, I, col.idx);
         GRID_SYNC();
-        TRACE(5);
-        unsigned long long t2 = gtime();
+        t2 = gtime();
         Cand row = reduce_candidates(D.cand2, g.nb, ARG_RATIO, D.heap);
         if (g.tid == 0) commit_row(st, row);
         if (row.idx < 0) break;
         TRACE(6);
-        unsigned long long w3 = gtime();
         stage_pivot_row(D, g, I, row.idx, 0);
-        unsigned long long w4 = gtime();
         TRACE(7);
         GRID_SYNC();
         TRACE(8);
-        unsigned long long t3 = gtime();
+        t3 = gtime();
         stage_update(D, g, I, col.idx, row.idx, col.v, 1);
         stage_update_rc(D, g, I, row.idx, col.v, smem_words);
         TRACE(9);
         GRID_SYNC();
-        unsigned long long t4 = gtime();
+        t4 = gtime();
         TRACE(10);
         if (st->wl_count > 0) {                 // final after the barrier: uniform
             stage_update_big(D, g, I);
             GRID_SYNC();
         }
         if (g.tid == 0) {
-#ifdef RELP_WTRACE
-            if (D.trace && st->iter < 7000) {      // per-iteration stage times behind the per-CTA slots
-                unsigned long long* q = D.trace + 160 * 16 + st->iter * 8;
-                q[0] = t1 - t0; q[1] = t2 - t1; q[2] = t3 - t2; q[3] = t4 - t3;
-                q[4] = w1 - t1; q[5] = w2 - t1; q[6] = w3 - t2; q[7] = w4 - t2;
-            }
-#endif
             end_of_iteration(D);
             unsigned long long t5 = gtime();
             st->stage_ns[0] += t1 - t0; st->stage_ns[1] += t2 - t1; st->stage_ns[2] += t3 - t2;
@@ -939,6 +1172,19 @@ __global__ void k_build_pattern(Dev D) {
         uint32_t bits = 0;
         for (int b = 0; b < 32; b++) if (D.xn[(size_t)k * ld + wb * 32 + b] != 0) bits |= 1u << b;
         D.colbits[w] = bits;
+    }
+    const int wsc = (wpc + 31) >> 5;
+    for (size_t w = tid; w < (size_t)(m + 1) * wsc; w += nthreads) {
+        int k = (int)(w / wsc), ws = (int)(w - (size_t)k * wsc);
+        uint32_t bits = 0;
+        for (int b = 0; b < 32; b++) {
+            int rb = ws * 32 + b;
+            if (rb >= wpc) break;
+            bool any = false;
+            for (int q = 0; q < 32 && !any; q++) any = D.xn[(size_t)k * ld + rb * 32 + q] != 0;
+            if (any) bits |= 1u << b;
+        }
+        D.colsum[w] = bits;
     }
     for (size_t w = tid; w < (size_t)ld * wpr; w += nthreads) {
         int kw = (int)(w / ld), li = (int)(w - (size_t)kw * ld);      // consecutive threads: consecutive rows

@@ -17,4 +17,4 @@ for rep in range(reps):
     print(f"rep {rep} m={m} n={n} status={st} pivots={s.pivots} loop_ms={s.loop_ms:.2f} wall_solve={1e3*(t2-t1):.1f}ms create+load={1e3*(t1-t0):.1f}ms "
           f"launches={s.kernel_launches} pivots/s(loop)={s.pivots/(s.loop_ms/1e3):.0f} sumTS={s.sum_TS} escal={s.escalated} obj={c.get_objective_function_value()}", flush=True)
     c.close()
-    print("   stage_us/iter:", [round(x / 1e3 / max(s.pivots, 1), 2) for x in s.stage_ns[:5]])
+    print("   stage_us/iter:", [round(x / 1e3 / max(s.pivots, 1), 2) for x in s.stage_ns[:6]], "narrow", s.narrow_pivots)
