@@ -117,15 +117,10 @@ RELP_HD uint64_t abs64(int64_t x) { return x < 0 ? (uint64_t)0 - (uint64_t)x : (
 // out = x + s * a * b, s = +1 or -1      (sparse.rs:213-248 add_multiple_of_row element,
 //                                          carry/mod.rs:283-313 update_b, :326-333 cost row,
 //                                          dense.rs:81-92 / sparse.rs:82-106 inner products)
-RELP_HD bool small_fma(const Val& x, const Val& a, const Val& b, int s, Val* out) {
-    if (a.n == 0 || b.n == 0) { *out = x; return true; }
-    if (x.d == 1 && a.d == 1 && b.d == 1) {                 // integer fast path
-        i128 t = (i128)a.n * b.n;
-        i128 r = s > 0 ? (i128)x.n + t : (i128)x.n - t;
-        if (r > RELP_I64_MAX || r < -RELP_I64_MAX) return false;
-        *out = make_small((int64_t)r, 1);
-        return true;
-    }
+// The general (rational) case is a separate, non-inlined function: it is long (three gcds, 128-bit
+// divisions) and the persistent kernel calls fma from dozens of places -- inlined everywhere it made
+// the kernel a megabyte of code that no instruction cache holds.  The integer case stays inline.
+RELP_HDN bool small_fma_rational(const Val& x, const Val& a, const Val& b, int s, Val* out) {
     // canonical product tn/td of a*b (cross-reduce, then multiply)
     uint64_t an = abs64(a.n), bn = abs64(b.n);
     uint64_t g1 = b.d == 1 ? 1 : gcd64(an, (uint64_t)b.d);
@@ -155,12 +150,20 @@ RELP_HD bool small_fma(const Val& x, const Val& a, const Val& b, int s, Val* out
     return true;
 }
 
-// out = x / y  (y != 0)      (sparse.rs:291-301 element_wise_divide, tableau/mod.rs:229 ratio)
-RELP_HD bool small_div(const Val& x, const Val& y, Val* out) {
-    if (x.n == 0) { *out = val_zero(); return true; }
-    if (y.d == 1 && (y.n == 1 || y.n == -1)) {          // unit pivots (totally unimodular bases)
-        *out = make_small(y.n > 0 ? x.n : -x.n, x.d); return true;
+RELP_HD bool small_fma(const Val& x, const Val& a, const Val& b, int s, Val* out) {
+    if (a.n == 0 || b.n == 0) { *out = x; return true; }
+    if (x.d == 1 && a.d == 1 && b.d == 1) {                 // integer fast path
+        i128 t = (i128)a.n * b.n;
+        i128 r = s > 0 ? (i128)x.n + t : (i128)x.n - t;
+        if (r > RELP_I64_MAX || r < -RELP_I64_MAX) return false;
+        *out = make_small((int64_t)r, 1);
+        return true;
     }
+    return small_fma_rational(x, a, b, s, out);
+}
+
+// out = x / y  (y != 0)      (sparse.rs:291-301 element_wise_divide, tableau/mod.rs:229 ratio)
+RELP_HDN bool small_div_general(const Val& x, const Val& y, Val* out) {
     uint64_t xn = abs64(x.n), yn = abs64(y.n);
     uint64_t g1 = gcd64(xn, yn);
     uint64_t g2 = (x.d == 1 || y.d == 1) ? 1 : gcd64((uint64_t)x.d, (uint64_t)y.d);
@@ -170,6 +173,14 @@ RELP_HD bool small_div(const Val& x, const Val& y, Val* out) {
     bool neg = (x.n < 0) != (y.n < 0);
     *out = make_small(neg ? -(int64_t)(uint64_t)n : (int64_t)(uint64_t)n, (int64_t)(uint64_t)d);
     return true;
+}
+
+RELP_HD bool small_div(const Val& x, const Val& y, Val* out) {
+    if (x.n == 0) { *out = val_zero(); return true; }
+    if (y.d == 1 && (y.n == 1 || y.n == -1)) {          // unit pivots (totally unimodular bases)
+        *out = make_small(y.n > 0 ? x.n : -x.n, x.d); return true;
+    }
+    return small_div_general(x, y, out);
 }
 
 RELP_HD int small_cmp(const Val& x, const Val& y) {
@@ -469,19 +480,45 @@ RELP_HDN int big_cmp(const Val& x, const Val& y, const uint32_t* heap) {
 // ------------------------------------------------------------------------------------------
 // Tier-dispatching front ends
 // ------------------------------------------------------------------------------------------
-RELP_HD Val val_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) {
+RELP_HDN Val val_fma_slow(const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) {
     Val out;
-    if (x.d > 0 && a.d > 0 && b.d > 0 && small_fma(x, a, b, s, &out)) return out;
+    if (x.d > 0 && a.d > 0 && b.d > 0) {
+        if (a.n == 0 || b.n == 0) return x;
+        if (small_fma_rational(x, a, b, s, &out)) return out;
+    }
     return big_fma(x, a, b, s, heap, ar);
 }
-RELP_HD Val val_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar) {
+RELP_HD Val val_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) {
+    if (x.d == 1 && a.d == 1 && b.d == 1) {                 // integers: one 128-bit multiply-add
+        i128 t = (i128)a.n * b.n;
+        i128 r = s > 0 ? (i128)x.n + t : (i128)x.n - t;
+        if (r <= RELP_I64_MAX && r >= -RELP_I64_MAX) return make_small((int64_t)r, 1);
+    }
+    return val_fma_slow(x, a, b, s, heap, ar);
+}
+RELP_HDN Val val_div_slow(const Val& x, const Val& y, uint32_t* heap, const Arena& ar) {
     Val out;
-    if (x.d > 0 && y.d > 0 && small_div(x, y, &out)) return out;
+    if (x.d > 0 && y.d > 0 && small_div_general(x, y, &out)) return out;
     return big_div(x, y, heap, ar);
+}
+RELP_HD Val val_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar) {
+    if (x.d > 0 && y.d == 1 && (y.n == 1 || y.n == -1)) return make_small(y.n > 0 ? x.n : -x.n, x.d);
+    if (x.d == 1 && x.n == 0) return x;
+    return val_div_slow(x, y, heap, ar);
 }
 RELP_HD int val_cmp(const Val& x, const Val& y, const uint32_t* heap) {
     if (x.d > 0 && y.d > 0) return small_cmp(x, y);
     return big_cmp(x, y, heap);
+}
+// b / d (d > 0) for COMPARISON only (ratio test, tableau/mod.rs:229): the unreduced fraction
+// (b.n d.d) / (b.d d.n) when it fits -- val_cmp cross-multiplies, it does not need lowest terms, and
+// reducing costs two gcds and four 64-bit divisions per row.  Falls back to the exact division.
+RELP_HD Val val_ratio(const Val& b, const Val& d, uint32_t* heap, const Arena& ar) {
+    if (b.d > 0 && d.d > 0) {
+        i128 n = (i128)b.n * d.d, q = (i128)b.d * d.n;
+        if (n <= RELP_I64_MAX && n >= -RELP_I64_MAX && q <= RELP_I64_MAX) return make_small((int64_t)n, (int64_t)q);
+    }
+    return val_div(b, d, heap, ar);
 }
 
 }  // namespace relp

@@ -92,7 +92,7 @@ struct relp_ctx {
     DBuf<int64_t> xn, xd, zn, zd, an_d, ad_d, cn_d, cd_d, rhsn_d, rhsd_d, dn, dd, pnd, tmpn, tmpd, sell_an, sell_ad;
     DBuf<long long> col_ptr_d, sell_ptr; DBuf<uint32_t> zbits; DBuf<int> row_idx_d, sell_row, basis, art_row, tlist, slist, cost_rows, scratch_i;
     DBuf<unsigned char> in_basis;
-    DBuf<int64_t> rn, rd; DBuf<long long> row_ptr_d; DBuf<int> csr_col, row_art; DBuf<uint32_t> colbits, rowbits, colsum;   // reduced-cost row, nonzero pattern
+    DBuf<int64_t> rn, rd; DBuf<long long> row_ptr_d; DBuf<int4> csr_ent; DBuf<int> row_art; DBuf<uint32_t> colbits, rowbits, colsum; DBuf<unsigned> claim;   // reduced-cost row, nonzero pattern
     size_t wl_cap = 0;
     DBuf<int2> worklist; DBuf<Cand> cand, cand2, gather; DBuf<LogEntry> log; DBuf<unsigned long long> trace;
     int n_slices = 0, a_int = 1, coop_blocks = 0, last_ratio_blocks = 1;
@@ -175,22 +175,23 @@ __global__ void k_csr_scan(int m, long long* row_ptr, long long* cursor) {      
     long long acc = 0;
     for (int i = 0; i <= m; i++) { acc += row_ptr[i]; row_ptr[i] = acc; if (i < m) cursor[i] = acc; }
 }
-__global__ void k_csr_fill(int n, const long long* col_ptr, const int* row_idx, long long* cursor, int* csr_col) {
+__global__ void k_csr_fill(int n, const long long* col_ptr, const int* row_idx, long long* cursor, int4* csr_ent) {
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
         for (long long t = col_ptr[j]; t < col_ptr[j + 1]; t++) {
             long long q = (long long)atomicAdd((unsigned long long*)&cursor[row_idx[t]], 1ull);
-            csr_col[q] = j;
+            csr_ent[q] = make_int4(j, (int)col_ptr[j], (int)col_ptr[j + 1], (int)t);
         }
 }
 
 static int build_csr(relp_ctx* c, long long nnz) {
     int m = c->m, n = c->n;
+    if (nnz >= (1ll << 31)) { set_error("more than 2^31 - 1 matrix entries"); return RELP_ERR_ARGUMENT; }
     DBuf<long long> cursor;
-    if (c->row_ptr_d.alloc(m + 1) || c->csr_col.alloc(nnz) || cursor.alloc(m + 1)) return RELP_ERR_CUDA;
+    if (c->row_ptr_d.alloc(m + 1) || c->csr_ent.alloc(nnz) || cursor.alloc(m + 1)) return RELP_ERR_CUDA;
     CUDA_TRY(cudaMemsetAsync(c->row_ptr_d.p, 0, (size_t)(m + 1) * sizeof(long long), c->stream));
     LAUNCH(c, k_csr_count, clampi((nnz + 255) / 256, 1, c->sm_count * 8), 256, n, c->col_ptr_d.p, c->row_idx_d.p, c->row_ptr_d.p);
     LAUNCH(c, k_csr_scan, 1, 1, m, c->row_ptr_d.p, cursor.p);
-    LAUNCH(c, k_csr_fill, clampi((n + 255) / 256, 1, c->sm_count * 8), 256, n, c->col_ptr_d.p, c->row_idx_d.p, cursor.p, c->csr_col.p);
+    LAUNCH(c, k_csr_fill, clampi((n + 255) / 256, 1, c->sm_count * 8), 256, n, c->col_ptr_d.p, c->row_idx_d.p, cursor.p, c->csr_ent.p);
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     return 0;
 }
@@ -345,8 +346,8 @@ static void wire_dev(relp_ctx* c) {
     D.art_row = c->art_row.p; D.dn = c->dn.p; D.dd = c->dd.p;
     D.pn = c->pnd.p; D.pd = c->pnd.p + (c->m + 1);
     D.tlist = c->tlist.p; D.slist = c->slist.p; D.worklist = c->worklist.p; D.cand = c->cand.p; D.cand2 = c->cand2.p;
-    D.rn = c->rn.p; D.rd = c->rd.p; D.row_ptr = c->row_ptr_d.p; D.csr_col = c->csr_col.p;
-    D.colbits = c->colbits.p; D.rowbits = c->rowbits.p; D.colsum = c->colsum.p; D.row_art = c->row_art.p;
+    D.rn = c->rn.p; D.rd = c->rd.p; D.row_ptr = c->row_ptr_d.p; D.csr_ent = c->csr_ent.p;
+    D.colbits = c->colbits.p; D.rowbits = c->rowbits.p; D.colsum = c->colsum.p; D.claim = c->claim.p; D.row_art = c->row_art.p;
     D.gather = c->gather.p; D.log = c->log.p; D.log_cap = (long long)c->log.n; D.trace = c->trace.p; D.zbits = c->zbits.p;
 }
 
@@ -362,6 +363,8 @@ static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
     if (c->pnd.alloc(2 * (size_t)(m + 1))) return RELP_ERR_CUDA;
     if (c->basis.alloc(m) || c->art_row.alloc(m) || c->tlist.alloc(c->mloc + 1) || c->slist.alloc(m + 1)) return RELP_ERR_CUDA;
     if (c->cost_rows.alloc(c->mloc + 1) || c->scratch_i.alloc(2 * (size_t)(m + 2))) return RELP_ERR_CUDA;
+    if (c->claim.alloc(c->n)) return RELP_ERR_CUDA;
+    CUDA_TRY(cudaMemsetAsync(c->claim.p, 0, (size_t)c->n * sizeof(unsigned), c->stream));
     if (c->rn.alloc(ncols_max) || c->rd.alloc(ncols_max) || c->row_art.alloc(m) ||
         c->colbits.alloc((size_t)(m + 1) * (c->ld / 32) + 2) || c->rowbits.alloc((size_t)c->ld * ((m + 32) / 32) + 4) ||
         c->colsum.alloc((size_t)(m + 1) * ((c->ld / 32 + 31) / 32) + 2)) return RELP_ERR_CUDA;
@@ -1031,6 +1034,7 @@ int relp_set_option(relp_ctx* c, const char* name, int64_t value) {
     if (!c || !name) return RELP_ERR_ARGUMENT;
     if (!strcmp(name, "persistent")) { c->use_persistent = value != 0; return RELP_OK; }
     if (!strcmp(name, "narrow")) { c->use_narrow = value != 0; return RELP_OK; }
+    if (!strcmp(name, "coop_blocks")) { c->coop_blocks = (int)value; return RELP_OK; }   // debug: CTAs of the persistent kernel
     if (!strcmp(name, "trace")) {      // debug: per-CTA barrier arrival times of the last iteration
         if (value) { if (c->trace.alloc(16 * 4096)) return RELP_ERR_CUDA; cudaMemset(c->trace.p, 0, 16 * 4096 * 8); }
         else c->trace.release();

@@ -97,7 +97,8 @@ struct Dev {
     uint32_t* zbits;                          // bit i set <=> -pi_i != 0 (maintained with the cost row)
     // Reduced-cost row, kept by the persistent loop (see stage_update_rc): one rational per tableau column
     int64_t* rn; int64_t* rd;
-    const long long* row_ptr; const int* csr_col;   // CSR pattern of A: which columns does a row touch
+    const long long* row_ptr; const int4* csr_ent;  // CSR copy of A's pattern: per entry (column, its CSC start, CSC end, CSC position of this entry)
+    unsigned* claim;                          // per provider column: ticket of the last reduced-cost update round that took it
     // Nonzero pattern of the Carry block, kept with it (stage_update): colbits word (k, li / 32) has bit
     // li % 32 set <=> X[li][k] != 0 (column generation tests 32 rows of a B^-1 column with one word);
     // rowbits word (li, k / 32) is the transpose (the pivot row's nonzero columns come from one
@@ -199,29 +200,37 @@ __device__ __forceinline__ Cand cand_shfl(const Cand& c, int delta) {
 }
 
 // Block-wide argmin; the result is returned to EVERY thread of the block.
-__device__ Cand block_argmin(Cand best, int mode, const uint32_t* heap) {
-    __shared__ Cand sh[RELP_MAXWARPS];
-    __shared__ Cand winner;
-    for (int d = 16; d > 0; d >>= 1) {
-        Cand o = cand_shfl(best, d);
-        if (cand_better(o, best, mode, heap)) best = o;
-    }
-    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    if (lane == 0) sh[w] = best;
-    __syncthreads();
-    if (w == 0) {
-        int nw = (blockDim.x + 31) >> 5;
-        if (lane < nw) best = sh[lane]; else best = cand_none();
+// Warp argmin, result in every lane.  Most warps hold no candidate at all (a few thousand reduced
+// costs of 200 000 are negative) or a single one: both cases are settled by one ballot.
+__device__ __forceinline__ Cand warp_argmin(Cand best, int mode, const uint32_t* heap) {
+#ifndef RELP_EMUL
+    const unsigned have = __ballot_sync(0xffffffffu, best.idx >= 0);
+    if (have == 0) return best;
+    if ((have & (have - 1)) != 0) {
         for (int d = 16; d > 0; d >>= 1) {
             Cand o = cand_shfl(best, d);
             if (cand_better(o, best, mode, heap)) best = o;
         }
-        if (lane == 0) winner = best;
     }
-    __syncthreads();
-    best = winner;
-    __syncthreads();
+    const int src = (have & (have - 1)) != 0 ? 0 : ctz32(have);
+    best.v.n = __shfl_sync(0xffffffffu, best.v.n, src); best.v.d = __shfl_sync(0xffffffffu, best.v.d, src);
+    best.key = __shfl_sync(0xffffffffu, best.key, src); best.idx = __shfl_sync(0xffffffffu, best.idx, src);
+#endif
     return best;
+}
+
+// Block-wide argmin; the result is returned to EVERY thread of the block.  Two block barriers: the
+// warp winners go through shared memory and every warp reduces them again for itself.
+__device__ Cand block_argmin(Cand best, int mode, const uint32_t* heap) {
+    __shared__ Cand sh[RELP_MAXWARPS];
+    best = warp_argmin(best, mode, heap);
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    __syncthreads();                      // the previous call's readers are done with sh
+    if (lane == 0) sh[w] = best;
+    __syncthreads();
+    int nw = (blockDim.x + 31) >> 5;
+    if (lane < nw) best = sh[lane]; else best = cand_none();
+    return warp_argmin(best, mode, heap);
 }
 
 // Reduce `count` candidates of `src` (every block can do this redundantly: same input, same
@@ -417,31 +426,32 @@ __device__ void stage_select_rc(const Dev& D, const Grid& g, const Inv& I, int m
 // from the other end of the grid.
 // rc_jj -= rc * (p . A_jj), done by the caller that came from the SMALLEST row k with p_k != 0 in
 // column jj (`from_k`), so a column touched from several rows is updated exactly once, no atomics.
-__device__ __forceinline__ void rc_column_update(const Dev& D, int jj, int from_k, const Val& rc, int off, const uint32_t* pbits, const Arena& ar) {
+// `ent` = (jj, CSC start, CSC end) from the CSR copy, so the chain is csr_ent -> row indices (all of a
+// segment of RELP_RCH requested together) -> values of the hits.
+#ifndef RELP_RCH
+#define RELP_RCH 24
+#endif
+__device__ __forceinline__ void rc_column_update(const Dev& D, const int4& ent, int from_k, const Val& rc, int off, const uint32_t* pbits, const Arena& ar) {
+    const int jj = ent.x;
     Val old = ld_val(D.rn, D.rd, off + jj);            // requested early, used last
-    const long long t0 = D.col_ptr[jj], t1 = D.col_ptr[jj + 1];
     Val alpha = val_zero();
     int first = 0x7fffffff;
-    for (long long seg = t0; seg < t1; seg += 32) {
-        const int wseg = t1 - seg < 32 ? (int)(t1 - seg) : 32;
+    for (int seg = ent.y; seg < ent.z; seg += RELP_RCH) {
+        const int wseg = ent.z - seg < RELP_RCH ? ent.z - seg : RELP_RCH;
+        int kk[RELP_RCH];
+#pragma unroll
+        for (int u = 0; u < RELP_RCH; u++) kk[u] = u < wseg ? D.row_idx[seg + u] + 1 : -1;
         unsigned hits = 0;
-        for (int t = 0; t < wseg; t += RELP_CHG) {
-            int kk[RELP_CHG]; uint32_t ww[RELP_CHG];
 #pragma unroll
-            for (int u = 0; u < RELP_CHG; u++) kk[u] = t + u < wseg ? D.row_idx[seg + t + u] + 1 : -1;
-#pragma unroll
-            for (int u = 0; u < RELP_CHG; u++) ww[u] = kk[u] >= 0 ? pbits[kk[u] >> 5] : 0u;
-#pragma unroll
-            for (int u = 0; u < RELP_CHG; u++) if (kk[u] >= 0 && ((ww[u] >> (kk[u] & 31)) & 1u)) {
-                hits |= 1u << (t + u);
-                if (kk[u] < first) first = kk[u];
-            }
+        for (int u = 0; u < RELP_RCH; u++) if (kk[u] >= 0 && ((pbits[kk[u] >> 5] >> (kk[u] & 31)) & 1u)) {
+            hits |= 1u << u;
+            if (kk[u] < first) first = kk[u];
         }
         if (first < from_k) return;                    // another caller owns this column
         while (hits) {
-            int t = ctz32(hits); hits &= hits - 1;
-            int kk = D.row_idx[seg + t] + 1;
-            alpha = val_fma(alpha, ld_val(D.pn, D.pd, kk), make_small(D.an[seg + t], D.ad[seg + t]), 1, D.heap, ar);
+            int u = ctz32(hits); hits &= hits - 1;
+            int k = D.row_idx[seg + u] + 1;
+            alpha = val_fma(alpha, ld_val(D.pn, D.pd, k), make_small(D.an[seg + u], D.ad[seg + u]), 1, D.heap, ar);
         }
     }
     if (first == from_k && alpha.n != 0)
@@ -457,7 +467,7 @@ __device__ __forceinline__ void rc_sparse_row(const Dev& D, const Inv& I, int s,
         if (a >= 0) st_val(D.rn, D.rd, a, val_fma(ld_val(D.rn, D.rd, a), rc, ld_val(D.pn, D.pd, k), -1, D.heap, ar));
     }
     const long long lo = D.row_ptr[k - 1], hi = D.row_ptr[k];
-    for (long long e = lo + threadIdx.x; e < hi; e += blockDim.x) rc_column_update(D, D.csr_col[e], k, rc, off, pbits, ar);
+    for (long long e = lo + threadIdx.x; e < hi; e += blockDim.x) rc_column_update(D, D.csr_ent[e], k, rc, off, pbits, ar);
 }
 
 #ifndef RELP_RC_SPARSE_S
@@ -568,7 +578,7 @@ __device__ __forceinline__ void gen_row_done(const Dev& D, const Inv& I, int li,
     if (acc.n == 0) return;
     int p = list_append(t_counter); D.tlist[p] = li;
     if (val_sign(acc, D.heap) > 0) {
-        Cand c; c.v = val_div(ld_val(D.xn, D.xd, li), acc, D.heap, ar);
+        Cand c; c.v = val_ratio(ld_val(D.xn, D.xd, li), acc, D.heap, ar);
         c.idx = I.row_lo + li; c.key = D.basis[I.row_lo + li];
         if (cand_better(c, best, ARG_RATIO, D.heap)) best = c;
     }
@@ -895,14 +905,17 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
     Cand best = cand_none();
     for (int q = warp; q < sm.nblk; q += nwarps) {
         const int rb = sm.blk[q], li = rb * 32 + lane;
+        // b_i and the row's basis column are requested before the column is generated: only rows with
+        // d_i > 0 need them, but asking now takes a round trip off the critical path
+        Val bv = val_zero(); int key = 0;
+        if (li < I.mloc) { bv = ld_val(D.xn, D.xd, li); key = D.basis[I.row_lo + li]; }
         Val acc = gen_rows_block(D, I, c.unit_row, sm.ent, nent, D.an + c.t0, D.ad + c.t0, rb, lane, tr);
         if (li < I.mloc && acc.n != 0) {
-            Val bv = ld_val(D.xn, D.xd, li); int key = D.basis[I.row_lo + li];
             st_val(D.dn, D.dd, li, acc);
             int t = list_append(&sm.T);
             if (t < RELP_NARROW_T) { sm.tl[t] = li; sm.dv[t] = acc; D.tlist[t] = li; }
             if (val_sign(acc, D.heap) > 0) {
-                Cand cd; cd.v = val_div(bv, acc, D.heap, tr); cd.idx = I.row_lo + li; cd.key = key;
+                Cand cd; cd.v = val_ratio(bv, acc, D.heap, tr); cd.idx = I.row_lo + li; cd.key = key;
                 if (cand_better(cd, best, ARG_RATIO, D.heap)) best = cd;
             }
         }
@@ -959,11 +972,12 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
     }
     __syncthreads();
     NT(5);
-    // one item space for the whole CTA: Carry elements, cost row, artificial and structural reduced costs
+    // one item space for the whole CTA: Carry elements, cost row, artificial reduced costs ...
     const int off = I.phase == 1 ? I.nr_art : 0;
     const int n_carry = T * S, n_cost = rc.n != 0 ? S : 0, n_art = (rc.n != 0 && rc_sparse && I.phase == 1) ? S : 0;
     const int n_rc = (rc.n != 0 && rc_sparse) ? W : 0;
-    const int total = n_carry + n_cost + n_art + n_rc;
+    const int total = n_carry + n_cost + n_art;
+    if (tid == nt - 1) pivot_bookkeeping(D, j, r, T, S, sm.b_nz, rc, 1);
     for (int w = tid; w < total; w += nt) {
         int it = w;
         if (it < n_carry) {
@@ -974,18 +988,45 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
         it -= n_carry;
         if (it < n_cost) { cost_row_update(D, sm.sl[it], rc, sm.pv[it], ar); continue; }
         it -= n_cost;
-        if (it < n_art) {          // artificial column e_i (cost one): p . e_i = p_k
-            int k = sm.sl[it];
-            int a = k > 0 ? D.row_art[k - 1] : -1;
-            if (a >= 0) st_val(D.rn, D.rd, a, val_fma(ld_val(D.rn, D.rd, a), rc, sm.pv[it], -1, D.heap, ar));
-            continue;
-        }
-        it -= n_art;
-        int q = 0;
-        while (q + 1 < S && sm.pre[q + 1] <= it) q++;
-        rc_column_update(D, D.csr_col[sm.plo[q] + (it - sm.pre[q])], sm.sl[q], rc, off, sm.pb, ar);
+        int k = sm.sl[it];         // artificial column e_i (cost one): p . e_i = p_k
+        int a = k > 0 ? D.row_art[k - 1] : -1;
+        if (a >= 0) st_val(D.rn, D.rd, a, val_fma(ld_val(D.rn, D.rd, a), rc, sm.pv[it], -1, D.heap, ar));
     }
-    if (tid == nt - 1) pivot_bookkeeping(D, j, r, T, S, sm.b_nz, rc, 1);
+    // ... and the structural reduced costs: one thread per entry (k - 1, jj) of the rows of A behind the
+    // nonzero p_k, each holding its own term p_k a_kj.  A column met from several rows is taken by one
+    // thread per round (ticket exchange on claim[jj]); the others retry in the next round, after the
+    // block barrier, so the read-modify-write of rc_jj is never concurrent.  Exact arithmetic makes the
+    // order of the terms irrelevant.
+    {
+        const unsigned base = ((unsigned)st->iter + 1u) << 10;
+        unsigned rid = 0;
+        for (int w0 = 0; w0 < n_rc; w0 += nt) {
+            const int it = w0 + tid;
+            bool pending = it < n_rc;
+            int jj = 0; Val term = val_zero(), old = val_zero();
+            if (pending) {
+                int q = 0;
+                while (q + 1 < S && sm.pre[q + 1] <= it) q++;
+                const int4 ent = D.csr_ent[sm.plo[q] + (it - sm.pre[q])];
+                jj = ent.x;
+                old = ld_val(D.rn, D.rd, off + jj);
+                term = val_fma(val_zero(), sm.pv[q], make_small(D.an[ent.w], I.a_int ? 1 : D.ad[ent.w]), 1, D.heap, ar);
+            }
+            bool first_round = true;
+            while (__syncthreads_or(pending)) {
+                if (pending) {
+                    const unsigned ticket = base + rid;
+                    if (atomicExch(&D.claim[jj], ticket) != ticket) {
+                        if (!first_round) old = ld_val(D.rn, D.rd, off + jj);
+                        st_val(D.rn, D.rd, off + jj, val_fma(old, rc, term, -1, D.heap, ar));
+                        pending = false;
+                    }
+                }
+                first_round = false;
+                rid++;
+            }
+        }
+    }
     NT(6);
     if (rc.n != 0 && !rc_sparse) stage_update_rc(D, g0, I, r, rc, smem_words);
     __syncthreads();
@@ -1030,14 +1071,15 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
         }
         unsigned long long t1 = gtime();
         TRACE(2);
-        Cand col = reduce_candidates(D.cand, g.nb, mode, D.heap);      // same winner in every CTA
-        if (g.tid == 0) commit_column(st, col, rule);
-        if (col.idx < 0) break;
+        Cand col = cand_none();
         unsigned long long t2 = t1, t3 = t1, t4 = t1;
 #ifndef RELP_EMUL
         if (use_narrow) {
+            // only CTA 0 needs the entering column now; the others learn it after the next barrier
             if (g.bid == 0) {
-                int verdict = narrow_iteration(D, I, col, smem_words);
+                col = reduce_candidates(D.cand, g.nb, mode, D.heap);
+                if (g.tid == 0) commit_column(st, col, rule);
+                int verdict = col.idx < 0 ? 2 : narrow_iteration(D, I, col, smem_words);
                 if (threadIdx.x == 0) {
                     st->narrow_verdict = verdict;
                     if (verdict == 0) { t2 = t3 = t4 = gtime(); }
@@ -1058,9 +1100,15 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
                 }
                 continue;
             }
+            if (g.bid != 0) { col.idx = st->j; col.v = st->rc; col.key = 0; }
             // verdict 1: nothing was modified; the whole grid redoes this iteration
-        }
+        } else
 #endif
+        {
+            col = reduce_candidates(D.cand, g.nb, mode, D.heap);      // same winner in every CTA
+            if (g.tid == 0) commit_column(st, col, rule);
+            if (col.idx < 0) break;
+        }
         TRACE(3);
         stage_gen_column(D, g, I, col.idx);
         GRID_SYNC();

@@ -23,6 +23,8 @@ struct emul_dim3 { unsigned x, y, z; };
 static emul_dim3 blockIdx = {0, 0, 0}, threadIdx = {0, 0, 0}, blockDim = {1, 1, 1}, gridDim = {1, 1, 1};
 struct int2 { int x, y; };
 static inline int2 make_int2(int x, int y) { int2 r; r.x = x; r.y = y; return r; }
+struct int4 { int x, y, z, w; };
+static inline int4 make_int4(int x, int y, int z, int w) { int4 r; r.x = x; r.y = y; r.z = z; r.w = w; return r; }
 
 template <typename T> static inline T atomicAdd(T* p, T v) { T o = *p; *p += v; return o; }
 static inline int atomicOr(int* p, int v) { int o = *p; *p |= v; return o; }
