@@ -109,12 +109,22 @@ def _p(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None else None
 
 
+_from_coprime = getattr(Fr, "_from_coprime_ints", None)     # Python >= 3.12: no gcd when the pair is known reduced
+
+
 def decode_rats(num, den, limbs):
-    """Rat array (see relp_b200.h) -> list of Fraction.  Asserts canonical form."""
+    """Rat array (see relp_b200.h) -> list of Fraction.  Asserts canonical form (lowest terms,
+    positive denominator): the gcds of the int64 tier are checked in one numpy call."""
+    num = np.asarray(num, np.int64); den = np.asarray(den, np.int64)
+    small = den > 0
+    if small.any():
+        g = np.gcd(np.abs(num[small]), den[small])
+        assert bool(np.all((g == 1) | ((num[small] == 0) & (den[small] == 1)))), "device returned a non-canonical rational"
     out = []
+    mk = _from_coprime if _from_coprime is not None else Fr
     for n, d in zip(num.tolist(), den.tolist()):
         if d > 0:
-            out.append(Fr(n, d))
+            out.append(mk(n, d))
             continue
         assert d == 0, "absent value crossed the boundary"
         h = int(limbs[n]); nn = h & 0x3fff; nd = (h >> 14) & 0x3fff
@@ -275,7 +285,7 @@ class Carry:
         per = (m + self.world - 1) // self.world
         return min(m, self.rank * per)
 
-    def _read(self, fn, count, *args):
+    def _read_raw(self, fn, count, *args):
         n = np.zeros(max(count, 1), np.int64); d = np.zeros(max(count, 1), np.int64)
         while True:
             limbs = np.zeros(self._limb_cap, np.uint32)
@@ -285,7 +295,10 @@ class Carry:
                 self._limb_cap = int(used.value) * 2
                 continue
             self._chk(st)
-            return decode_rats(n[:count], d[:count], limbs)
+            return n[:count], d[:count], limbs
+
+    def _read(self, fn, count, *args):
+        return decode_rats(*self._read_raw(fn, count, *args))
 
     def basis_indices(self):
         out = np.zeros(self.m, np.int32)
@@ -315,10 +328,13 @@ class Carry:
 
     def current_bfs(self):
         """carry/mod.rs:616-625: (basis column, value) for b_i != 0, sorted by column."""
-        b = self.b(); basis = self.basis_indices()
-        t = [(int(basis[self.row_lo + i]), v) for i, v in enumerate(b) if v != 0]
-        t.sort(key=lambda x: x[0])
-        return t
+        n, d, limbs = self._read_raw(self.L.relp_read_b, self.mloc)
+        basis = self.basis_indices()
+        nz = np.nonzero((n != 0) | (d == 0))[0]    # d == 0: multi-limb value (exported handles start at 0), never zero
+        vals = decode_rats(n[nz], d[nz], limbs)
+        cols = basis[self.row_lo + nz]
+        order = np.argsort(cols, kind="stable")
+        return [(int(cols[i]), vals[i]) for i in order]
 
     def log(self):
         n = self.L.relp_log_size(self.h)

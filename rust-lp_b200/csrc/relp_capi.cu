@@ -170,10 +170,18 @@ __global__ void k_csr_count(int n, const long long* col_ptr, const int* row_idx,
     for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < nnz; t += (long long)gridDim.x * blockDim.x)
         atomicAdd((unsigned long long*)&row_ptr[row_idx[t] + 1], 1ull);
 }
-__global__ void k_csr_scan(int m, long long* row_ptr, long long* cursor) {      // m is small next to nnz: one thread
-    if (blockIdx.x != 0 || threadIdx.x != 0) return;
-    long long acc = 0;
-    for (int i = 0; i <= m; i++) { acc += row_ptr[i]; row_ptr[i] = acc; if (i < m) cursor[i] = acc; }
+__global__ void k_csr_scan(int m, long long* row_ptr, long long* cursor) {      // one block: chunk sums, then chunk prefixes
+    __shared__ long long part[1024];
+    const int nt = blockDim.x, t = threadIdx.x;
+    const int per = (m + 1 + nt - 1) / nt, lo = t * per, hi = lo + per < m + 1 ? lo + per : m + 1;
+    long long sum = 0;
+    for (int i = lo; i < hi; i++) sum += row_ptr[i];
+    part[t] = sum;
+    __syncthreads();
+    if (t == 0) { long long acc = 0; for (int q = 0; q < nt; q++) { long long v = part[q]; part[q] = acc; acc += v; } }
+    __syncthreads();
+    long long acc = part[t];
+    for (int i = lo; i < hi; i++) { acc += row_ptr[i]; row_ptr[i] = acc; if (i < m) cursor[i] = acc; }
 }
 __global__ void k_csr_fill(int n, const long long* col_ptr, const int* row_idx, long long* cursor, int4* csr_ent) {
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
@@ -190,7 +198,7 @@ static int build_csr(relp_ctx* c, long long nnz) {
     if (c->row_ptr_d.alloc(m + 1) || c->csr_ent.alloc(nnz) || cursor.alloc(m + 1)) return RELP_ERR_CUDA;
     CUDA_TRY(cudaMemsetAsync(c->row_ptr_d.p, 0, (size_t)(m + 1) * sizeof(long long), c->stream));
     LAUNCH(c, k_csr_count, clampi((nnz + 255) / 256, 1, c->sm_count * 8), 256, n, c->col_ptr_d.p, c->row_idx_d.p, c->row_ptr_d.p);
-    LAUNCH(c, k_csr_scan, 1, 1, m, c->row_ptr_d.p, cursor.p);
+    LAUNCH(c, k_csr_scan, 1, 1024, m, c->row_ptr_d.p, cursor.p);
     LAUNCH(c, k_csr_fill, clampi((n + 255) / 256, 1, c->sm_count * 8), 256, n, c->col_ptr_d.p, c->row_idx_d.p, cursor.p, c->csr_ent.p);
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     return 0;
@@ -595,8 +603,11 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     }
     wire_dev(c);
     LAUNCH(c, k_init_planes, c->sm_count * 8, RELP_THREADS, c->D, c->rhsn_d.p, c->rhsd_d.p);
-    LAUNCH(c, k_build_pattern, c->sm_count * 8, RELP_THREADS, c->D);
-    LAUNCH(c, k_init_cost_row_artificial, 1, 1, c->D, c->rhsn_d.p, c->rhsd_d.p);
+    CUDA_TRY(cudaMemsetAsync(c->colbits.p, 0, ((size_t)(m + 1) * (c->ld / 32)) * 4, c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->rowbits.p, 0, ((size_t)c->ld * ((m + 32) / 32)) * 4, c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->colsum.p, 0, ((size_t)(m + 1) * ((c->ld / 32 + 31) / 32)) * 4, c->stream));
+    LAUNCH(c, k_init_pattern, grid_for(c, c->mloc), RELP_THREADS, c->D, c->rhsn_d.p);
+    LAUNCH(c, k_init_cost_row_artificial, grid_for(c, m), RELP_THREADS, c->D, c->rhsn_d.p, c->rhsd_d.p);
     LAUNCH(c, k_build_zbits, grid_for(c, (m + 31) / 32), RELP_THREADS, c->D);
     if (check_cuda(c)) return RELP_ERR_CUDA;
     CUDA_TRY(cudaStreamSynchronize(c->stream));

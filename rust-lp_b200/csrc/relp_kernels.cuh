@@ -1242,18 +1242,40 @@ __global__ void k_build_pattern(Dev D) {
     }
 }
 
+// Pattern of the initial planes (B^-1 = I, b = rhs) without reading them back: the bitmaps are zeroed by
+// the host and this kernel sets one bit per row in each (plus the b column's).
+__global__ void k_init_pattern(Dev D, const int64_t* rhs_n) {
+    DState* st = D.st;
+    const int wpc = st->ld >> 5, wpr = (st->m + 32) >> 5, wsc = (wpc + 31) >> 5;
+    for (int li = blockIdx.x * blockDim.x + threadIdx.x; li < st->mloc; li += gridDim.x * blockDim.x) {
+        const int k = st->row_lo + li + 1;
+        uint32_t rowword0 = 0;
+        atomicOr(&D.colbits[(size_t)k * wpc + (li >> 5)], 1u << (li & 31));
+        atomicOr(&D.colsum[(size_t)k * wsc + (li >> 10)], 1u << ((li >> 5) & 31));
+        if (rhs_n[st->row_lo + li] != 0) {
+            atomicOr(&D.colbits[li >> 5], 1u << (li & 31));
+            atomicOr(&D.colsum[li >> 10], 1u << ((li >> 5) & 31));
+            rowword0 = 1u;
+        }
+        if ((k >> 5) == 0) D.rowbits[(size_t)li * wpr] = rowword0 | (1u << k);
+        else { D.rowbits[(size_t)li * wpr] = rowword0; D.rowbits[(size_t)li * wpr + (k >> 5)] = 1u << (k & 31); }
+    }
+}
+
 // cost row of the artificial tableau: -pi_i = -1 on artificial rows, -obj = -sum of their b_i
 __global__ void k_init_cost_row_artificial(Dev D, const int64_t* rhs_n, const int64_t* rhs_d) {
     DState* st = D.st;
+    // -pi: -1 on artificial rows, 0 elsewhere (every thread); -obj: exact sum, one thread
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < st->m; i += gridDim.x * blockDim.x) {
+        D.zn[1 + i] = D.row_art[i] >= 0 ? -1 : 0; D.zd[1 + i] = 1;
+    }
     if (blockIdx.x != 0 || threadIdx.x != 0) return;
     Arena ar = persistent(D);
-    for (int k = 0; k <= st->m; k++) { D.zn[k] = 0; D.zd[k] = 1; }
     Val acc = val_zero();
     Val one = make_small(1, 1);
     for (int a = 0; a < st->nr_art; a++) {
         int i = D.art_row[a];
         acc = val_fma(acc, make_small(rhs_n[i], rhs_d[i]), one, -1, D.heap, ar);
-        D.zn[1 + i] = -1; D.zd[1 + i] = 1;
     }
     st_val(D.zn, D.zd, 0, acc);
 }
