@@ -61,6 +61,7 @@ struct DState {
     int W;                         // sum of the CSR row lengths over the pivot row's nonzero columns
     int wl_cap;                    // capacity of the escalation worklist
     int narrow_verdict;            // persistent loop: outcome of CTA 0's attempt at the current iteration
+    int narrow_skip, narrow_backoff;   // after a pivot that was too big for one CTA, do not try again for a while
     unsigned long long narrow_done;   // iterations completed by CTA 0 alone
     unsigned long long iter, iter_limit;
     unsigned long long pool_top, pool_limit, pool_base;   // active persistent region of the limb heap
@@ -646,20 +647,18 @@ __device__ void stage_pivot_row(const Dev& D, const Grid& g, const Inv& I, int r
         }
         return;
     }
-    // the row's nonzero columns come from its row of rowbits: (m + 1) / 32 contiguous words
+    // the row's nonzero columns come from its row of rowbits ((m + 1) / 32 contiguous words; a warp shares
+    // one word); one thread per nonzero column, so a dense row of multi-limb entries is divided in parallel
     const uint32_t* rb = D.rowbits + (size_t)lr * I.wpr;
     int len = 0;
-    for (int w = g.tid; w < I.wpr; w += g.nth) {
-        uint32_t bits = rb[w];
-        while (bits) {
-            int k = w * 32 + ctz32(bits); bits &= bits - 1;
-            size_t e = (size_t)k * ld + lr;
-            Val p = val_div(ld_val(D.xn, D.xd, e), pivot, D.heap, ar);
-            st_val(D.xn, D.xd, e, p);
-            st_val(D.pn, D.pd, k, p);
-            int s = list_append(&st->S); D.slist[s] = k;
-            if (k > 0) len += (int)(D.row_ptr[k] - D.row_ptr[k - 1]);
-        }
+    for (int k = g.tid; k <= I.m; k += g.nth) {
+        if (!((rb[k >> 5] >> (k & 31)) & 1u)) continue;
+        size_t e = (size_t)k * ld + lr;
+        Val p = val_div(ld_val(D.xn, D.xd, e), pivot, D.heap, ar);
+        st_val(D.xn, D.xd, e, p);
+        st_val(D.pn, D.pd, k, p);
+        int s = list_append(&st->S); D.slist[s] = k;
+        if (k > 0) len += (int)(D.row_ptr[k] - D.row_ptr[k - 1]);
     }
     if (len) atomicAdd(&st->W, len);
 }
@@ -935,26 +934,32 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
     Arena ar = persistent(D);
     const uint32_t* rbits = D.rowbits + (size_t)lr * I.wpr;
     const size_t ld = I.ld;
-    for (int w = tid; w < I.wpr; w += nt) {
+    for (int w = tid; w < I.wpr; w += nt) {          // the row's nonzero columns first: nothing is divided for a row that is too long
         uint32_t bits = rbits[w];
         sm.pb[w] = bits;
         while (bits) {
             int k = w * 32 + ctz32(bits); bits &= bits - 1;
-            Val x = ld_val(D.xn, D.xd, (size_t)k * ld + lr);
-            long long lo = k > 0 ? D.row_ptr[k - 1] : 0, hi = k > 0 ? D.row_ptr[k] : 0;
-            Val p = val_div(x, pivot, D.heap, ar);
             int q = atomicAdd(&sm.S, 1);
-            if (q < RELP_NARROW_S) { sm.sl[q] = k; sm.pv[q] = p; sm.plo[q] = lo; sm.pre[q] = (int)(hi - lo); }
-            atomicAdd(&sm.W, (int)(hi - lo));
-            if (k == 0) sm.b_nz = 1;
+            if (q < RELP_NARROW_S) sm.sl[q] = k;
         }
     }
     __syncthreads();
-    const int S = sm.S, W = sm.W;
+    const int S = sm.S;
+    if (S > RELP_NARROW_S || (long long)T * S > RELP_NARROW_TS) return 1;
+    for (int q = tid; q < S; q += nt) {               // one thread per nonzero column
+        const int k = sm.sl[q];
+        Val x = ld_val(D.xn, D.xd, (size_t)k * ld + lr);
+        long long lo = k > 0 ? D.row_ptr[k - 1] : 0, hi = k > 0 ? D.row_ptr[k] : 0;
+        sm.pv[q] = val_div(x, pivot, D.heap, ar);
+        sm.plo[q] = lo; sm.pre[q] = (int)(hi - lo);
+        atomicAdd(&sm.W, (int)(hi - lo));
+        if (k == 0) sm.b_nz = 1;
+    }
+    __syncthreads();
+    const int W = sm.W;
     const long long nnz = D.col_ptr[I.n];
     const bool rc_sparse = S <= RELP_RC_SPARSE_S && (long long)W * 32 <= nnz + 1024;
-    if (S > RELP_NARROW_S || (long long)T * S > RELP_NARROW_TS ||
-        (rc.n != 0 && (rc_sparse ? W > RELP_NARROW_W : (I.sl_hi - I.sl_lo) > 256))) return 1;
+    if (rc.n != 0 && (rc_sparse ? W > RELP_NARROW_W : (I.sl_hi - I.sl_lo) > 256)) return 1;
     NT(4);
     // (d) commit: row r in place and in the pivot-row buffer, then everything that depends on p
     if (tid == 0) {
@@ -1072,9 +1077,10 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
         unsigned long long t1 = gtime();
         TRACE(2);
         Cand col = cand_none();
+        bool narrow_failed = false;
         unsigned long long t2 = t1, t3 = t1, t4 = t1;
 #ifndef RELP_EMUL
-        if (use_narrow) {
+        if (use_narrow && st->narrow_skip == 0) {
             // only CTA 0 needs the entering column now; the others learn it after the next barrier
             if (g.bid == 0) {
                 col = reduce_candidates(D.cand, g.nb, mode, D.heap);
@@ -1092,7 +1098,7 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
             if (verdict == 2) break;
             if (verdict == 0) {
                 if (g.tid == 0) {
-                    st->narrow_done++;
+                    st->narrow_done++; st->narrow_backoff = 0;
                     end_of_iteration(D);
                     unsigned long long t5 = gtime();
                     st->stage_ns[0] += t1 - t0; st->stage_ns[5] += t4 - t1; st->stage_ns[4] += t5 - t4;
@@ -1101,6 +1107,7 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
                 continue;
             }
             if (g.bid != 0) { col.idx = st->j; col.v = st->rc; col.key = 0; }
+            narrow_failed = true;
             // verdict 1: nothing was modified; the whole grid redoes this iteration
         } else
 #endif
@@ -1133,6 +1140,10 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
             GRID_SYNC();
         }
         if (g.tid == 0) {
+            if (narrow_failed) {           // too big for one CTA: stay wide for a while, longer each time
+                int bo = st->narrow_backoff ? st->narrow_backoff * 2 : 2;
+                st->narrow_backoff = bo > 64 ? 64 : bo; st->narrow_skip = st->narrow_backoff;
+            } else if (st->narrow_skip > 0) st->narrow_skip--;
             end_of_iteration(D);
             unsigned long long t5 = gtime();
             st->stage_ns[0] += t1 - t0; st->stage_ns[1] += t2 - t1; st->stage_ns[2] += t3 - t2;
