@@ -270,18 +270,49 @@ RELP_HD int mag_shl(uint32_t* a, int n, int s) {
     return mag_trim(a, n);
 }
 
-// Binary GCD of two nonzero magnitudes; destroys both buffers; *res points at the buffer (u or
-// v) holding the result; returns its limb count.  Buffers need one spare limb for the final shift
-// beyond max(nu, nv).
+RELP_HD uint64_t mag_lo64(const uint32_t* a, int n) { return n == 0 ? 0 : (n == 1 ? (uint64_t)a[0] : ((uint64_t)a[1] << 32) | a[0]); }
+// u mod v for a 64-bit v != 0
+RELP_HD uint64_t mag_mod64(const uint32_t* u, int nu, uint64_t v) {
+    if (v >> 32 == 0) {                       // 32-bit divisor: 64-bit steps
+        uint64_t r = 0;
+        for (int i = nu - 1; i >= 0; i--) r = ((r << 32) | u[i]) % v;
+        return r;
+    }
+    u128 r = 0;
+    for (int i = nu - 1; i >= 0; i--) r = ((r << 32) | u[i]) % v;
+    return (uint64_t)r;
+}
+RELP_HD int mag_set64(uint32_t* a, uint64_t x) { a[0] = (uint32_t)x; a[1] = (uint32_t)(x >> 32); return a[1] ? 2 : (a[0] ? 1 : 0); }
+
+// GCD of two nonzero magnitudes; destroys both buffers; *res points at the buffer (u or v) holding the
+// result; returns its limb count.  Buffers need one spare limb beyond max(nu, nv) and at least 2 limbs.
+// As soon as one operand fits 64 bits the other is reduced modulo it and the rest is a 64-bit gcd;
+// above that, binary GCD (subtract, strip trailing zeros).
 RELP_HD int mag_gcd(uint32_t* u, int nu, uint32_t* v, int nv, uint32_t** res) {
+    if (nu <= 2 || nv <= 2) {
+        if (nv > nu) { uint32_t* t = u; u = v; v = t; int ti = nu; nu = nv; nv = ti; }
+        uint64_t b = mag_lo64(v, nv);
+        uint64_t a = nu <= 2 ? mag_lo64(u, nu) : mag_mod64(u, nu, b);
+        *res = u;
+        return mag_set64(u, gcd64(a, b));
+    }
     int zu = mag_ctz(u, nu), zv = mag_ctz(v, nv);
     int sh = zu < zv ? zu : zv;
     nu = mag_shr(u, nu, zu);
     nv = mag_shr(v, nv, zv);
     for (;;) {                                   // invariant: u, v odd and nonzero
+        if (nu <= 2 && nv <= 2) {
+            nu = mag_set64(u, gcd64(mag_lo64(u, nu), mag_lo64(v, nv)));
+            break;
+        }
         int c = mag_cmp(u, nu, v, nv);
         if (c == 0) break;
         if (c < 0) { uint32_t* t = u; u = v; v = t; int ti = nu; nu = nv; nv = ti; }
+        if (nv <= 2 && nu > nv + 1) {            // much smaller operand: one modular reduction instead of many subtractions
+            uint64_t b = mag_lo64(v, nv);
+            nu = mag_set64(u, gcd64(mag_mod64(u, nu, b), b));
+            break;
+        }
         nu = mag_sub(u, u, nu, v, nv);           // u > v, both odd => u even and nonzero
         nu = mag_shr(u, nu, mag_ctz(u, nu));
     }
@@ -404,53 +435,96 @@ RELP_HD Val copy_val(const Val& v, uint32_t* heap, const Arena& ar) {
     return o;
 }
 
-// Reduce sign * num / den (den > 0, both in scratch buffers that may be destroyed) and store.
-// g1, g2: scratch of RELP_TL limbs each; q: scratch of RELP_TL limbs.
-RELP_HD Val reduce_store(int sign, uint32_t* num, int nn, uint32_t* den, int nd,
-                         uint32_t* g1, uint32_t* g2, uint32_t* q,
-                         uint32_t* heap, const Arena& ar) {
-    if (nn == 0) return val_zero();
-    if (nd == 1 && den[0] == 1) return store_val(sign, num, nn, den, nd, heap, ar);
-    for (int i = 0; i < nn; i++) g1[i] = num[i];
-    for (int i = 0; i < nd; i++) g2[i] = den[i];
-    uint32_t* g;
-    int ng = mag_gcd(g1, nn, g2, nd, &g);
-    if (ng == 1 && g[0] == 1) return store_val(sign, num, nn, den, nd, heap, ar);
-    uint32_t* other = (g == g1) ? g2 : g1;       // free scratch: reused as the stripped divisor
-    int nq = mag_divexact(q, num, nn, g, ng, other);
-    // num buffer is now free: use it for the reduced denominator
-    int ndq = mag_divexact(num, den, nd, g, ng, other);
-    return store_val(sign, q, nq, num, ndq, heap, ar);
+// gcd of two magnitudes that must stay intact: copies into scratch (each max(na, nb) + 2 limbs) first.
+// g == 1 is recognised without any work when either operand is 1.
+RELP_HD int gcd_keep(const uint32_t* a, int na, const uint32_t* b, int nb, uint32_t* s1, uint32_t* s2, uint32_t** g) {
+    if ((na == 1 && a[0] == 1) || (nb == 1 && b[0] == 1)) { s1[0] = 1; *g = s1; return 1; }
+    for (int i = 0; i < na; i++) s1[i] = a[i];
+    for (int i = 0; i < nb; i++) s2[i] = b[i];
+    return mag_gcd(s1, na, s2, nb, g);
+}
+// q = a / g exactly, a stays intact (tmp: na limbs for the running remainder, dtmp: ng limbs)
+RELP_HD int div_keep(uint32_t* q, const uint32_t* a, int na, const uint32_t* g, int ng, uint32_t* tmp, uint32_t* dtmp) {
+    if (ng == 1 && g[0] == 1) { for (int i = 0; i < na; i++) q[i] = a[i]; return na; }
+    for (int i = 0; i < na; i++) tmp[i] = a[i];
+    return mag_divexact(q, tmp, na, g, ng, dtmp);
 }
 
 // out = x + s * a * b for arbitrary tiers.                      (slow path of K1/K2/K3/K5)
+// Knuth 4.5.1 / GMP mpq: the product is formed from cross-reduced factors (two gcds of operand size),
+// the sum needs gcd(x.d, t.d) and -- only when that is not 1 -- one gcd against it.  No gcd ever sees
+// the full-size numerator and denominator of the unreduced result, which is what made the plain
+// "compute, then reduce" version spend 98 % of its time in one 3x-length binary GCD.
 RELP_HDN Val big_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) {
     Ref rx, ra, rb;
     ref_load(rx, x, heap); ref_load(ra, a, heap); ref_load(rb, b, heap);
     if (ra.sign == 0 || rb.sign == 0) return copy_val(x, heap, ar);
     if (rx.nn > RELP_OPL || rx.nd > RELP_OPL || ra.nn > RELP_OPL || ra.nd > RELP_OPL ||
         rb.nn > RELP_OPL || rb.nd > RELP_OPL) { set_err(ar.err, ERR_LIMB_CAPACITY); return val_zero(); }
-    uint32_t n1[2 * RELP_OPL], d1[2 * RELP_OPL];
-    uint32_t p[RELP_TL], q[RELP_TL], den[RELP_TL], g1[RELP_TL], g2[RELP_TL];
-    int nn1 = mag_mul(n1, ra.num, ra.nn, rb.num, rb.nn);
-    int nd1 = mag_mul(d1, ra.den, ra.nd, rb.den, rb.nd);
-    int s1 = ra.sign * rb.sign * s;
-    if (rx.sign == 0) return reduce_store(s1, n1, nn1, d1, nd1, g1, g2, q, heap, ar);
-    int np = mag_mul(p, rx.num, rx.nn, d1, nd1);         // x.n * d1
-    int nq = mag_mul(q, rx.den, rx.nd, n1, nn1);         // x.d * n1
-    int nden = mag_mul(den, rx.den, rx.nd, d1, nd1);
-    int sign;
-    if (rx.sign == s1) { np = mag_add(p, p, np, q, nq); sign = s1; }
-    else {
-        int c = mag_cmp(p, np, q, nq);
-        if (c == 0) return val_zero();
-        if (c > 0) { np = mag_sub(p, p, np, q, nq); sign = rx.sign; }
-        else { np = mag_sub(p, q, nq, p, np); sign = s1; }
+    uint32_t s1[RELP_TL], s2[RELP_TL], s3[RELP_TL];          // scratch
+    uint32_t f1[RELP_OPL + 2], f2[RELP_OPL + 2];             // reduced factors
+    uint32_t tn[2 * RELP_OPL + 2], td[2 * RELP_OPL + 2];     // t = a * b in lowest terms
+    uint32_t* g;
+    // t.n = (a.n / g1)(b.n / g2), t.d = (a.d / g2)(b.d / g1), g1 = gcd(a.n, b.d), g2 = gcd(b.n, a.d)
+    int ng = gcd_keep(ra.num, ra.nn, rb.den, rb.nd, s1, s2, &g);
+    int n1 = div_keep(f1, ra.num, ra.nn, g, ng, s3, g == s1 ? s2 : s1);
+    int n2 = div_keep(f2, rb.den, rb.nd, g, ng, s3, g == s1 ? s2 : s1);
+    // (f1 = a.n / g1, f2 = b.d / g1)  -- second pair goes through s-buffers, products are formed at once
+    uint32_t h1[RELP_OPL + 2], h2[RELP_OPL + 2];
+    ng = gcd_keep(rb.num, rb.nn, ra.den, ra.nd, s1, s2, &g);
+    int m1 = div_keep(h1, rb.num, rb.nn, g, ng, s3, g == s1 ? s2 : s1);
+    int m2 = div_keep(h2, ra.den, ra.nd, g, ng, s3, g == s1 ? s2 : s1);
+    int ntn = mag_mul(tn, f1, n1, h1, m1);
+    int ntd = mag_mul(td, h2, m2, f2, n2);
+    const int st = ra.sign * rb.sign * s;
+    if (rx.sign == 0) return store_val(st, tn, ntn, td, ntd, heap, ar);
+    // x + t
+    ng = gcd_keep(rx.den, rx.nd, td, ntd, s1, s2, &g);
+    if (ng == 1 && g[0] == 1) {
+        // coprime denominators: (x.n t.d + t.n x.d) / (x.d t.d) is already in lowest terms
+        int np = mag_mul(s1, rx.num, rx.nn, td, ntd);
+        int nq = mag_mul(s2, tn, ntn, rx.den, rx.nd);
+        int sign;
+        if (rx.sign == st) { np = mag_add(s1, s1, np, s2, nq); sign = st; }
+        else {
+            int c = mag_cmp(s1, np, s2, nq);
+            if (c == 0) return val_zero();
+            if (c > 0) { np = mag_sub(s1, s1, np, s2, nq); sign = rx.sign; }
+            else { np = mag_sub(s1, s2, nq, s1, np); sign = st; }
+        }
+        int nden = mag_mul(s3, rx.den, rx.nd, td, ntd);
+        return store_val(sign, s1, np, s3, nden, heap, ar);
     }
-    return reduce_store(sign, p, np, den, nden, g1, g2, q, heap, ar);
+    // d1 = g: num = x.n (t.d / d1) + t.n (x.d / d1); d2 = gcd(num, d1); result (num / d2) / ((x.d / d1)(t.d / d2))
+    uint32_t d1[RELP_OPL + 2];
+    const int nd1 = ng;
+    for (int i = 0; i < ng; i++) d1[i] = g[i];
+    uint32_t xq[RELP_OPL + 2], tq[2 * RELP_OPL + 2];
+    int nxq = div_keep(xq, rx.den, rx.nd, d1, nd1, s1, s2);
+    int ntq = div_keep(tq, td, ntd, d1, nd1, s1, s2);
+    int np = mag_mul(s1, rx.num, rx.nn, tq, ntq);
+    int nq = mag_mul(s2, tn, ntn, xq, nxq);
+    int sign;
+    if (rx.sign == st) { np = mag_add(s1, s1, np, s2, nq); sign = st; }
+    else {
+        int c = mag_cmp(s1, np, s2, nq);
+        if (c == 0) return val_zero();
+        if (c > 0) { np = mag_sub(s1, s1, np, s2, nq); sign = rx.sign; }
+        else { np = mag_sub(s1, s2, nq, s1, np); sign = st; }
+    }
+    // s1 = num (np limbs).  d2 = gcd(num, d1)
+    uint32_t g3[RELP_OPL + 2];
+    ng = gcd_keep(s1, np, d1, nd1, s2, s3, &g);
+    const int ng3 = ng;
+    for (int i = 0; i < ng; i++) g3[i] = g[i];
+    int nnum = div_keep(s2, s1, np, g3, ng3, s3, tn);             // tn is free now (used as divisor scratch)
+    int ntd2 = div_keep(s1, td, ntd, g3, ng3, s3, tn);            // s1 = t.d / d2
+    int nden = mag_mul(s3, xq, nxq, s1, ntd2);
+    return store_val(sign, s2, nnum, s3, nden, heap, ar);
 }
 
-// out = x / y (y != 0) for arbitrary tiers.
+// out = x / y (y != 0) for arbitrary tiers: (x.n / g1)(y.d / g2) / ((x.d / g2)(y.n / g1)), g1 = gcd(x.n, y.n),
+// g2 = gcd(y.d, x.d) -- in lowest terms without a gcd of the products.
 RELP_HDN Val big_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar) {
     Ref rx, ry;
     ref_load(rx, x, heap); ref_load(ry, y, heap);
@@ -458,10 +532,19 @@ RELP_HDN Val big_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar
     if (rx.nn > RELP_OPL || rx.nd > RELP_OPL || ry.nn > RELP_OPL || ry.nd > RELP_OPL) {
         set_err(ar.err, ERR_LIMB_CAPACITY); return val_zero();
     }
-    uint32_t num[RELP_TL], den[RELP_TL], g1[RELP_TL], g2[RELP_TL], q[RELP_TL];
-    int nn = mag_mul(num, rx.num, rx.nn, ry.den, ry.nd);
-    int nd = mag_mul(den, rx.den, rx.nd, ry.num, ry.nn);
-    return reduce_store(rx.sign * ry.sign, num, nn, den, nd, g1, g2, q, heap, ar);
+    uint32_t s1[RELP_OPL + 2], s2[RELP_OPL + 2], s3[RELP_OPL + 2];
+    uint32_t f1[RELP_OPL + 2], f2[RELP_OPL + 2], h1[RELP_OPL + 2], h2[RELP_OPL + 2];
+    uint32_t num[2 * RELP_OPL + 2], den[2 * RELP_OPL + 2];
+    uint32_t* g;
+    int ng = gcd_keep(rx.num, rx.nn, ry.num, ry.nn, s1, s2, &g);
+    int n1 = div_keep(f1, rx.num, rx.nn, g, ng, s3, g == s1 ? s2 : s1);
+    int n2 = div_keep(f2, ry.num, ry.nn, g, ng, s3, g == s1 ? s2 : s1);
+    ng = gcd_keep(ry.den, ry.nd, rx.den, rx.nd, s1, s2, &g);
+    int m1 = div_keep(h1, ry.den, ry.nd, g, ng, s3, g == s1 ? s2 : s1);
+    int m2 = div_keep(h2, rx.den, rx.nd, g, ng, s3, g == s1 ? s2 : s1);
+    int nn = mag_mul(num, f1, n1, h1, m1);
+    int nd = mag_mul(den, h2, m2, f2, n2);
+    return store_val(rx.sign * ry.sign, num, nn, den, nd, heap, ar);
 }
 
 // sign(x - y) for arbitrary tiers.
