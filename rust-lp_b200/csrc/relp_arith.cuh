@@ -284,41 +284,112 @@ RELP_HD uint64_t mag_mod64(const uint32_t* u, int nu, uint64_t v) {
 }
 RELP_HD int mag_set64(uint32_t* a, uint64_t x) { a[0] = (uint32_t)x; a[1] = (uint32_t)(x >> 32); return a[1] ? 2 : (a[0] ? 1 : 0); }
 
-// GCD of two nonzero magnitudes; destroys both buffers; *res points at the buffer (u or v) holding the
-// result; returns its limb count.  Buffers need one spare limb beyond max(nu, nv) and at least 2 limbs.
-// As soon as one operand fits 64 bits the other is reduced modulo it and the rest is a 64-bit gcd;
-// above that, binary GCD (subtract, strip trailing zeros).
-RELP_HD int mag_gcd(uint32_t* u, int nu, uint32_t* v, int nv, uint32_t** res) {
-    if (nu <= 2 || nv <= 2) {
-        if (nv > nu) { uint32_t* t = u; u = v; v = t; int ti = nu; nu = nv; nv = ti; }
-        uint64_t b = mag_lo64(v, nv);
-        uint64_t a = nu <= 2 ? mag_lo64(u, nu) : mag_mod64(u, nu, b);
-        *res = u;
-        return mag_set64(u, gcd64(a, b));
+RELP_HD int clz32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __clz((int)x);
+#else
+    return __builtin_clz(x);
+#endif
+}
+
+// u = u mod v in place (Knuth 4.3.1 D), nv >= 2, v[nv-1] != 0; u needs one spare limb above nu;
+// vn: scratch of nv limbs.  Returns the trimmed limb count of the remainder.
+RELP_HD int mag_mod(uint32_t* u, int nu, const uint32_t* v, int nv, uint32_t* vn) {
+    if (nu < nv) return nu;
+    const int sft = clz32(v[nv - 1]);
+    if (sft) {
+        for (int i = nv - 1; i > 0; i--) vn[i] = (v[i] << sft) | (v[i - 1] >> (32 - sft));
+        vn[0] = v[0] << sft;
+        u[nu] = u[nu - 1] >> (32 - sft);
+        for (int i = nu - 1; i > 0; i--) u[i] = (u[i] << sft) | (u[i - 1] >> (32 - sft));
+        u[0] <<= sft;
+    } else {
+        for (int i = 0; i < nv; i++) vn[i] = v[i];
+        u[nu] = 0;
     }
-    int zu = mag_ctz(u, nu), zv = mag_ctz(v, nv);
-    int sh = zu < zv ? zu : zv;
-    nu = mag_shr(u, nu, zu);
-    nv = mag_shr(v, nv, zv);
-    for (;;) {                                   // invariant: u, v odd and nonzero
-        if (nu <= 2 && nv <= 2) {
-            nu = mag_set64(u, gcd64(mag_lo64(u, nu), mag_lo64(v, nv)));
-            break;
+    const uint64_t vtop = vn[nv - 1], vsec = vn[nv - 2];
+    for (int j = nu - nv; j >= 0; j--) {
+        uint64_t num = ((uint64_t)u[j + nv] << 32) | u[j + nv - 1];
+        uint64_t qhat = num / vtop, rhat = num - qhat * vtop;
+        while (qhat >> 32 || qhat * vsec > ((rhat << 32) | u[j + nv - 2])) {
+            qhat--; rhat += vtop;
+            if (rhat >> 32) break;
         }
-        int c = mag_cmp(u, nu, v, nv);
-        if (c == 0) break;
-        if (c < 0) { uint32_t* t = u; u = v; v = t; int ti = nu; nu = nv; nv = ti; }
-        if (nv <= 2 && nu > nv + 1) {            // much smaller operand: one modular reduction instead of many subtractions
-            uint64_t b = mag_lo64(v, nv);
-            nu = mag_set64(u, gcd64(mag_mod64(u, nu, b), b));
-            break;
+        int64_t borrow = 0; uint64_t carry = 0;
+        for (int i = 0; i < nv; i++) {
+            uint64_t pr = qhat * vn[i] + carry;
+            carry = pr >> 32;
+            int64_t t = (int64_t)u[i + j] - (int64_t)(uint32_t)pr + borrow;
+            u[i + j] = (uint32_t)t;
+            borrow = t >> 32;                       // 0 or -1
         }
-        nu = mag_sub(u, u, nu, v, nv);           // u > v, both odd => u even and nonzero
-        nu = mag_shr(u, nu, mag_ctz(u, nu));
+        int64_t t = (int64_t)u[j + nv] - (int64_t)carry + borrow;
+        u[j + nv] = (uint32_t)t;
+        if (t < 0) {                                // qhat was one too large: add v back
+            uint64_t c = 0;
+            for (int i = 0; i < nv; i++) { c += (uint64_t)u[i + j] + vn[i]; u[i + j] = (uint32_t)c; c >>= 32; }
+            u[j + nv] += (uint32_t)c;
+        }
     }
-    if (sh) nu = mag_shl(u, nu, sh);
+    if (sft) {
+        for (int i = 0; i < nv - 1; i++) u[i] = (u[i] >> sft) | (u[i + 1] << (32 - sft));
+        u[nv - 1] >>= sft;
+    }
+    return mag_trim(u, nv);
+}
+
+// GCD of two nonzero magnitudes (Lehmer, Knuth 4.5.2 L, with 62-bit leading parts and 31-bit cofactors);
+// destroys both buffers; *res points at the buffer (u or v) holding the result; returns its limb
+// count.  Each buffer needs one spare limb beyond max(nu, nv).  `tmp`: min(nu, nv) limbs.
+// One outer step removes about 30 bits from both operands for two passes over the limbs; as soon as the
+// smaller operand fits 64 bits the rest is one modular reduction and a 64-bit gcd.
+RELP_HD int mag_gcd(uint32_t* u, int nu, uint32_t* v, int nv, uint32_t** res, uint32_t* tmp) {
+    if (mag_cmp(u, nu, v, nv) < 0) { uint32_t* t = u; u = v; v = t; int ti = nu; nu = nv; nv = ti; }
+    while (nv > 2) {                                 // invariant: u >= v > 0
+        // leading 62 bits of u and the bits of v in the same position
+        const int top = nu - 1;
+        const int sft = clz32(u[top]);
+        uint64_t uw = ((uint64_t)u[top] << 32) | u[top - 1], vw = 0;
+        uint32_t u3 = top >= 2 ? u[top - 2] : 0, v3 = 0;
+        if (nv == nu) { vw = ((uint64_t)v[top] << 32) | v[top - 1]; v3 = top >= 2 ? v[top - 2] : 0; }
+        else if (nv == nu - 1) { vw = v[top - 1]; v3 = top >= 2 ? v[top - 2] : 0; }
+        if (sft) { uw = (uw << sft) | (u3 >> (32 - sft)); vw = (vw << sft) | (v3 >> (32 - sft)); }
+        int64_t uh = (int64_t)(uw >> 2), vh = (int64_t)(vw >> 2);
+        int64_t A = 1, B = 0, C = 0, D = 1;
+        if (nv >= nu - 1) {
+            for (;;) {
+                if (vh + C <= 0 || vh + D <= 0 || uh + A < 0 || uh + B < 0) break;
+                int64_t q = (uh + A) / (vh + C);
+                if (q > 0x7fffffffLL || q != (uh + B) / (vh + D)) break;
+                int64_t nA = A - q * C, nB = B - q * D;
+                if (nA > 0x3fffffffLL || nA < -0x3fffffffLL || nB > 0x3fffffffLL || nB < -0x3fffffffLL) break;
+                int64_t nh = uh - q * vh;
+                A = C; C = nA; B = D; D = nB; uh = vh; vh = nh;
+            }
+        }
+        if (B == 0) {                                // no usable cofactors: one full remainder step
+            int nr = mag_mod(u, nu, v, nv, tmp);
+            uint32_t* t = u; u = v; v = t; nu = nv; nv = nr;
+            if (nv == 0) { *res = u; return nu; }
+            continue;
+        }
+        // (u, v) <- (A u + B v, C u + D v); both are non-negative and smaller than before
+        int64_t cu = 0, cv = 0;
+        for (int i = 0; i < nu; i++) {
+            int64_t ui = u[i], vi = i < nv ? v[i] : 0;
+            int64_t tu = A * ui + B * vi + cu, tv = C * ui + D * vi + cv;
+            u[i] = (uint32_t)tu; cu = tu >> 32;
+            v[i] = (uint32_t)tv; cv = tv >> 32;
+        }
+        int n2 = mag_trim(v, nu);
+        nu = mag_trim(u, nu); nv = n2;
+        if (nv == 0) { *res = u; return nu; }
+        if (mag_cmp(u, nu, v, nv) < 0) { uint32_t* t = u; u = v; v = t; int ti = nu; nu = nv; nv = ti; }
+    }
+    uint64_t bq = mag_lo64(v, nv);
+    uint64_t aq = nu <= 2 ? mag_lo64(u, nu) : mag_mod64(u, nu, bq);
     *res = u;
-    return nu;
+    return mag_set64(u, gcd64(aq, bq));
 }
 
 // inverse of an odd 32-bit number modulo 2^32 (Newton)
@@ -437,11 +508,11 @@ RELP_HD Val copy_val(const Val& v, uint32_t* heap, const Arena& ar) {
 
 // gcd of two magnitudes that must stay intact: copies into scratch (each max(na, nb) + 2 limbs) first.
 // g == 1 is recognised without any work when either operand is 1.
-RELP_HD int gcd_keep(const uint32_t* a, int na, const uint32_t* b, int nb, uint32_t* s1, uint32_t* s2, uint32_t** g) {
+RELP_HD int gcd_keep(const uint32_t* a, int na, const uint32_t* b, int nb, uint32_t* s1, uint32_t* s2, uint32_t** g, uint32_t* tmp) {
     if ((na == 1 && a[0] == 1) || (nb == 1 && b[0] == 1)) { s1[0] = 1; *g = s1; return 1; }
     for (int i = 0; i < na; i++) s1[i] = a[i];
     for (int i = 0; i < nb; i++) s2[i] = b[i];
-    return mag_gcd(s1, na, s2, nb, g);
+    return mag_gcd(s1, na, s2, nb, g, tmp);
 }
 // q = a / g exactly, a stays intact (tmp: na limbs for the running remainder, dtmp: ng limbs)
 RELP_HD int div_keep(uint32_t* q, const uint32_t* a, int na, const uint32_t* g, int ng, uint32_t* tmp, uint32_t* dtmp) {
@@ -466,12 +537,12 @@ RELP_HDN Val big_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* 
     uint32_t tn[2 * RELP_OPL + 2], td[2 * RELP_OPL + 2];     // t = a * b in lowest terms
     uint32_t* g;
     // t.n = (a.n / g1)(b.n / g2), t.d = (a.d / g2)(b.d / g1), g1 = gcd(a.n, b.d), g2 = gcd(b.n, a.d)
-    int ng = gcd_keep(ra.num, ra.nn, rb.den, rb.nd, s1, s2, &g);
+    int ng = gcd_keep(ra.num, ra.nn, rb.den, rb.nd, s1, s2, &g, s3);
     int n1 = div_keep(f1, ra.num, ra.nn, g, ng, s3, g == s1 ? s2 : s1);
     int n2 = div_keep(f2, rb.den, rb.nd, g, ng, s3, g == s1 ? s2 : s1);
     // (f1 = a.n / g1, f2 = b.d / g1)  -- second pair goes through s-buffers, products are formed at once
     uint32_t h1[RELP_OPL + 2], h2[RELP_OPL + 2];
-    ng = gcd_keep(rb.num, rb.nn, ra.den, ra.nd, s1, s2, &g);
+    ng = gcd_keep(rb.num, rb.nn, ra.den, ra.nd, s1, s2, &g, s3);
     int m1 = div_keep(h1, rb.num, rb.nn, g, ng, s3, g == s1 ? s2 : s1);
     int m2 = div_keep(h2, ra.den, ra.nd, g, ng, s3, g == s1 ? s2 : s1);
     int ntn = mag_mul(tn, f1, n1, h1, m1);
@@ -479,7 +550,7 @@ RELP_HDN Val big_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* 
     const int st = ra.sign * rb.sign * s;
     if (rx.sign == 0) return store_val(st, tn, ntn, td, ntd, heap, ar);
     // x + t
-    ng = gcd_keep(rx.den, rx.nd, td, ntd, s1, s2, &g);
+    ng = gcd_keep(rx.den, rx.nd, td, ntd, s1, s2, &g, s3);
     if (ng == 1 && g[0] == 1) {
         // coprime denominators: (x.n t.d + t.n x.d) / (x.d t.d) is already in lowest terms
         int np = mag_mul(s1, rx.num, rx.nn, td, ntd);
@@ -514,7 +585,7 @@ RELP_HDN Val big_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* 
     }
     // s1 = num (np limbs).  d2 = gcd(num, d1)
     uint32_t g3[RELP_OPL + 2];
-    ng = gcd_keep(s1, np, d1, nd1, s2, s3, &g);
+    ng = gcd_keep(s1, np, d1, nd1, s2, s3, &g, tn);            // tn is free now; the remainder scratch needs min(np, nd1) limbs
     const int ng3 = ng;
     for (int i = 0; i < ng; i++) g3[i] = g[i];
     int nnum = div_keep(s2, s1, np, g3, ng3, s3, tn);             // tn is free now (used as divisor scratch)
@@ -536,10 +607,10 @@ RELP_HDN Val big_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar
     uint32_t f1[RELP_OPL + 2], f2[RELP_OPL + 2], h1[RELP_OPL + 2], h2[RELP_OPL + 2];
     uint32_t num[2 * RELP_OPL + 2], den[2 * RELP_OPL + 2];
     uint32_t* g;
-    int ng = gcd_keep(rx.num, rx.nn, ry.num, ry.nn, s1, s2, &g);
+    int ng = gcd_keep(rx.num, rx.nn, ry.num, ry.nn, s1, s2, &g, s3);
     int n1 = div_keep(f1, rx.num, rx.nn, g, ng, s3, g == s1 ? s2 : s1);
     int n2 = div_keep(f2, ry.num, ry.nn, g, ng, s3, g == s1 ? s2 : s1);
-    ng = gcd_keep(ry.den, ry.nd, rx.den, rx.nd, s1, s2, &g);
+    ng = gcd_keep(ry.den, ry.nd, rx.den, rx.nd, s1, s2, &g, s3);
     int m1 = div_keep(h1, ry.den, ry.nd, g, ng, s3, g == s1 ? s2 : s1);
     int m2 = div_keep(h2, rx.den, rx.nd, g, ng, s3, g == s1 ? s2 : s1);
     int nn = mag_mul(num, f1, n1, h1, m1);

@@ -3,6 +3,7 @@
 // Python's fractions.Fraction without a GPU.  Not part of the product library.
 #include "relp_arith.cuh"
 #include <vector>
+#include <algorithm>
 #include <cstring>
 using namespace relp;
 
@@ -37,4 +38,18 @@ int t_read(const int64_t* x, uint32_t* out) {
     return (int)w;
 }
 uint64_t t_gcd64(uint64_t a, uint64_t b) { return gcd64(a, b); }
+// multi-limb gcd and remainder on their own (out: limbs of the result, returns its count)
+int t_mag_gcd(const uint32_t* a, int na, const uint32_t* b, int nb, uint32_t* out) {
+    std::vector<uint32_t> u(a, a + na), v(b, b + nb), tmp(std::max(na, nb) + 2);
+    u.resize(std::max(na, nb) + 2); v.resize(std::max(na, nb) + 2);
+    uint32_t* g; int ng = mag_gcd(u.data(), na, v.data(), nb, &g, tmp.data());
+    for (int i = 0; i < ng; i++) out[i] = g[i];
+    return ng;
+}
+int t_mag_mod(const uint32_t* a, int na, const uint32_t* b, int nb, uint32_t* out) {
+    std::vector<uint32_t> u(a, a + na), tmp(nb + 2); u.resize(na + 2);
+    int nr = mag_mod(u.data(), na, b, nb, tmp.data());
+    for (int i = 0; i < nr; i++) out[i] = u[i];
+    return nr;
+}
 }

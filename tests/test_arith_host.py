@@ -83,6 +83,49 @@ def test_gcd64(L):
         assert L.t_gcd64(a, b) == math.gcd(a, b)
 
 
+def _limbs_arg(x):
+    a, n = limbs(x)
+    return a, a.ctypes.data_as(C.c_void_p), n
+
+
+def _from_limbs(buf, n):
+    return sum(int(buf[i]) << (32 * i) for i in range(n))
+
+
+def test_mag_gcd_and_mod(L):
+    """Lehmer gcd (relp_arith.cuh mag_gcd) and the Knuth-D remainder behind it, against math.gcd / %:
+    equal and very different lengths, shared powers of two, multiples, quotient digits at the
+    2^32 - 1 boundary, operands that trigger the add-back step."""
+    rnd = random.Random(7)
+    out = np.zeros(600, dtype=np.uint32)
+    po = out.ctypes.data_as(C.c_void_p)
+    for it in range(6000):
+        ba = rnd.choice([33, 64, 65, 96, 97, 128, 160, 200, 257, 512, 1000, 2047])
+        bb = rnd.choice([33, 64, 65, 96, 97, 128, 160, 200, 257, 512, 1000, 2047])
+        a = rnd.getrandbits(ba) | 1 << (ba - 1); b = rnd.getrandbits(bb) | 1 << (bb - 1)
+        mode = it % 6
+        if mode == 1:
+            g = rnd.getrandbits(rnd.choice([1, 31, 32, 64, 100, 300])) + 1; a *= g; b *= g
+        elif mode == 2:
+            a = b * (rnd.getrandbits(rnd.choice([1, 32, 33, 70])) + 1)
+        elif mode == 3:
+            a <<= rnd.randint(0, 70); b <<= rnd.randint(0, 70)
+        elif mode == 4:            # quotient digits 0xffffffff / add-back candidates
+            b = (1 << bb) - rnd.getrandbits(20) - 1; a = b * ((1 << 32) - 1) + rnd.getrandbits(bb - 1)
+        elif mode == 5:
+            a = (1 << ba) - 1; b = (1 << bb) - 1
+        if a.bit_length() > 2048 * 2 or b.bit_length() > 2048 * 2:
+            continue
+        aa, pa, na = _limbs_arg(a); bbv, pb, nb = _limbs_arg(b)
+        if max(na, nb) + 2 > 290:
+            continue
+        n = L.t_mag_gcd(pa, na, pb, nb, po)
+        assert _from_limbs(out, n) == math.gcd(a, b), (hex(a), hex(b))
+        if nb >= 2 and na >= nb:
+            n = L.t_mag_mod(pa, na, pb, nb, po)
+            assert _from_limbs(out, n) == a % b, (hex(a), hex(b))
+
+
 def test_canonical_form_kats(L):
     """rational/mod.rs:26-60: 3/2 == 6/4, 0/2 == 0/5, 3/2 + 6/4 = 3, 3/2 * 6/4 = 9/4, (3/2)/(6/4) = 1"""
     a = mk(L, Fr(3, 2)); b = mk(L, Fr(6, 4)); z = mk(L, 0); one = mk(L, 1)
