@@ -131,6 +131,10 @@ int relp_carry_from_artificial(relp_ctx*);
  * filter/generic_wrapper.rs:224-300): additionally remove `rows` (sorted) from the Carry, from
  * every column of A and from b. */
 int relp_carry_from_artificial_remove_rows(relp_ctx*, int32_t n_rows, const int32_t* sorted_rows);
+/* InverseMaintener::from_basis (inverse_maintenance/mod.rs:91, carry/mod.rs:428-463): the phase-two Carry of
+ * a given basis, basis[i] = provider column in row i (from_basis_pivots, carry/mod.rs:465-482, sorts its
+ * pairs by row and calls this).  RELP_ERR_ARGUMENT if the columns are linearly dependent. */
+int relp_carry_from_basis(relp_ctx*, const int32_t* basis /* m */);
 
 /* ---- per-iteration trait methods (one call per step; results stay on the device) ------------- */
 /* PivotRule::select_primal_pivot_column (pivot_rule.rs:21-33) over Tableau::relative_cost

@@ -38,6 +38,7 @@ def lib():
             getattr(L, f).argtypes = [C.c_void_p, C.c_int, C.c_char_p]
         L.orc_set_value.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p]
         L.orc_begin.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.orc_from_basis.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_advance.argtypes = [C.c_void_p, C.c_long]
         L.orc_advance.restype = C.c_int
         L.orc_advance_to_handover.argtypes = [C.c_void_p]
@@ -88,6 +89,12 @@ class COracle:
 
     def begin(self, rule1=1, rule2=2):
         lib().orc_begin(self.h, rule1, rule2)
+
+    def from_basis(self, basis, rule2=2):
+        """carry/mod.rs:428-463: phase-two Carry of a given basis (basis[i] = column in row i)."""
+        lib().orc_begin(self.h, 1, rule2)
+        b = np.ascontiguousarray(basis, dtype=np.int32)
+        return lib().orc_from_basis(self.h, b.ctypes.data_as(C.c_void_p))
 
     def advance(self, max_new_pivots=-1):
         return lib().orc_advance(self.h, max_new_pivots)

@@ -307,6 +307,46 @@ struct Solver {
         last_selected = -1;
     }
 
+    // carry/mod.rs:428-463 (from_basis): basis[i] = column in row i.  The reference inverts through LU
+    // (basis_inverse_rows.rs:103-129); the inverse is unique, here plain Gauss-Jordan on [B | I].
+    bool from_basis(const std::vector<int>& basis) {
+        int m = lp.m;
+        std::vector<std::vector<Rat>> M(m, std::vector<Rat>(2 * m));
+        for (int k = 0; k < m; k++) {
+            for (const auto& e : lp.cols[basis[k]]) M[e.first][k] = e.second;
+            M[k][m + k] = Rat(1);
+        }
+        for (int k = 0; k < m; k++) {
+            int p = -1;
+            for (int i = k; i < m; i++) if (!M[i][k].is_zero()) { p = i; break; }
+            if (p < 0) return false;
+            std::swap(M[p], M[k]);
+            Rat piv = M[k][k];
+            for (int q = 0; q < 2 * m; q++) if (!M[k][q].is_zero()) M[k][q] = M[k][q] / piv;
+            for (int i = 0; i < m; i++) {
+                if (i == k || M[i][k].is_zero()) continue;
+                Rat f = M[i][k];
+                for (int q = 0; q < 2 * m; q++) if (!M[k][q].is_zero()) M[i][q] -= f * M[k][q];
+            }
+        }
+        nr_art = 0; phase1 = false; stage = 1; status = 0; last_selected = -1; log.clear(); rows_removed.clear();
+        c.basis_indices = basis; c.rows.assign(m, SparseVec()); c.b.assign(m, Rat()); c.minus_pi.assign(m, Rat());
+        for (int i = 0; i < m; i++) {
+            Rat bi;
+            for (int k = 0; k < m; k++) {
+                const Rat& v = M[i][m + k];
+                if (v.is_zero()) continue;
+                c.rows[i].emplace_back(k, v);
+                bi += v * lp.rhs[k];
+            }
+            c.b[i] = bi;
+        }
+        recompute_cost_row();
+        in_basis.assign(lp.n, 0);
+        for (int j : basis) in_basis[j] = 1;
+        return true;
+    }
+
     // phase_one.rs:125-170, phase_two.rs:22-51, mod.rs:30-75 as a resumable state machine
     int advance(long max_new_pivots, bool stop_at_handover = false) {
         auto t0 = std::chrono::steady_clock::now();
@@ -348,6 +388,8 @@ struct Solver {
 // come out as decimal strings "num/den" (or "num"); strings stay valid until the next call.
 // ---------------------------------------------------------------------------------------------
 extern "C" {
+
+int orc_from_basis(void* h, const int32_t* basis);
 
 void* orc_create(int m, int n, const int64_t* col_ptr, const int32_t* row_idx,
                  const int64_t* val_num, const int64_t* val_den,
@@ -444,4 +486,9 @@ const char* orc_rat_op(const char* a, const char* b, char op) {
     }
     return out.c_str();
 }
-}  // extern "C"
+int orc_from_basis(void* h, const int32_t* basis) {
+    Solver* s = (Solver*)h;
+    return s->from_basis(std::vector<int>(basis, basis + s->lp.m)) ? 0 : -1;
+}
+
+}

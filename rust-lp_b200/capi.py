@@ -23,7 +23,7 @@ FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
 SYMBOLS = [
     "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_comm_unique_id",
     "relp_attach_comm", "relp_attach_comm_callbacks", "relp_load_matrix", "relp_carry_create_partially_artificial",
-    "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_price",
+    "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_carry_from_basis", "relp_price",
     "relp_generate_column", "relp_ratio_test", "relp_change_basis", "relp_generate_element",
     "relp_iterate", "relp_solve_relaxation", "relp_solve_continue", "relp_solve_to_handover",
     "relp_dims", "relp_read_basis", "relp_read_block", "relp_read_carry", "relp_read_b",
@@ -82,6 +82,7 @@ def load_library(path=None):
     L.relp_carry_create_partially_artificial.argtypes = [vp, i32, vp, vp]
     L.relp_carry_from_artificial.argtypes = [vp]
     L.relp_carry_from_artificial_remove_rows.argtypes = [vp, i32, vp]
+    L.relp_carry_from_basis.argtypes = [vp, vp]
     L.relp_price.argtypes = [vp, C.c_int, vp, vp, vp, vp, sz]
     L.relp_generate_column.argtypes = [vp, i32]
     L.relp_ratio_test.argtypes = [vp, vp]
@@ -206,6 +207,12 @@ class Carry:
 
     def from_artificial(self):
         self._chk(self.L.relp_carry_from_artificial(self.h))
+
+    def from_basis(self, basis):
+        """`IM::from_basis(&basis, provider)` (inverse_maintenance/mod.rs:91): basis[i] = column in row i."""
+        b = np.ascontiguousarray(basis, dtype=np.int32)
+        assert b.size == self.pa.m
+        self._chk(self.L.relp_carry_from_basis(self.h, _p(b)))
 
     def from_artificial_remove_rows(self, rows):
         r = np.ascontiguousarray(rows, dtype=np.int32)

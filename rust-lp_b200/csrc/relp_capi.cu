@@ -746,6 +746,81 @@ static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* r
     return handover_common(c, basis, true);
 }
 
+// Carry::from_basis (carry/mod.rs:428-463, inverse_maintenance/mod.rs:91): the Carry of a GIVEN basis,
+// basis[i] = provider column that sits in row i.  The reference inverts through an LU factorisation
+// (basis_inverse_rows.rs:103-129); the inverse is unique, so it is built here by exact Gauss-Jordan with
+// the pivot stages of the loop: start from [rhs | I], bring the basis columns in one by one (pivot row =
+// smallest unused row with a nonzero entry), then put row "where column basis[i] landed" at position i.
+static int from_basis(relp_ctx* c, const int32_t* basis_in) {
+    if (!c->loaded) { set_error("relp_load_matrix first"); return RELP_ERR_ARGUMENT; }
+    if (c->world > 1) { set_error("from_basis is single-GPU only"); return RELP_ERR_COMM; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    int m = c->m, n = c->n;
+    std::vector<unsigned char> inb(n, 0);
+    for (int i = 0; i < m; i++) {
+        if (basis_in[i] < 0 || basis_in[i] >= n || inb[basis_in[i]]) { set_error("basis: column out of range or repeated"); return RELP_ERR_ARGUMENT; }
+        inb[basis_in[i]] = 1;
+    }
+    c->nr_art = 0; c->phase = 2; c->art_rows_h.clear();
+    int rc = alloc_carry(c, m, n);
+    if (rc) return rc;
+    std::vector<int> none(m, -1);
+    CUDA_TRY(cudaMemcpyAsync(c->basis.p, none.data(), m * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(c->row_art.p, none.data(), m * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->in_basis.p, 0, n, c->stream));
+    DState* s = c->h_st;
+    memset(s, 0, sizeof(DState));
+    s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld; s->n = n; s->nr_art = 0;
+    s->phase = 2; s->ncols = n; shard_cols(c, s); s->a_int = c->a_int;
+    s->status = ST_RUNNING; s->last_selected = -1; s->iter = 0; s->iter_limit = ~0ull; s->tag = 'b'; s->go = 1;
+    s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap;
+    init_heap_regions(c, s);
+    if (push_state(c)) return RELP_ERR_CUDA;
+    wire_dev(c);
+    LAUNCH(c, k_init_planes, c->sm_count * 8, RELP_THREADS, c->D, c->rhsn_d.p, c->rhsd_d.p);
+    CUDA_TRY(cudaMemsetAsync(c->colbits.p, 0, ((size_t)(m + 1) * (c->ld / 32)) * 4, c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->rowbits.p, 0, ((size_t)c->ld * ((m + 32) / 32)) * 4, c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->colsum.p, 0, ((size_t)(m + 1) * ((c->ld / 32 + 31) / 32)) * 4, c->stream));
+    LAUNCH(c, k_init_pattern, grid_for(c, c->mloc), RELP_THREADS, c->D, c->rhsn_d.p);
+    CUDA_TRY(cudaMemsetAsync(c->zn.p, 0, (size_t)(m + 1) * 8, c->stream));     // cost row 0/1 until K5 below (rc = 0 pivots do not touch it)
+    { std::vector<int64_t> ones(m + 1, 1); CUDA_TRY(cudaMemcpyAsync(c->zd.p, ones.data(), (size_t)(m + 1) * 8, cudaMemcpyHostToDevice, c->stream)); CUDA_TRY(cudaStreamSynchronize(c->stream)); }
+    DBuf<int> taken, where;
+    if (taken.alloc(m) || where.alloc(m)) return RELP_ERR_CUDA;
+    CUDA_TRY(cudaMemsetAsync(taken.p, 0, (size_t)m * sizeof(int), c->stream));
+    for (int i = 0; i < m; i++) {
+        LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'b', 0, 1);
+        enqueue_begin(c);                      // limb-pool compaction when the previous pivot asked for it
+        LAUNCH(c, k_set_pivot, 1, 1, c->st.p, basis_in[i], -1, 1);
+        if (enqueue_column_and_ratio(c, false)) return RELP_ERR_COMM;
+        LAUNCH(c, k_pick_unused_row, 1, RELP_THREADS, c->D, taken.p, where.p, i);
+        if (enqueue_change_basis(c)) return RELP_ERR_COMM;
+        if ((i & 1023) == 1023 && check_cuda(c)) return RELP_ERR_CUDA;
+    }
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    if (c->h_st->err) return err_status(c->h_st);
+    if (c->h_st->status != ST_RUNNING) { set_error("basis is singular"); return RELP_ERR_ARGUMENT; }
+    // rows into the order of `basis`
+    std::vector<int> keep_col(m + 1);
+    for (int k = 0; k <= m; k++) keep_col[k] = k;
+    DBuf<int> kc; DBuf<int64_t> nxn, nxd;
+    size_t plane = (size_t)(m + 1) * c->ld;
+    if (kc.alloc(m + 1) || nxn.alloc(plane) || nxd.alloc(plane)) return RELP_ERR_CUDA;
+    CUDA_TRY(cudaMemcpyAsync(kc.p, keep_col.data(), (m + 1) * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    LAUNCH(c, k_gather_planes, c->sm_count * 8, RELP_THREADS, c->xn.p, c->xd.p, c->ld, nxn.p, nxd.p, c->ld, m, m + 1, where.p, kc.p);
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    std::swap(c->xn.p, nxn.p); std::swap(c->xn.n, nxn.n); std::swap(c->xn.cap, nxn.cap);
+    std::swap(c->xd.p, nxd.p); std::swap(c->xd.n, nxd.n); std::swap(c->xd.cap, nxd.cap);
+    c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0; c->phase = 1;   // handover_common expects phase-1 numbering + nr_art (0)
+    std::vector<int> basis(basis_in, basis_in + m);
+    rc = handover_common(c, basis, true);
+    if (rc) return rc;
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    c->h_st->iter = 0; c->h_st->sum_T = c->h_st->sum_S = c->h_st->sum_TS = 0; c->h_st->escalated = 0;
+    if (push_state(c)) return RELP_ERR_CUDA;
+    c->stage = 2;
+    return RELP_OK;
+}
+
 // phase_one.rs:223-260
 static int remove_artificial_basis_variables(relp_ctx* c) {
     std::vector<int> basis;
@@ -855,6 +930,7 @@ int relp_carry_create_partially_artificial(relp_ctx* c, int32_t n_piv, const int
     return create_partially_artificial(c, n_piv, piv_rows, piv_cols);
 }
 int relp_carry_from_artificial(relp_ctx* c) { return c ? from_artificial(c) : RELP_ERR_ARGUMENT; }
+int relp_carry_from_basis(relp_ctx* c, const int32_t* basis) { return (c && basis) ? from_basis(c, basis) : RELP_ERR_ARGUMENT; }
 int relp_carry_from_artificial_remove_rows(relp_ctx* c, int32_t n_rows, const int32_t* sorted_rows) {
     return c ? from_artificial_remove_rows(c, n_rows, sorted_rows) : RELP_ERR_ARGUMENT;
 }

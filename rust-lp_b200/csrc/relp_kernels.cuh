@@ -703,7 +703,8 @@ __device__ __forceinline__ void pivot_bookkeeping(const Dev& D, int j, int r, in
     DState* st = D.st;
     int leaving = D.basis[r];
     D.basis[r] = j;
-    D.in_basis[leaving] = 0; D.in_basis[j] = 1;
+    if (leaving >= 0) D.in_basis[leaving] = 0;
+    D.in_basis[j] = 1;
     st->leaving = leaving; st->j = j; st->r = r;
     if (!keeps_rc) st->rc_valid = 0;     // step-wise / multi-GPU drivers price from scratch
     int Tl = T - 1;                       // reference's col.len() - 1 (rows eliminated) on this rank
@@ -1374,6 +1375,22 @@ __global__ void k_reprice_selected(Dev D) {   // rc of st->j for the step-wise A
     DState* st = D.st;
     Arena ar = transient(D);
     st->rc = price_column_csc(D, st, st->j, ar);
+}
+
+// Warm start (Carry::from_basis, carry/mod.rs:428-463): pivot row for the column being brought in = the
+// smallest row with d_i != 0 that no earlier column took.  One block.
+__global__ void k_pick_unused_row(Dev D, int* taken, int* where, int slot) {
+    DState* st = D.st;
+    if (halted(st)) return;
+    __shared__ int best;
+    if (threadIdx.x == 0) best = 0x7fffffff;
+    __syncthreads();
+    for (int t = threadIdx.x; t < st->T; t += blockDim.x) { int li = D.tlist[t]; if (!taken[li]) atomicMin(&best, li); }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (best == 0x7fffffff) st->status = ST_NO_ROW;       // the columns are linearly dependent
+        else { st->r = st->row_lo + best; taken[best] = 1; where[slot] = best; }
+    }
 }
 
 // Row/column removal (basis_inverse_rows.rs:194-205, carry/mod.rs:650-689): gather the kept rows

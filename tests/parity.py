@@ -138,3 +138,31 @@ def _check_state(state, expected):
     assert mo == emo and list(mpi) == empi and list(b) == eb and list(basis) == ebasis
     m = len(eb)
     assert [[r.get(k, Fr(0)) for k in range(m)] for r in rows] == [[Fr(x) for x in r] for r in erows]
+
+
+def check_from_basis(pa, lib_path, pivots_before=3, rule2=2):
+    """Warm start (`IM::from_basis`): take the basis the oracle has after `pivots_before` phase-two pivots,
+    rebuild the Carry from that basis alone on both sides (oracle: Gauss-Jordan on [B | I]; product:
+    relp_carry_from_basis) -- every entry must equal the Carry the simplex iterations had produced --
+    then solve on from there: identical pivots, objective and solution."""
+    o = coracle.COracle(pa); o.begin(1, rule2)
+    st = o.advance_to_handover()
+    if st != coracle.RUNNING:
+        return False
+    o.advance(pivots_before)
+    reached = o.carry()
+    basis = list(reached[3])
+    o2 = coracle.COracle(pa)
+    assert o2.from_basis(basis, rule2) == 0
+    assert o2.carry() == reached, "oracle: from_basis differs from the iterated Carry"
+    c = capi.Carry(pa, heap_words=1 << 22, lib_path=lib_path)
+    c.from_basis(basis)
+    assert_same_carry(c, o2, "after from_basis")
+    st_c = c.iterate(rule2)
+    st_o = o2.advance(-1)
+    assert st_c == STATUS[st_o]
+    assert c.log() == oracle_log(o2)
+    assert_same_carry(c, o2, "at termination after a warm start")
+    assert c.current_bfs() == o2.current_bfs()
+    c.close()
+    return True

@@ -63,6 +63,16 @@ def test_stage_per_launch_path(seed):
                                 expect_escalation=True, persistent=False)
 
 
+@pytest.mark.parametrize("seed", range(8))
+def test_from_basis_warm_start(seed):
+    """`IM::from_basis` (carry/mod.rs:428-463): the Carry rebuilt from a basis alone equals the iterated one"""
+    lp = feasible_lp(seed + 300, 3, 1, 3, 2, 10, frac=(seed % 2 == 0))
+    parity.check_from_basis(pa_from_lp(lp), LIB, pivots_before=seed % 4)
+    if seed == 0:      # escalated entries, and a sparse structured basis
+        assert parity.check_from_basis(pa_from_lp(feasible_lp(0, 6, 2, 6, 4, 24, frac=True, maxval=9, density=0.4)), LIB, pivots_before=6)
+        assert parity.check_from_basis(synthetic_lp(200, 2000, 20, "tu"), LIB, pivots_before=15)
+
+
 @pytest.mark.parametrize("m,n,k", [(60, 400, 6), (200, 2000, 20), (2000, 20000, 20)])
 def test_synthetic_tu(m, n, k):
     """BASELINE config 5a scaled down to sizes the oracle finishes: int64 tier, no escalation."""
