@@ -1,0 +1,36 @@
+"""Full exact solves of the BASELINE.json configs[2..3] problems (tests/golden/mps_prefix) on the GPU, in
+chunks of pivots, with a wall-clock limit per problem.  One JSON line per chunk -> gpurun_out/big_times.jsonl.
+usage: python scripts/big_time.py [seconds per problem] [chunk] [names...]"""
+import json, os, sys, time
+sys.path.insert(0, '.'); sys.path.insert(0, 'tests')
+from rust_lp_b200 import capi
+from test_mps_prefix import load, EXPECTED
+
+limit = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
+chunk = int(sys.argv[2]) if len(sys.argv) > 2 else 250
+only = sys.argv[3:]
+os.makedirs("gpurun_out", exist_ok=True)
+out = open(os.path.join("gpurun_out", "big_times.jsonl"), "a")
+for e in EXPECTED:
+    name = e["name"]
+    if only and name not in only: continue
+    pa = load(name)
+    c = capi.Carry(pa, heap_words=1 << 28)
+    t0 = time.time()
+    st, first = 0, True
+    try:
+        while st == 0 and time.time() - t0 < limit:
+            t1 = time.time()
+            st = c.solve_relaxation(1, 2, max_pivots=chunk) if first else c.solve_continue(chunk)
+            first = False
+            s = c.stats()
+            rec = dict(name=name, m=pa.m, n=pa.n, status=st, pivots=s.pivots, chunk_s=time.time() - t1, total_s=time.time() - t0,
+                       loop_ms=s.loop_ms, escalated=s.escalated, max_limbs=s.max_limbs, compactions=s.compactions,
+                       narrow=s.narrow_pivots, phase=s.phase, heap_peak_words=s.heap_peak_words)
+            print(json.dumps(rec), flush=True); out.write(json.dumps(rec) + "\n"); out.flush()
+        if st == capi.OPTIMAL:
+            print(name, "objective", float(c.get_objective_function_value()), "reference", e["full_solve_reference"], flush=True)
+    except capi.RelpError as err:
+        print(name, "ERROR", err, flush=True)
+        out.write(json.dumps(dict(name=name, error=str(err), total_s=time.time() - t0)) + "\n"); out.flush()
+    c.close()
