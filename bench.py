@@ -229,6 +229,19 @@ def run_single(args):
     tfile = os.path.join(ROOT, "profiles", "traffic_r01.json")
     if os.path.exists(tfile):
         traffic = json.load(open(tfile)).get("dram_bytes_per_launch")
+    # ---- K1 alone at the dense bound: every element of the Carry block changes (micro-benchmark) -------
+    k1 = None
+    if not args.no_k1_dense:
+        c.create_for_partially_artificial(pa.piv_rows, pa.piv_cols)
+        ms_row, ms_upd, T, S = c.debug_k1_dense(seed=20260101, reps=6)
+        k1_bytes = W_BYTES * (2 * T * S + S + T)
+        k1 = {"kernel": "k_update (stage_update, tiled) on a dense Carry block: T = m - 1 rows x S = m + 1 columns of "
+                        "small integers, d_r = 1", "T": T, "S": S, "ms_update": ms_upd, "ms_pivot_row": ms_row,
+              "algorithmic_bytes": k1_bytes, "achieved": k1_bytes / (ms_upd * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+              "frac": k1_bytes / (ms_upd * 1e-3) / 1e9 / peak, "bound": "hbm",
+              "moved_bytes": (8 + 8 + 8) * T * S,
+              "note": "algorithmic = w (2 T S + S + T), w = 16 (SURVEY 8(d)); the kernel leaves unchanged denominators "
+                      "unwritten (24 B per element on integer data)"}
     # ---- CPU baseline (oracle, 1 core, bounded sample) ----------------------------------------------
     cpu_v, cpu_done, cpu_dt = cpu_sample(pa, args.cpu_pivots)
     line = {"metric": METRIC, "value": pivots / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
@@ -258,6 +271,8 @@ def run_single(args):
             "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": 1, "kind": "port",
                              "sample": f"first {cpu_done} pivots of the same LP, {cpu_dt:.1f} s (oracle/simplex.cpp, single "
                                        "thread like the reference)"}}
+    if k1:
+        line["roofline_k1_dense"] = k1
     print(json.dumps(line), flush=True)
 
 
@@ -271,6 +286,7 @@ def main():
     ap.add_argument("--n", type=int, default=200000)
     ap.add_argument("--nnz-col", type=int, default=20)
     ap.add_argument("--variant", default="tu")
+    ap.add_argument("--no-k1-dense", action="store_true", help="skip the dense Carry-update micro-benchmark")
     ap.add_argument("--cpu-pivots", type=int, default=150, help="oracle sample: pivots per CPU step")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -76,6 +76,7 @@ typedef struct relp_stats {
     uint64_t stage_ns[8];       /* persistent loop, ns: [0] selection, [1] column+ratio, [2] pivot row, [3] update,
                                    [4] multi-limb + housekeeping, [5] narrow iterations (CTA 0 alone, all stages) */
     uint64_t narrow_pivots;     /* pivots done by one CTA alone (sparse B^-1), the rest by the whole grid   */
+    uint64_t wide_handoffs;     /* pivots whose dense Carry update the persistent loop handed to the staged update kernel */
 } relp_stats;
 
 /* ---- life cycle ------------------------------------------------------------------------- */
@@ -88,12 +89,20 @@ const char* relp_last_error(void);
 int relp_abi_version(void);
 /* options: "persistent" = 1 (default) runs single-GPU loops as one cooperative kernel, 0 as one
  * launch per stage (the path multi-GPU solves use, with NCCL between the stages); "narrow" = 1
- * (default) lets CTA 0 of the persistent kernel do small pivots alone, 0 always uses the whole grid. */
+ * (default) lets CTA 0 of the persistent kernel do small pivots alone, 0 always uses the whole grid;
+ * "k1_exit" / "k1_min" = number of Carry elements (T x S) from which the persistent loop hands a dense
+ * update to the staged update kernel / from which that kernel tiles the update (set before the Carry
+ * is created; tests lower them so that small problems take the large-problem paths). */
 int relp_set_option(relp_ctx*, const char* name, int64_t value);
 /* the cudaStream_t all work of this context is enqueued on (for CUDA-event timing by the caller) */
 void* relp_stream(relp_ctx*);
 /* debug (option "trace" = 1): globaltimer of every CTA at 16 points of the last loop iteration */
 int relp_debug_trace(relp_ctx*, uint64_t* out /* n_ctas x 16 */, int32_t n_ctas);
+/* K1 micro-benchmark: overwrite the Carry planes with dense small integers and a dense generated
+ * column with d_r = 1, then time `reps` pivot-row + update kernel pairs (carry/mod.rs:549-570 at
+ * T = m - 1 rows, S = m + 1 columns) with CUDA events.  The Carry is invalid afterwards. */
+int relp_debug_k1_dense(relp_ctx*, uint64_t seed, int32_t reps, float* ms_pivot_row, float* ms_update,
+                        int64_t* T_out, int64_t* S_out);
 
 /* Multi-GPU only: attach an NCCL communicator (ncclComm_t, created by the caller from
  * torch.distributed's rendezvous) used for the per-pivot pivot-row broadcast and the two

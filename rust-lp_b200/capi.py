@@ -21,7 +21,7 @@ FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
 
 # every symbol include/relp_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
-    "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_comm_unique_id",
+    "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_debug_k1_dense", "relp_comm_unique_id",
     "relp_attach_comm", "relp_attach_comm_callbacks", "relp_load_matrix", "relp_carry_create_partially_artificial",
     "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_carry_from_basis", "relp_price",
     "relp_generate_column", "relp_ratio_test", "relp_change_basis", "relp_generate_element",
@@ -48,7 +48,7 @@ class Stats(C.Structure):
                 ("sum_S", C.c_uint64), ("sum_TS", C.c_uint64), ("heap_peak_words", C.c_uint64),
                 ("compactions", C.c_uint64), ("kernel_launches", C.c_uint64), ("max_limbs", C.c_int32),
                 ("m", C.c_int32), ("n", C.c_int32), ("nr_artificial", C.c_int32), ("phase", C.c_int32),
-                ("loop_ms", C.c_double), ("stage_ns", C.c_uint64 * 8), ("narrow_pivots", C.c_uint64)]
+                ("loop_ms", C.c_double), ("stage_ns", C.c_uint64 * 8), ("narrow_pivots", C.c_uint64), ("wide_handoffs", C.c_uint64)]
 
 
 ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
@@ -59,7 +59,7 @@ _libs = {}
 
 def load_library(path=None):
     """dlopen the C-ABI library and declare its prototypes.  No fallback of any kind."""
-    path = path or LIB_PATH
+    path = path or os.environ.get("RELP_B200_LIB") or LIB_PATH      # the env override is for A/B builds of the same library
     if path in _libs:
         return _libs[path]
     if not os.path.exists(path):
@@ -75,6 +75,8 @@ def load_library(path=None):
     L.relp_stream.argtypes = [vp]
     L.relp_stream.restype = vp
     L.relp_debug_trace.argtypes = [vp, vp, i32]
+    if hasattr(L, "relp_debug_k1_dense"):      # absent from A/B builds of older sources only
+        L.relp_debug_k1_dense.argtypes = [vp, C.c_uint64, i32, vp, vp, vp, vp]
     L.relp_comm_unique_id.argtypes = [vp, C.c_char_p]
     L.relp_attach_comm.argtypes = [vp, vp, C.c_char_p]
     L.relp_attach_comm_callbacks.argtypes = [vp, ALLGATHER_FN, ALLREDUCE_FN, vp]
@@ -179,6 +181,14 @@ class Carry:
         out = np.zeros((n_ctas, 16), np.uint64)
         self._chk(self.L.relp_debug_trace(self.h, _p(out), n_ctas))
         return out
+
+    def debug_k1_dense(self, seed=1, reps=4):
+        """K1 micro-benchmark (dense rank-1 update of the whole Carry block); the Carry is invalid afterwards.
+        Returns (ms pivot row, ms update, T, S)."""
+        a, b = C.c_float(), C.c_float()
+        t, s_ = C.c_int64(), C.c_int64()
+        self._chk(self.L.relp_debug_k1_dense(self.h, seed, reps, C.byref(a), C.byref(b), C.byref(t), C.byref(s_)))
+        return a.value, b.value, t.value, s_.value
 
     def close(self):
         if getattr(self, "h", None):

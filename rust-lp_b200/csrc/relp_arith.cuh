@@ -153,6 +153,19 @@ RELP_HDN bool small_fma_rational(const Val& x, const Val& a, const Val& b, int s
 RELP_HD bool small_fma(const Val& x, const Val& a, const Val& b, int s, Val* out) {
     if (a.n == 0 || b.n == 0) { *out = x; return true; }
     if (x.d == 1 && a.d == 1 && b.d == 1) {                 // integer fast path
+#ifndef RELP_NO_FMA32
+        if (a.n == (int64_t)(int32_t)a.n && b.n == (int64_t)(int32_t)b.n) {
+            // both factors fit 32 bits: one 32 x 32 -> 64 multiply (IMAD.WIDE) instead of an emulated
+            // 64 x 64 -> 128 product, and a sign test instead of a 128-bit range check
+            const int64_t t = (int64_t)(int32_t)a.n * (int64_t)(int32_t)b.n;
+            int64_t r; bool ovf;
+            if (s > 0) { r = (int64_t)((uint64_t)x.n + (uint64_t)t); ovf = ((x.n ^ r) & (t ^ r)) < 0; }
+            else       { r = (int64_t)((uint64_t)x.n - (uint64_t)t); ovf = ((x.n ^ t) & (x.n ^ r)) < 0; }
+            if (ovf || r == INT64_MIN) return false;
+            *out = make_small(r, 1);
+            return true;
+        }
+#endif
         i128 t = (i128)a.n * b.n;
         i128 r = s > 0 ? (i128)x.n + t : (i128)x.n - t;
         if (r > RELP_I64_MAX || r < -RELP_I64_MAX) return false;

@@ -89,14 +89,17 @@ struct relp_ctx {
     std::vector<int64_t> an, ad, cn, cd, rhsn, rhsd;
     // device buffers
     DBuf<DState> st; DBuf<uint32_t> heap;
-    DBuf<int64_t> xn, xd, zn, zd, an_d, ad_d, cn_d, cd_d, rhsn_d, rhsd_d, dn, dd, pnd, tmpn, tmpd, sell_an, sell_ad;
+    DBuf<int64_t> xn, xd, zn, zd, an_d, ad_d, cn_d, cd_d, rhsn_d, rhsd_d, dn, dd, pnd, psnd, tmpn, tmpd, sell_an, sell_ad;
     DBuf<long long> col_ptr_d, sell_ptr; DBuf<uint32_t> zbits; DBuf<int> row_idx_d, sell_row, basis, art_row, tlist, slist, cost_rows, scratch_i;
     DBuf<unsigned char> in_basis;
     DBuf<int64_t> rn, rd; DBuf<long long> row_ptr_d; DBuf<int4> csr_ent; DBuf<int> row_art; DBuf<uint32_t> colbits, rowbits, colsum; DBuf<unsigned> claim;   // reduced-cost row, nonzero pattern
     size_t wl_cap = 0;
     DBuf<int2> worklist; DBuf<Cand> cand, cand2, gather; DBuf<LogEntry> log; DBuf<unsigned long long> trace;
     int n_slices = 0, a_int = 1, coop_blocks = 0, last_ratio_blocks = 1;
-    bool use_persistent = true, use_narrow = true, smem_opt_in = false;
+    bool use_persistent = true, use_narrow = true, smem_opt_in = false, upd_opt_in = false;
+    long long wide_handoffs = 0;
+    long long k1_exit = 8 << 20;    // option "k1_exit": T x S from which the persistent loop hands a dense update to k_update
+    long long k1_min = 300000;      // option "k1_min": T x S from which the wide Carry update is tiled / staged
     DState* h_st = nullptr;       // pinned mirror
     Dev D;
     bool loaded = false, carry_ready = false;
@@ -353,6 +356,7 @@ static void wire_dev(relp_ctx* c) {
     D.cn = c->cn_d.p; D.cd = c->cd_d.p; D.basis = c->basis.p; D.in_basis = c->in_basis.p;
     D.art_row = c->art_row.p; D.dn = c->dn.p; D.dd = c->dd.p;
     D.pn = c->pnd.p; D.pd = c->pnd.p + (c->m + 1);
+    D.psn = c->psnd.p; D.psd = c->psnd.p + (c->m + 1);
     D.tlist = c->tlist.p; D.slist = c->slist.p; D.worklist = c->worklist.p; D.cand = c->cand.p; D.cand2 = c->cand2.p;
     D.rn = c->rn.p; D.rd = c->rd.p; D.row_ptr = c->row_ptr_d.p; D.csr_ent = c->csr_ent.p;
     D.colbits = c->colbits.p; D.rowbits = c->rowbits.p; D.colsum = c->colsum.p; D.claim = c->claim.p; D.row_art = c->row_art.p;
@@ -367,8 +371,8 @@ static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
     size_t plane = (size_t)(m + 1) * c->ld;
     if (c->xn.alloc(plane) || c->xd.alloc(plane) || c->zn.alloc(m + 1) || c->zd.alloc(m + 1)) return RELP_ERR_CUDA;
     if (c->in_basis.alloc(ncols_max) || c->zbits.alloc((m + 31) / 32 + 1)) return RELP_ERR_CUDA;
-    if (c->dn.alloc(c->mloc + 1) || c->dd.alloc(c->mloc + 1) || c->tmpn.alloc(m + 2) || c->tmpd.alloc(m + 2)) return RELP_ERR_CUDA;
-    if (c->pnd.alloc(2 * (size_t)(m + 1))) return RELP_ERR_CUDA;
+    if (c->dn.alloc(c->ld + 32) || c->dd.alloc(c->ld + 32) || c->tmpn.alloc(m + 2) || c->tmpd.alloc(m + 2)) return RELP_ERR_CUDA;
+    if (c->pnd.alloc(2 * (size_t)(m + 1)) || c->psnd.alloc(2 * (size_t)(m + 1))) return RELP_ERR_CUDA;
     if (c->basis.alloc(m) || c->art_row.alloc(m) || c->tlist.alloc(c->mloc + 1) || c->slist.alloc(m + 1)) return RELP_ERR_CUDA;
     if (c->cost_rows.alloc(c->mloc + 1) || c->scratch_i.alloc(2 * (size_t)(m + 2))) return RELP_ERR_CUDA;
     if (c->claim.alloc(c->n)) return RELP_ERR_CUDA;
@@ -479,13 +483,28 @@ static int enqueue_column_and_ratio(relp_ctx* c, bool select_row) {
     if (!select_row) return 0;
     return enqueue_select(c, (int)ARG_RATIO, gb, 0);
 }
+// k_update: one CTA of RELP_UTHREADS per SM, with the shared-memory ring of the dense update behind it
+static int launch_update(relp_ctx* c) {
+#ifdef RELP_EMUL
+    LAUNCH(c, k_update, 1, 1, c->D, -1);
+#else
+    const size_t smem = k1_smem_bytes(RELP_UTHREADS) + 128;
+    if (!c->upd_opt_in) {
+        CUDA_TRY(cudaFuncSetAttribute(k_update, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        c->upd_opt_in = true;
+    }
+    LAUNCH_SMEM(c, k_update, c->sm_count, RELP_UTHREADS, smem, c->D, 0);
+#endif
+    return 0;
+}
+
 static int enqueue_change_basis(relp_ctx* c) {
     LAUNCH(c, k_pivot_row, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D, c->world > 1 ? 1 : 0);
     if (c->world > 1) {
         if (comm_allreduce_i64(c, c->pnd.p, 2 * (size_t)(c->m + 1))) return RELP_ERR_COMM;
         LAUNCH(c, k_build_slist, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D);
     }
-    LAUNCH(c, k_update, c->sm_count * 8, RELP_THREADS, c->D);
+    if (launch_update(c)) return RELP_ERR_CUDA;
     LAUNCH(c, k_update_big, c->sm_count * 2, 128, c->D);
     LAUNCH(c, k_iter_end, 1, 1, c->D);
     return 0;
@@ -554,6 +573,13 @@ static int run_loop(relp_ctx* c, int rule, int64_t max_iters, int tag) {
         if (sync_state(c)) return RELP_ERR_CUDA;
         const DState* s = c->h_st;
         if (s->err) { result = err_status(s); break; }
+        if (s->want_wide) {      // the persistent loop left with a large dense update pending (see k_simplex_loop)
+            if (launch_update(c)) return RELP_ERR_CUDA;
+            LAUNCH(c, k_update_big, c->sm_count * 2, 128, c->D);
+            LAUNCH(c, k_iter_end, 1, 1, c->D);
+            c->wide_handoffs++;
+            continue;
+        }
         if (s->status == ST_NO_COLUMN) { result = RELP_OPTIMAL; break; }
         if (s->status == ST_NO_ROW) { result = RELP_UNBOUNDED; break; }
         if (s->iter >= limit) { result = RELP_OK; break; }
@@ -592,7 +618,7 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld; s->n = n; s->nr_art = nr_art;
     s->phase = 1; s->ncols = nr_art + n; shard_cols(c, s); s->a_int = c->a_int;
     s->status = ST_RUNNING; s->last_selected = -1; s->iter = 0; s->iter_limit = ~0ull; s->tag = '1'; s->go = 1;
-    s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap;
+    s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap; s->k1_min = c->k1_min; s->k1_exit = c->k1_exit;
     init_heap_regions(c, s);
     if (push_state(c)) return RELP_ERR_CUDA;
     {   // row -> artificial column
@@ -773,7 +799,7 @@ static int from_basis(relp_ctx* c, const int32_t* basis_in) {
     s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld; s->n = n; s->nr_art = 0;
     s->phase = 2; s->ncols = n; shard_cols(c, s); s->a_int = c->a_int;
     s->status = ST_RUNNING; s->last_selected = -1; s->iter = 0; s->iter_limit = ~0ull; s->tag = 'b'; s->go = 1;
-    s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap;
+    s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap; s->k1_min = c->k1_min; s->k1_exit = c->k1_exit;
     init_heap_regions(c, s);
     if (push_state(c)) return RELP_ERR_CUDA;
     wire_dev(c);
@@ -1108,6 +1134,7 @@ int relp_stats_get(relp_ctx* c, relp_stats* out) {
         out->sum_TS = s->sum_TS; out->heap_peak_words = s->pool_peak; out->compactions = s->compactions;
         for (int k = 0; k < 8; k++) out->stage_ns[k] = s->stage_ns[k];
         out->narrow_pivots = s->narrow_done;
+        out->wide_handoffs = (uint64_t)c->wide_handoffs;
     }
     return RELP_OK;
 }
@@ -1121,6 +1148,8 @@ int relp_set_option(relp_ctx* c, const char* name, int64_t value) {
     if (!c || !name) return RELP_ERR_ARGUMENT;
     if (!strcmp(name, "persistent")) { c->use_persistent = value != 0; return RELP_OK; }
     if (!strcmp(name, "narrow")) { c->use_narrow = value != 0; return RELP_OK; }
+    if (!strcmp(name, "k1_min")) { c->k1_min = value; return RELP_OK; }
+    if (!strcmp(name, "k1_exit")) { c->k1_exit = value; return RELP_OK; }     // takes effect when the Carry is next created
     if (!strcmp(name, "coop_blocks")) { c->coop_blocks = (int)value; return RELP_OK; }   // debug: CTAs of the persistent kernel
     if (!strcmp(name, "trace")) {      // debug: per-CTA barrier arrival times of the last iteration
         if (value) { if (c->trace.alloc(16 * 4096)) return RELP_ERR_CUDA; cudaMemset(c->trace.p, 0, 16 * 4096 * 8); }
@@ -1131,6 +1160,81 @@ int relp_set_option(relp_ctx* c, const char* name, int64_t value) {
     return RELP_ERR_ARGUMENT;
 }
 void* relp_stream(relp_ctx* c) { return c ? (void*)c->stream : nullptr; }
+// K1 micro-benchmark (bench.py "k1_dense"): the Carry planes are overwritten with dense small integers
+// and a dense generated column with d_r = 1, so that one pivot-row + update pair is a full-size rank-1
+// update (T = local rows, S = m + 1).  Times the two kernels with CUDA events.  The Carry is garbage
+// afterwards: set the problem up again before solving.
+__global__ void k_debug_fill_planes(Dev D, unsigned long long seed) {
+    DState* st = D.st;
+    const size_t ld = st->ld, total = (size_t)(st->m + 1) * ld;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        unsigned long long h = (e + seed) * 0x9E3779B97F4A7C15ull; h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
+        int64_t v = (int64_t)(h % 1000) + 100;      // wide enough that x - d p = 0 is rare, as in a filled-in B^-1
+        if (h & 1024) v = -v;
+        if ((int)(e % ld) >= st->mloc) v = 0;
+        D.xn[e] = v; D.xd[e] = 1;
+    }
+}
+__global__ void k_debug_fill_column(Dev D, unsigned long long seed, int r, int j) {
+    DState* st = D.st;
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int li = tid; li < st->mloc; li += gridDim.x * blockDim.x) {
+        unsigned long long h = (li + seed) * 0xD6E8FEB86659FD93ull; h ^= h >> 31;
+        int64_t v = (int64_t)(h % 3) + 1;
+        if (h & 8) v = -v;
+        if (li == r - st->row_lo) v = 1;
+        D.dn[li] = v; D.dd[li] = 1; D.tlist[li] = li;
+    }
+    if (tid == 0) {
+        st->T = st->mloc; st->S = 0; st->W = 0; st->wl_count = 0; st->r = r; st->j = j;
+        st->rc = make_small(0, 1); st->status = ST_RUNNING; st->rc_valid = 0;
+    }
+}
+
+int relp_debug_k1_dense(relp_ctx* c, uint64_t seed, int32_t reps, float* ms_pivot_row, float* ms_update,
+                        int64_t* T_out, int64_t* S_out) {
+#ifdef RELP_EMUL
+    (void)c; (void)seed; (void)reps; (void)ms_pivot_row; (void)ms_update; (void)T_out; (void)S_out;
+    return RELP_ERR_ARGUMENT;
+#else
+    if (!c || !c->carry_ready || c->world != 1 || reps < 1) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaEvent_t e0, e1, e2;
+    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1)); CUDA_TRY(cudaEventCreate(&e2));
+    double tp = 0, tu = 0;
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    const int j = c->h_st->ncols - 1;
+    for (int rep = 0; rep < reps; rep++) {
+        const int r = (int)((seed + 7919ull * rep) % (uint64_t)c->m);
+        LAUNCH(c, k_debug_fill_planes, c->sm_count * 8, RELP_THREADS, c->D, (unsigned long long)seed + rep);
+        LAUNCH(c, k_build_pattern, c->sm_count * 8, RELP_THREADS, c->D);
+        LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'B', 1, 1);
+        LAUNCH(c, k_debug_fill_column, c->sm_count, RELP_THREADS, c->D, (unsigned long long)seed + rep, r, j);
+        CUDA_TRY(cudaEventRecord(e0, c->stream));
+        LAUNCH(c, k_pivot_row, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D, 0);
+        CUDA_TRY(cudaEventRecord(e1, c->stream));
+        if (launch_update(c)) return RELP_ERR_CUDA;
+        CUDA_TRY(cudaEventRecord(e2, c->stream));
+        LAUNCH(c, k_update_big, c->sm_count * 2, 128, c->D);
+        LAUNCH(c, k_iter_end, 1, 1, c->D);
+        CUDA_TRY(cudaEventSynchronize(e2));
+        float a = 0, b = 0;
+        cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2);
+        tp += a; tu += b;
+        if (check_cuda(c)) return RELP_ERR_CUDA;
+        if (sync_state(c)) return RELP_ERR_CUDA;
+        if (c->h_st->err) return err_status(c->h_st);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+    if (ms_pivot_row) *ms_pivot_row = (float)(tp / reps);
+    if (ms_update) *ms_update = (float)(tu / reps);
+    if (T_out) *T_out = c->mloc - 1;
+    if (S_out) *S_out = c->m + 1;
+    c->carry_ready = false;
+    return RELP_OK;
+#endif
+}
+
 int relp_debug_trace(relp_ctx* c, uint64_t* out, int32_t n_ctas) {
     if (!c || !c->trace.p || n_ctas > 4096) return RELP_ERR_ARGUMENT;
     CUDA_TRY(cudaMemcpy(out, c->trace.p, (size_t)n_ctas * 16 * 8, cudaMemcpyDeviceToHost));

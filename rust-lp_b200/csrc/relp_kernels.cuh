@@ -61,6 +61,9 @@ struct DState {
     int W;                         // sum of the CSR row lengths over the pivot row's nonzero columns
     int wl_cap;                    // capacity of the escalation worklist
     int narrow_verdict;            // persistent loop: outcome of CTA 0's attempt at the current iteration
+    long long k1_min;              // k_update: T x S from which the Carry update is tiled (dense d: staged through shared memory)
+    long long k1_exit;             // persistent loop: T x S from which a dense update is handed to k_update
+    int want_wide;                 // persistent loop left with the pivot row ready and the update pending
     int narrow_skip, narrow_backoff;   // after a pivot that was too big for one CTA, do not try again for a while
     unsigned long long narrow_done;   // iterations completed by CTA 0 alone
     unsigned long long iter, iter_limit;
@@ -89,6 +92,7 @@ struct Dev {
     const int* art_row;                       // artificial column -> row (Partially::column_to_row)
     int64_t* dn; int64_t* dd;                 // generated column, local rows
     int64_t* pn; int64_t* pd;                 // normalised pivot row (m + 1), replicated
+    int64_t* psn; int64_t* psd;               // the same values compacted in slist order (wide update: contiguous reads)
     int* tlist; int* slist;
     int2* worklist;
     Cand* cand;                               // per-block partial argmin: pricing
@@ -111,6 +115,7 @@ struct Dev {
 };
 
 #define RELP_THREADS 256          // stage wrappers
+#define RELP_UTHREADS 512         // k_update: one CTA per SM (its shared-memory ring takes most of the SM's)
 #ifndef RELP_PTHREADS
 #define RELP_PTHREADS 512         // persistent kernel: one CTA per SM; 512 threads leave 128 registers each
 #endif
@@ -290,6 +295,14 @@ __device__ __forceinline__ void price_consider(const Dev& D, Val rc, int j, int 
 
 #ifndef RELP_EMUL
 extern __shared__ uint32_t relp_dyn_smem[];
+// staging ring of the dense Carry update: `off` bytes into the dynamic shared memory, < 0 = none
+__device__ __forceinline__ unsigned char* k1_region(int off) {
+    if (off < 0) return nullptr;
+    unsigned char* p = (unsigned char*)relp_dyn_smem + off;
+    return p + ((128u - ((uint32_t)__cvta_generic_to_shared(p) & 127u)) & 127u);     // bulk copies want 16-byte aligned shared addresses
+}
+#else
+static inline unsigned char* k1_region(int) { return nullptr; }
 #endif
 
 // One pass over this rank's SELL slices, one lane per column jj.  `init(jj, acc)` says whether the
@@ -657,7 +670,7 @@ __device__ void stage_pivot_row(const Dev& D, const Grid& g, const Inv& I, int r
         Val p = val_div(ld_val(D.xn, D.xd, e), pivot, D.heap, ar);
         st_val(D.xn, D.xd, e, p);
         st_val(D.pn, D.pd, k, p);
-        int s = list_append(&st->S); D.slist[s] = k;
+        int s = list_append(&st->S); D.slist[s] = k; D.psn[s] = p.n; D.psd[s] = p.d;
         if (k > 0) len += (int)(D.row_ptr[k] - D.row_ptr[k - 1]);
     }
     if (len) atomicAdd(&st->W, len);
@@ -667,7 +680,7 @@ __device__ void stage_pivot_row(const Dev& D, const Grid& g, const Inv& I, int r
 __device__ void stage_build_slist(const Dev& D, const Grid& g, const Inv& I) {
     DState* st = D.st;
     for (int k = g.tid; k <= I.m; k += g.nth)
-        if (D.pn[k] != 0) { int s = list_append(&st->S); D.slist[s] = k; }
+        if (D.pn[k] != 0) { int s = list_append(&st->S); D.slist[s] = k; D.psn[s] = D.pn[k]; D.psd[s] = D.pd[k]; }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -675,19 +688,24 @@ __device__ void stage_build_slist(const Dev& D, const Grid& g, const Inv& I) {
 // row.  Fixed-width tier in place; elements whose operands or result leave int64/int64 are queued
 // for the multi-limb stage.  One thread does the basis bookkeeping (tableau/mod.rs:72-84).
 // ---------------------------------------------------------------------------------------------
-// x_ik -= d_i p_k for one element (fixed-width tier in place, else queued for the multi-limb stage)
-__device__ __forceinline__ void carry_elem_update(const Dev& D, const Inv& I, int li, int k, const Val& dv, const Val& p) {
+// x_ik -= d_i p_k for one element whose old value `x` is already in registers (fixed-width tier in
+// place, else queued for the multi-limb stage).  The denominator plane is only written when the
+// denominator changes: on integer data (den = 1 throughout) the update moves 24 bytes per element, not 32.
+__device__ __forceinline__ void carry_elem_apply(const Dev& D, const Inv& I, int li, int k, const Val& x, const Val& dv, const Val& p) {
     DState* st = D.st;
     size_t e = (size_t)k * I.ld + li;
-    Val x = ld_val(D.xn, D.xd, e);
     Val out;
     if (x.d > 0 && dv.d > 0 && p.d > 0 && small_fma(x, dv, p, -1, &out)) {
-        st_val(D.xn, D.xd, e, out);
+        D.xn[e] = out.n;
+        if (out.d != x.d) D.xd[e] = out.d;
         if ((x.n != 0) != (out.n != 0)) pattern_set(D, I, li, k, out.n != 0);
     } else {
         int q = atomicAdd(&st->wl_count, 1);
         if (q < st->wl_cap) D.worklist[q] = make_int2(li, k); else atomicOr(&st->err, ERR_HEAP_EXHAUSTED);
     }
+}
+__device__ __forceinline__ void carry_elem_update(const Dev& D, const Inv& I, int li, int k, const Val& dv, const Val& p) {
+    carry_elem_apply(D, I, li, k, ld_val(D.xn, D.xd, (size_t)k * I.ld + li), dv, p);
 }
 // z_k -= rc p_k on the cost row [-obj | -pi] and its bitmap      (carry/mod.rs:326-333)
 __device__ __forceinline__ void cost_row_update(const Dev& D, int k, const Val& rc, const Val& p, const Arena& ar) {
@@ -717,11 +735,203 @@ __device__ __forceinline__ void pivot_bookkeeping(const Dev& D, int j, int r, in
     st->sum_T += rows; st->sum_S += (unsigned long long)S; st->sum_TS += rows * (unsigned long long)S;
 }
 
-__device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, int r, Val rc, int keeps_rc) {
+#ifndef RELP_EMUL
+// ---- bulk asynchronous copies (TMA, 1-D) global -> shared, completion on an mbarrier ----------
+#ifndef RELP_TMA_INLINE
+#define RELP_TMA_INLINE __forceinline__
+#endif
+#define RELP_K1_STAGES 4           // tiles in the shared-memory ring (STAGES - 1 loads in flight)
+#define RELP_K1_NC 2               // columns per tile
+__host__ __device__ __forceinline__ size_t k1_smem_bytes(int threads) {
+    return 128 + (size_t)RELP_K1_STAGES * 2 * RELP_K1_NC * (2 * (size_t)threads) * 8;
+}
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_inval(uint64_t* b) {
+    asm volatile("mbarrier.inval.shared::cta.b64 [%0];" :: "r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
+    const uint32_t a = smem_u32(b);
+    uint32_t ok;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// one element of the pair a thread owns in the dense-row update: returns the new value, or the old one
+// when the element went to the multi-limb queue (stage_update_big reads it from memory)
+__device__ __noinline__ Val dense_elem(const Dev& D, const Inv& I, int li, int k, const Val& x, const Val& dv, const Val& p) {
+    Val out;
+    if (x.d > 0 && dv.d > 0 && p.d > 0 && small_fma(x, dv, p, -1, &out)) {
+        if ((x.n != 0) != (out.n != 0)) pattern_set(D, I, li, k, out.n != 0);
+        return out;
+    }
+    DState* st = D.st;
+    int w = atomicAdd(&st->wl_count, 1);
+    if (w < st->wl_cap) D.worklist[w] = make_int2(li, k); else atomicOr(&st->err, ERR_HEAP_EXHAUSTED);
+    return x;
+}
+
+// K1 when d is dense, staged through shared memory: a tile is 2 * blockDim.x consecutive rows of
+// RELP_K1_NC pivot-row columns, both planes; one thread issues the bulk copies of the tile STAGES - 1
+// ahead (8 KB contiguous per column and plane at 512 threads), every thread owns two consecutive rows
+// (16-byte shared loads, 16-byte global stores; a denominator pair is stored only if it changed).  The
+// loads in flight are set by the ring (96 KB per SM), not by registers or occupancy.  Every CTA takes
+// a contiguous run of tiles with the column chunks fastest, so d_i stays in registers.
+__device__ __forceinline__ void mbar_arrive(uint64_t* b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(b)) : "memory");
+}
+__device__ RELP_TMA_INLINE void update_dense_tma(const Dev& D, const Grid& g, const Inv& I, int S, int lr, unsigned char* smem) {
+    const int NS = RELP_K1_STAGES, NC = RELP_K1_NC;
+    const int R = blockDim.x * 2, nwarps = blockDim.x >> 5;
+    uint64_t* full = (uint64_t*)smem;                      // tile landed (bulk copies complete)
+    uint64_t* empty = full + NS;                           // tile consumed (one arrival per warp)
+    int64_t* buf = (int64_t*)(smem + 128);                 // [NS][plane][NC][R]
+    const size_t stage_elems = (size_t)2 * NC * R;
+    const size_t ld = I.ld;
+    const int ntc = ((int)ld + R - 1) / R, nsc = (S + NC - 1) / NC;
+    const long long ntiles = (long long)ntc * nsc;
+    const long long lo = ntiles * g.bid / g.nb, hi = ntiles * (g.bid + 1) / g.nb;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NS; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], nwarps); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](long long tile) {
+        const long long it = tile - lo;
+        const int st = (int)(it % NS);
+        if (it >= NS) mbar_wait(&empty[st], (uint32_t)((it / NS - 1) & 1));    // every warp is done with the tile that was there
+        const int tc = (int)(tile / nsc), sc = (int)(tile - (long long)tc * nsc);
+        const int row0 = tc * R;
+        const int rows = (int)ld - row0 < R ? (int)ld - row0 : R;
+        const int ncols = S - sc * NC < NC ? S - sc * NC : NC;
+        const uint32_t bytes = (uint32_t)rows * 8u;
+        mbar_expect_tx(&full[st], 2u * (uint32_t)ncols * bytes);
+        int64_t* dst = buf + (size_t)st * stage_elems;
+        for (int q = 0; q < ncols; q++) {
+            const size_t src = (size_t)D.slist[sc * NC + q] * ld + row0;
+            bulk_g2s(dst + (size_t)q * R, D.xn + src, bytes, &full[st]);
+            bulk_g2s(dst + (size_t)(NC + q) * R, D.xd + src, bytes, &full[st]);
+        }
+    };
+    if (threadIdx.x == 0) for (int i = 0; i < NS - 1 && lo + i < hi; i++) issue(lo + i);
+    int cur_tc = -1, li0 = 0;
+    bool a0 = false, a1 = false, f0 = false, f1 = false;
+    Val d0 = val_zero(), d1 = val_zero();
+    for (long long tile = lo; tile < hi; tile++) {
+        const long long it = tile - lo;
+        const int st = (int)(it % NS);
+        if (threadIdx.x == 0 && tile + NS - 1 < hi) issue(tile + NS - 1);
+        const int tc = (int)(tile / nsc), sc = (int)(tile - (long long)tc * nsc);
+        if (tc != cur_tc) {
+            cur_tc = tc; li0 = tc * R + threadIdx.x * 2;
+            longlong2 dn2 = make_longlong2(0, 0), dd2 = make_longlong2(1, 1);
+            if (li0 < I.mloc) { dn2 = *(const longlong2*)(D.dn + li0); dd2 = *(const longlong2*)(D.dd + li0); }
+            if (li0 == lr || li0 >= I.mloc) dn2.x = 0;
+            if (li0 + 1 == lr || li0 + 1 >= I.mloc) dn2.y = 0;
+            a0 = dn2.x != 0; a1 = dn2.y != 0;
+            d0.n = dn2.x; d0.d = dd2.x; d1.n = dn2.y; d1.d = dd2.y;
+            f0 = d0.d == 1 && d0.n == (int64_t)(int32_t)d0.n; f1 = d1.d == 1 && d1.n == (int64_t)(int32_t)d1.n;
+        }
+        // the tile's columns and their p_k (compacted in slist order by the pivot-row stage): independent
+        // loads, requested before the wait
+        const int ncols = S - sc * NC < NC ? S - sc * NC : NC;
+        int kk[NC]; Val pp[NC];
+#pragma unroll
+        for (int q = 0; q < NC; q++) if (q < ncols) { kk[q] = D.slist[sc * NC + q]; pp[q] = ld_val(D.psn, D.psd, sc * NC + q); }
+        mbar_wait(&full[st], (uint32_t)((it / NS) & 1));
+        const int64_t* sb = buf + (size_t)st * stage_elems + threadIdx.x * 2;
+        longlong2 xn2[NC], xd2[NC];
+#pragma unroll
+        for (int q = 0; q < NC; q++) if (q < ncols) { xn2[q] = *(const longlong2*)(sb + (size_t)q * R); xd2[q] = *(const longlong2*)(sb + (size_t)(NC + q) * R); }
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) mbar_arrive(&empty[st]);
+        if (a0 || a1) {
+#pragma unroll
+            for (int q = 0; q < NC; q++) if (q < ncols) {
+                const int k = kk[q];
+                longlong2 on = xn2[q], od = xd2[q];
+                // common case in line: integer element, d_i and p_k fit 32 bits -> one IMAD.WIDE, a subtraction and
+                // a sign test; everything else (rationals, overflow, zero <-> nonzero) goes through dense_elem
+                const bool pf = pp[q].d == 1 && pp[q].n == (int64_t)(int32_t)pp[q].n;
+                if (a0) {
+                    const int64_t t = (int64_t)(int32_t)d0.n * (int64_t)(int32_t)pp[q].n;
+                    const int64_t r = (int64_t)((uint64_t)xn2[q].x - (uint64_t)t);
+                    if (f0 && pf && xd2[q].x == 1 && xn2[q].x != 0 && r != 0 && r != INT64_MIN && ((xn2[q].x ^ t) & (xn2[q].x ^ r)) >= 0) on.x = r;
+                    else { Val x; x.n = xn2[q].x; x.d = xd2[q].x; Val o = dense_elem(D, I, li0, k, x, d0, pp[q]); on.x = o.n; od.x = o.d; }
+                }
+                if (a1) {
+                    const int64_t t = (int64_t)(int32_t)d1.n * (int64_t)(int32_t)pp[q].n;
+                    const int64_t r = (int64_t)((uint64_t)xn2[q].y - (uint64_t)t);
+                    if (f1 && pf && xd2[q].y == 1 && xn2[q].y != 0 && r != 0 && r != INT64_MIN && ((xn2[q].y ^ t) & (xn2[q].y ^ r)) >= 0) on.y = r;
+                    else { Val x; x.n = xn2[q].y; x.d = xd2[q].y; Val o = dense_elem(D, I, li0 + 1, k, x, d1, pp[q]); on.y = o.n; od.y = o.d; }
+                }
+                if (on.x != xn2[q].x || on.y != xn2[q].y) *(longlong2*)(D.xn + (size_t)k * ld + li0) = on;
+                if (od.x != xd2[q].x || od.y != xd2[q].y) *(longlong2*)(D.xd + (size_t)k * ld + li0) = od;
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) for (int s = 0; s < NS; s++) { mbar_inval(&full[s]); mbar_inval(&empty[s]); }
+    __syncthreads();
+}
+#endif
+
+// Large T x S blocks are cut into tiles of blockDim.x consecutive entries of tlist x RELP_US entries of
+// slist: a thread keeps its row's d_i in registers, has RELP_US independent element loads in flight, and a
+// warp reads 32 rows of one column (list_append hands a warp consecutive slots, so when d is dense they are
+// 32 consecutive rows = 256 contiguous bytes per plane).  Small blocks keep one element per thread.
+#ifndef RELP_US
+#define RELP_US 8
+#endif
+
+// TILED = false: the persistent loop's instance (one element per thread; keeping the tiled code out of
+// that kernel keeps its register allocation -- and the narrow iterations -- as they were; a pivot that is
+// large enough to matter is handed to k_update, see k_simplex_loop).
+template <bool TILED>
+__device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, int r, Val rc, int keeps_rc, unsigned char* k1_smem) {
     DState* st = D.st;
     const int T = st->T, S = st->S;
     const int lr = r - I.row_lo;
     const long long total = (long long)T * S;
+#ifndef RELP_EMUL
+    if (TILED && k1_smem && total >= st->k1_min && 2 * T >= I.mloc) {
+        // d is dense: walk the rows themselves (rows with d_i = 0 are carried along unchanged;
+        // stage_gen_column wrote d_i for every local row)
+        update_dense_tma(D, g, I, S, lr, k1_smem);
+    } else if (TILED && total >= st->k1_min) {
+        const int TT = blockDim.x;
+        const int ntc = (T + TT - 1) / TT, nsc = (S + RELP_US - 1) / RELP_US;
+        const size_t ld = I.ld;
+        for (long long tile = g.bid; tile < (long long)ntc * nsc; tile += g.nb) {
+            const int sc = (int)(tile / ntc), tc = (int)(tile - (long long)sc * ntc);
+            const int t = tc * TT + threadIdx.x, s0 = sc * RELP_US;
+            const int li = t < T ? D.tlist[t] : -1;
+            const bool act = li >= 0 && li != lr;
+            Val dv = val_zero();
+            if (act) dv = ld_val(D.dn, D.dd, li);
+            int kk[RELP_US]; Val xx[RELP_US], pp[RELP_US];
+#pragma unroll
+            for (int q = 0; q < RELP_US; q++) kk[q] = s0 + q < S ? D.slist[s0 + q] : -1;
+#pragma unroll
+            for (int q = 0; q < RELP_US; q++) if (act && kk[q] >= 0) xx[q] = ld_val(D.xn, D.xd, (size_t)kk[q] * ld + li);
+#pragma unroll
+            for (int q = 0; q < RELP_US; q++) if (kk[q] >= 0) pp[q] = ld_val(D.pn, D.pd, kk[q]);
+#pragma unroll
+            for (int q = 0; q < RELP_US; q++) if (act && kk[q] >= 0) carry_elem_apply(D, I, li, kk[q], xx[q], dv, pp[q]);
+        }
+    } else
+#endif
     for (long long w = g.tid; w < total; w += g.nth) {
         int s = (int)(w / T), t = (int)(w - (long long)s * T);
         int li = D.tlist[t];
@@ -1130,7 +1340,22 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
         GRID_SYNC();
         TRACE(8);
         t3 = gtime();
-        stage_update(D, g, I, col.idx, row.idx, col.v, 1);
+#ifndef RELP_EMUL
+        // A dense update of this size is bandwidth work for the whole GPU: leave the loop and let the host
+        // run it as k_update (shared-memory ring fed by bulk copies), then come back.  T and S are final
+        // after the barrier above, so every thread takes the same branch.
+        if ((long long)st->T * st->S >= st->k1_exit && 2 * st->T >= I.mloc) {
+            if (g.tid == 0) {
+                st->want_wide = 1;
+                if (narrow_failed) {
+                    int bo = st->narrow_backoff ? st->narrow_backoff * 2 : 2;
+                    st->narrow_backoff = bo > 64 ? 64 : bo; st->narrow_skip = st->narrow_backoff;
+                } else if (st->narrow_skip > 0) st->narrow_skip--;
+            }
+            break;
+        }
+#endif
+        stage_update<false>(D, g, I, col.idx, row.idx, col.v, 1, nullptr);
         stage_update_rc(D, g, I, row.idx, col.v, smem_words);
         TRACE(9);
         GRID_SYNC();
@@ -1190,9 +1415,9 @@ __global__ void k_build_slist(Dev D) {
     if (halted(D.st)) return;
     stage_build_slist(D, this_grid_dims(), load_inv(D.st));
 }
-__global__ void k_update(Dev D) {
+__global__ void __launch_bounds__(RELP_UTHREADS, 1) k_update(Dev D, int k1_off) {
     if (halted(D.st)) return;
-    stage_update(D, this_grid_dims(), load_inv(D.st), D.st->j, D.st->r, D.st->rc, 0);
+    stage_update<true>(D, this_grid_dims(), load_inv(D.st), D.st->j, D.st->r, D.st->rc, 0, k1_region(k1_off));
 }
 __global__ void k_update_big(Dev D) {
     if (halted(D.st)) return;
@@ -1200,6 +1425,7 @@ __global__ void k_update_big(Dev D) {
 }
 __global__ void k_iter_end(Dev D) {
     if (halted(D.st)) return;
+    D.st->want_wide = 0;
     end_of_iteration(D);
 }
 

@@ -26,13 +26,15 @@ def assert_same_carry(c, o, what=""):
     assert got[4] == exp[4], f"B^-1 differs {what}"
 
 
-def check_full_solve(pa, lib_path, rule1=1, rule2=2, heap_words=1 << 22, expect_escalation=None, persistent=True):
+def check_full_solve(pa, lib_path, rule1=1, rule2=2, heap_words=1 << 22, expect_escalation=None, persistent=True, options=None):
     """Whole solve through relp_solve_relaxation: identical status, pivot log (entering column,
     row, leaving column, T, S per pivot), objective, basic solution and every Carry entry."""
     o = coracle.COracle(pa)
     st_o = o.solve(rule1, rule2)
     c = capi.Carry(pa, heap_words=heap_words, lib_path=lib_path)
     c.set_option("persistent", persistent)
+    for name, value in (options or {}).items():
+        c.set_option(name, value)
     st = c.solve_relaxation(rule1, rule2)
     assert st == STATUS[st_o], (st, st_o)
     assert c.log() == oracle_log(o)

@@ -53,6 +53,22 @@ def test_resumable(seed):
     parity.check_resumable(pa_from_lp(lp), LIB)
 
 
+@pytest.mark.parametrize("seed", range(10))
+def test_dense_update_paths(seed):
+    """the large-problem paths of the Carry update on small problems: thresholds lowered so that every wide
+    pivot with a dense generated column leaves the persistent loop for k_update (shared-memory ring fed by
+    bulk copies, two rows per thread) and every other one is tiled there; same pivots, same Carry"""
+    lp = feasible_lp(seed + 300, 4, 1, 5, 3, 14, frac=(seed % 2 == 0), dup_rows=(1 if seed % 4 == 0 else 0), density=0.8)
+    opts = {"narrow": 0, "k1_exit": 1, "k1_min": 1}
+    s, _ = parity.check_full_solve(pa_from_lp(lp), LIB, options=opts)
+    assert s.wide_handoffs > 0
+    parity.check_full_solve(pa_from_lp(lp), LIB, persistent=False, options=opts)
+    if seed == 0:
+        s, _ = parity.check_full_solve(pa_from_lp(feasible_lp(0, 6, 2, 6, 4, 24, frac=True, maxval=9, density=0.4)), LIB,
+                                       expect_escalation=True, options=opts)
+        assert s.wide_handoffs > 0
+
+
 @pytest.mark.parametrize("seed", range(8))
 def test_stage_per_launch_path(seed):
     """the one-launch-per-stage driver (what multi-GPU solves use) gives the same results"""
