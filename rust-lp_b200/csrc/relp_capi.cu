@@ -1204,12 +1204,12 @@ int relp_debug_k1_dense(relp_ctx* c, uint64_t seed, int32_t reps, float* ms_pivo
     double tp = 0, tu = 0;
     if (sync_state(c)) return RELP_ERR_CUDA;
     const int j = c->h_st->ncols - 1;
-    for (int rep = 0; rep < reps; rep++) {
-        const int r = (int)((seed + 7919ull * rep) % (uint64_t)c->m);
-        LAUNCH(c, k_debug_fill_planes, c->sm_count * 8, RELP_THREADS, c->D, (unsigned long long)seed + rep);
+    for (int rep = -1; rep < reps; rep++) {          // rep -1: warm-up, not timed
+        const int r = (int)((seed + 7919ull * (rep + 1)) % (uint64_t)c->m);
+        LAUNCH(c, k_debug_fill_planes, c->sm_count * 8, RELP_THREADS, c->D, (unsigned long long)seed + rep + 1);
         LAUNCH(c, k_build_pattern, c->sm_count * 8, RELP_THREADS, c->D);
         LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'B', 1, 1);
-        LAUNCH(c, k_debug_fill_column, c->sm_count, RELP_THREADS, c->D, (unsigned long long)seed + rep, r, j);
+        LAUNCH(c, k_debug_fill_column, c->sm_count, RELP_THREADS, c->D, (unsigned long long)seed + rep + 1, r, j);
         CUDA_TRY(cudaEventRecord(e0, c->stream));
         LAUNCH(c, k_pivot_row, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D, 0);
         CUDA_TRY(cudaEventRecord(e1, c->stream));
@@ -1220,7 +1220,7 @@ int relp_debug_k1_dense(relp_ctx* c, uint64_t seed, int32_t reps, float* ms_pivo
         CUDA_TRY(cudaEventSynchronize(e2));
         float a = 0, b = 0;
         cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2);
-        tp += a; tu += b;
+        if (rep >= 0) { tp += a; tu += b; }
         if (check_cuda(c)) return RELP_ERR_CUDA;
         if (sync_state(c)) return RELP_ERR_CUDA;
         if (c->h_st->err) return err_status(c->h_st);

@@ -740,7 +740,9 @@ __device__ __forceinline__ void pivot_bookkeeping(const Dev& D, int j, int r, in
 #ifndef RELP_TMA_INLINE
 #define RELP_TMA_INLINE __forceinline__
 #endif
-#define RELP_K1_STAGES 4           // tiles in the shared-memory ring (STAGES - 1 loads in flight)
+#ifndef RELP_K1_STAGES
+#define RELP_K1_STAGES 6           // tiles in the shared-memory ring (STAGES - 1 loads in flight, 32 KB each)
+#endif
 #define RELP_K1_NC 2               // columns per tile
 __host__ __device__ __forceinline__ size_t k1_smem_bytes(int threads) {
     return 128 + (size_t)RELP_K1_STAGES * 2 * RELP_K1_NC * (2 * (size_t)threads) * 8;
@@ -797,42 +799,44 @@ __device__ RELP_TMA_INLINE void update_dense_tma(const Dev& D, const Grid& g, co
     uint64_t* full = (uint64_t*)smem;                      // tile landed (bulk copies complete)
     uint64_t* empty = full + NS;                           // tile consumed (one arrival per warp)
     int64_t* buf = (int64_t*)(smem + 128);                 // [NS][plane][NC][R]
-    const size_t stage_elems = (size_t)2 * NC * R;
+    const int stage_elems = 2 * NC * R;
     const size_t ld = I.ld;
     const int ntc = ((int)ld + R - 1) / R, nsc = (S + NC - 1) / NC;
     const long long ntiles = (long long)ntc * nsc;
     const long long lo = ntiles * g.bid / g.nb, hi = ntiles * (g.bid + 1) / g.nb;
+    const int count = (int)(hi - lo);                      // tiles of this CTA: (tc, sc) runs on from (lo / nsc, lo % nsc)
     if (threadIdx.x == 0) {
         for (int s = 0; s < NS; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], nwarps); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    auto issue = [&](long long tile) {
-        const long long it = tile - lo;
-        const int st = (int)(it % NS);
-        if (it >= NS) mbar_wait(&empty[st], (uint32_t)((it / NS - 1) & 1));    // every warp is done with the tile that was there
-        const int tc = (int)(tile / nsc), sc = (int)(tile - (long long)tc * nsc);
-        const int row0 = tc * R;
+    // producer state (thread 0): next tile to request
+    int p_it = 0, p_tc = (int)(lo / nsc), p_sc = (int)(lo - (long long)p_tc * nsc), p_st = 0, p_use = 0;
+    auto issue = [&]() {
+        if (p_use > 0) mbar_wait(&empty[p_st], (uint32_t)((p_use - 1) & 1));    // every warp is done with the tile that was there
+        const int row0 = p_tc * R;
         const int rows = (int)ld - row0 < R ? (int)ld - row0 : R;
-        const int ncols = S - sc * NC < NC ? S - sc * NC : NC;
+        const int ncols = S - p_sc * NC < NC ? S - p_sc * NC : NC;
         const uint32_t bytes = (uint32_t)rows * 8u;
-        mbar_expect_tx(&full[st], 2u * (uint32_t)ncols * bytes);
-        int64_t* dst = buf + (size_t)st * stage_elems;
+        mbar_expect_tx(&full[p_st], 2u * (uint32_t)ncols * bytes);
+        int64_t* dst = buf + p_st * stage_elems;
         for (int q = 0; q < ncols; q++) {
-            const size_t src = (size_t)D.slist[sc * NC + q] * ld + row0;
-            bulk_g2s(dst + (size_t)q * R, D.xn + src, bytes, &full[st]);
-            bulk_g2s(dst + (size_t)(NC + q) * R, D.xd + src, bytes, &full[st]);
+            const size_t src = (size_t)D.slist[p_sc * NC + q] * ld + row0;
+            bulk_g2s(dst + q * R, D.xn + src, bytes, &full[p_st]);
+            bulk_g2s(dst + (NC + q) * R, D.xd + src, bytes, &full[p_st]);
         }
+        p_it++;
+        if (++p_sc == nsc) { p_sc = 0; p_tc++; }
+        if (++p_st == NS) { p_st = 0; p_use++; }
     };
-    if (threadIdx.x == 0) for (int i = 0; i < NS - 1 && lo + i < hi; i++) issue(lo + i);
+    if (threadIdx.x == 0) for (int i = 0; i < NS - 1 && i < count; i++) issue();
+    int tc = (int)(lo / nsc), sc = (int)(lo - (long long)tc * nsc), st = 0;
+    uint32_t parity = 0;
     int cur_tc = -1, li0 = 0;
     bool a0 = false, a1 = false, f0 = false, f1 = false;
     Val d0 = val_zero(), d1 = val_zero();
-    for (long long tile = lo; tile < hi; tile++) {
-        const long long it = tile - lo;
-        const int st = (int)(it % NS);
-        if (threadIdx.x == 0 && tile + NS - 1 < hi) issue(tile + NS - 1);
-        const int tc = (int)(tile / nsc), sc = (int)(tile - (long long)tc * nsc);
+    for (int it = 0; it < count; it++) {
+        if (threadIdx.x == 0 && p_it < count) issue();
         if (tc != cur_tc) {
             cur_tc = tc; li0 = tc * R + threadIdx.x * 2;
             longlong2 dn2 = make_longlong2(0, 0), dd2 = make_longlong2(1, 1);
@@ -849,11 +853,11 @@ __device__ RELP_TMA_INLINE void update_dense_tma(const Dev& D, const Grid& g, co
         int kk[NC]; Val pp[NC];
 #pragma unroll
         for (int q = 0; q < NC; q++) if (q < ncols) { kk[q] = D.slist[sc * NC + q]; pp[q] = ld_val(D.psn, D.psd, sc * NC + q); }
-        mbar_wait(&full[st], (uint32_t)((it / NS) & 1));
-        const int64_t* sb = buf + (size_t)st * stage_elems + threadIdx.x * 2;
+        mbar_wait(&full[st], parity);
+        const int64_t* sb = buf + st * stage_elems + threadIdx.x * 2;
         longlong2 xn2[NC], xd2[NC];
 #pragma unroll
-        for (int q = 0; q < NC; q++) if (q < ncols) { xn2[q] = *(const longlong2*)(sb + (size_t)q * R); xd2[q] = *(const longlong2*)(sb + (size_t)(NC + q) * R); }
+        for (int q = 0; q < NC; q++) if (q < ncols) { xn2[q] = *(const longlong2*)(sb + q * R); xd2[q] = *(const longlong2*)(sb + (NC + q) * R); }
         __syncwarp();
         if ((threadIdx.x & 31) == 0) mbar_arrive(&empty[st]);
         if (a0 || a1) {
@@ -880,6 +884,8 @@ __device__ RELP_TMA_INLINE void update_dense_tma(const Dev& D, const Grid& g, co
                 if (od.x != xd2[q].x || od.y != xd2[q].y) *(longlong2*)(D.xd + (size_t)k * ld + li0) = od;
             }
         }
+        if (++sc == nsc) { sc = 0; tc++; }
+        if (++st == NS) { st = 0; parity ^= 1u; }
     }
     __syncthreads();
     if (threadIdx.x == 0) for (int s = 0; s < NS; s++) { mbar_inval(&full[s]); mbar_inval(&empty[s]); }
