@@ -109,6 +109,14 @@ int relp_debug_k1_dense(relp_ctx*, uint64_t seed, int32_t reps, float* ms_pivot_
  * candidate all-gathers.  `nccl_lib` is the dlopen path of libnccl (NULL = "libnccl.so.2"). */
 int relp_comm_unique_id(void* id128, const char* nccl_lib);
 int relp_attach_comm(relp_ctx*, const void* id128, const char* nccl_lib);
+/* Peer transport for the multi-GPU solve (one process per GPU, same node): every rank allocates an
+ * exchange buffer sized for LPs of up to max_m rows and exports it (CUDA IPC handle, 64 bytes); after
+ * the handles have been all-gathered (rank order, 64 bytes each) every rank maps its peers' buffers.
+ * The persistent loop kernel then runs on every rank and exchanges the ratio-test candidates and the
+ * pivot row itself, by stores into peer memory over NVLink -- no NCCL call and no launch per pivot.
+ * The NCCL communicator (or the callbacks) is still used once per solve, at the phase hand-over. */
+int relp_peer_export(relp_ctx*, int32_t max_m, void* handle64);
+int relp_peer_attach(relp_ctx*, const void* handles /* world x 64 bytes */);
 /* Alternative transport: host-staged callbacks (e.g. torch.distributed over gloo).  `send`/`recv`/`buf`
  * are HOST buffers; all-gather concatenates `bytes` from every rank in rank order; all-reduce sums
  * int64 in place.  Return 0 on success.  Used by the world_size-2 CPU tests. */

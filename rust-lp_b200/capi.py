@@ -22,7 +22,7 @@ FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
 # every symbol include/relp_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_debug_k1_dense", "relp_comm_unique_id",
-    "relp_attach_comm", "relp_attach_comm_callbacks", "relp_load_matrix", "relp_carry_create_partially_artificial",
+    "relp_attach_comm", "relp_attach_comm_callbacks", "relp_peer_export", "relp_peer_attach", "relp_load_matrix", "relp_carry_create_partially_artificial",
     "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_carry_from_basis", "relp_price",
     "relp_generate_column", "relp_ratio_test", "relp_change_basis", "relp_generate_element",
     "relp_iterate", "relp_solve_relaxation", "relp_solve_continue", "relp_solve_to_handover",
@@ -80,6 +80,8 @@ def load_library(path=None):
     L.relp_comm_unique_id.argtypes = [vp, C.c_char_p]
     L.relp_attach_comm.argtypes = [vp, vp, C.c_char_p]
     L.relp_attach_comm_callbacks.argtypes = [vp, ALLGATHER_FN, ALLREDUCE_FN, vp]
+    L.relp_peer_export.argtypes = [vp, i32, vp]
+    L.relp_peer_attach.argtypes = [vp, vp]
     L.relp_load_matrix.argtypes = [vp, i32, i32] + [vp] * 8
     L.relp_carry_create_partially_artificial.argtypes = [vp, i32, vp, vp]
     L.relp_carry_from_artificial.argtypes = [vp]
@@ -176,6 +178,15 @@ class Carry:
     def attach_comm_callbacks(self, allgather, allreduce):
         self._cb = (ALLGATHER_FN(allgather), ALLREDUCE_FN(allreduce))     # keep alive
         self._chk(self.L.relp_attach_comm_callbacks(self.h, self._cb[0], self._cb[1], None))
+
+    def peer_export(self, max_m):
+        h = (C.c_ubyte * 64)()
+        self._chk(self.L.relp_peer_export(self.h, max_m, h))
+        return bytes(h)
+
+    def peer_attach(self, handles):
+        buf = b"".join(handles)
+        self._chk(self.L.relp_peer_attach(self.h, buf))
 
     def debug_trace(self, n_ctas=148):
         out = np.zeros((n_ctas, 16), np.uint64)

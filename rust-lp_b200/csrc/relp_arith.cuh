@@ -40,7 +40,7 @@ typedef __int128 i128;
 
 struct Val { int64_t n; int64_t d; };
 
-enum { ERR_NONE = 0, ERR_LIMB_CAPACITY = 1, ERR_HEAP_EXHAUSTED = 2, ERR_ZERO_PIVOT = 4 };
+enum { ERR_NONE = 0, ERR_LIMB_CAPACITY = 1, ERR_HEAP_EXHAUSTED = 2, ERR_ZERO_PIVOT = 4, ERR_PEER = 8, ERR_PEER_BIG = 16 };
 
 // Bump allocator over a region [*top, limit) of the limb heap.
 struct Arena {

@@ -98,6 +98,9 @@ struct relp_ctx {
     int n_slices = 0, a_int = 1, coop_blocks = 0, last_ratio_blocks = 1;
     bool use_persistent = true, use_narrow = true, smem_opt_in = false, upd_opt_in = false;
     long long wide_handoffs = 0;
+    // peer transport (multi-GPU persistent loop): this rank's exchange buffer and the peers' as mapped here
+    DBuf<unsigned char> xbuf; void* peer_base[RELP_MAX_WORLD] = {}; bool peer_mode = false; int peer_max_m = 0;
+    unsigned long long epoch = 0;
     long long k1_exit = 8 << 20;    // option "k1_exit": T x S from which the persistent loop hands a dense update to k_update
     long long k1_min = 300000;      // option "k1_min": T x S from which the wide Carry update is tiled / staged
     DState* h_st = nullptr;       // pinned mirror
@@ -142,6 +145,8 @@ static int err_status(const DState* s) {
     if (s->err & ERR_ZERO_PIVOT) { set_error("Pivot value can't be zero"); return RELP_ERR_ZERO_PIVOT; }
     if (s->err & ERR_LIMB_CAPACITY) { set_error("a numerator/denominator exceeded RELP_OPL limbs"); return RELP_ERR_LIMB_CAPACITY; }
     if (s->err & ERR_HEAP_EXHAUSTED) { set_error("limb heap exhausted: create the context with a larger heap_words"); return RELP_ERR_HEAP_EXHAUSTED; }
+    if (s->err & ERR_PEER_BIG) { set_error("a multi-limb value would have to cross GPUs (ratio or pivot row): solve this LP on one GPU"); return RELP_ERR_LIMB_CAPACITY; }
+    if (s->err & ERR_PEER) { set_error("peer exchange: a rank reported an error or did not answer in time"); return RELP_ERR_COMM; }
     return 0;
 }
 
@@ -230,6 +235,16 @@ static int build_sell(relp_ctx* c, const long long* col_ptr) {
     return build_csr(c, col_ptr[n]);
 }
 
+// layout of an exchange buffer: XHead, then pn | pd | psn | psd (max_m + 1 each), slist, pivot-row bitmap
+static size_t xbuf_layout(int max_m, size_t off[6]) {
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    size_t o = up(sizeof(XHead));
+    for (int a = 0; a < 4; a++) { off[a] = o; o = up(o + (size_t)(max_m + 1) * 8); }
+    off[4] = o; o = up(o + (size_t)(max_m + 1) * 4);
+    off[5] = o; o = up(o + ((size_t)(max_m + 32) / 32 + 1) * 4);
+    return o;
+}
+
 extern "C" {
 
 int relp_abi_version(void) { return 1; }
@@ -267,6 +282,9 @@ void relp_destroy(relp_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+#ifndef RELP_EMUL
+    for (int w = 0; w < RELP_MAX_WORLD; w++) if (c->peer_base[w] && w != c->rank) cudaIpcCloseMemHandle(c->peer_base[w]);
+#endif
     if (c->h_st) cudaFreeHost(c->h_st);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -292,6 +310,40 @@ int relp_attach_comm(relp_ctx* c, const void* id128, const char* nccl_lib) {
     return RELP_OK;
 }
 
+int relp_peer_export(relp_ctx* c, int32_t max_m, void* handle64) {
+#ifdef RELP_EMUL
+    (void)c; (void)max_m; (void)handle64; set_error("peer transport needs GPUs"); return RELP_ERR_ARGUMENT;
+#else
+    if (!c || !handle64 || max_m < 1 || c->world < 2 || c->world > RELP_MAX_WORLD) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    size_t off[6];
+    const size_t bytes = xbuf_layout(max_m, off);
+    if (c->xbuf.alloc(bytes)) return RELP_ERR_CUDA;
+    CUDA_TRY(cudaMemset(c->xbuf.p, 0, bytes));
+    c->peer_max_m = max_m;
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, c->xbuf.p));
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy(handle64, &h, 64);
+    return RELP_OK;
+#endif
+}
+int relp_peer_attach(relp_ctx* c, const void* handles) {
+#ifdef RELP_EMUL
+    (void)c; (void)handles; set_error("peer transport needs GPUs"); return RELP_ERR_ARGUMENT;
+#else
+    if (!c || !handles || !c->xbuf.p) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    for (int w = 0; w < c->world; w++) {
+        if (w == c->rank) { c->peer_base[w] = c->xbuf.p; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char*)handles + 64 * (size_t)w, 64);
+        CUDA_TRY(cudaIpcOpenMemHandle(&c->peer_base[w], h, cudaIpcMemLazyEnablePeerAccess));
+    }
+    c->peer_mode = true;
+    return RELP_OK;
+#endif
+}
 int relp_attach_comm_callbacks(relp_ctx* c, relp_allgather_fn ag, relp_allreduce_fn ar, void* user) {
     if (!c || !ag || !ar) return RELP_ERR_ARGUMENT;
     c->cb_allgather = ag; c->cb_allreduce = ar; c->cb_user = user;
@@ -339,6 +391,10 @@ static void shard_rows(relp_ctx* c, int m) {
 }
 // pricing shard: contiguous SELL slices and contiguous artificial columns
 static void shard_cols(relp_ctx* c, DState* s) {
+    if (c->peer_mode) {     // peer transport: the reduced-cost row is replicated, every rank prices every column
+        s->sl_lo = 0; s->sl_hi = c->n_slices; s->art_lo = 0; s->art_hi = s->phase == 1 ? s->nr_art : 0;
+        return;
+    }
     int per = (c->n_slices + c->world - 1) / c->world;
     s->sl_lo = std::min(c->n_slices, c->rank * per);
     s->sl_hi = std::min(c->n_slices, s->sl_lo + per);
@@ -346,6 +402,23 @@ static void shard_cols(relp_ctx* c, DState* s) {
     int pera = (na + c->world - 1) / c->world;
     s->art_lo = std::min(na, c->rank * pera);
     s->art_hi = std::min(na, s->art_lo + pera);
+}
+
+static void wire_peers(relp_ctx* c) {
+    Dev& D = c->D;
+    D.xworld = 1; D.xrank = 0; D.xepoch = c->epoch; D.xbits = nullptr;
+    for (int w = 0; w < RELP_MAX_WORLD; w++) D.xp[w] = XPeer{};
+    if (!c->peer_mode) return;
+    size_t off[6]; xbuf_layout(c->peer_max_m, off);
+    for (int w = 0; w < c->world; w++) {
+        unsigned char* b = (unsigned char*)c->peer_base[w];
+        XPeer P; P.head = (XHead*)b; P.pn = (int64_t*)(b + off[0]); P.pd = (int64_t*)(b + off[1]);
+        P.psn = (int64_t*)(b + off[2]); P.psd = (int64_t*)(b + off[3]); P.slist = (int*)(b + off[4]); P.pbits = (uint32_t*)(b + off[5]);
+        D.xp[w] = P;
+    }
+    const XPeer& me = D.xp[c->rank];
+    D.xworld = c->world; D.xrank = c->rank; D.xbits = me.pbits;
+    D.pn = me.pn; D.pd = me.pd; D.psn = me.psn; D.psd = me.psd; D.slist = me.slist;
 }
 
 static void wire_dev(relp_ctx* c) {
@@ -360,12 +433,14 @@ static void wire_dev(relp_ctx* c) {
     D.tlist = c->tlist.p; D.slist = c->slist.p; D.worklist = c->worklist.p; D.cand = c->cand.p; D.cand2 = c->cand2.p;
     D.rn = c->rn.p; D.rd = c->rd.p; D.row_ptr = c->row_ptr_d.p; D.csr_ent = c->csr_ent.p;
     D.colbits = c->colbits.p; D.rowbits = c->rowbits.p; D.colsum = c->colsum.p; D.claim = c->claim.p; D.row_art = c->row_art.p;
+    wire_peers(c);
     D.gather = c->gather.p; D.log = c->log.p; D.log_cap = (long long)c->log.n; D.trace = c->trace.p; D.zbits = c->zbits.p;
 }
 
 static const int MAX_PARTIAL_BLOCKS = 2048;
 
 static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
+    if (c->peer_mode && m > c->peer_max_m) { set_error("relp_peer_export was sized for fewer rows"); return RELP_ERR_ARGUMENT; }
     shard_rows(c, m);
     c->ld = std::max(32, (c->mloc + 31) / 32 * 32);      // a warp's 32 rows share one word of colbits
     size_t plane = (size_t)(m + 1) * c->ld;
@@ -563,7 +638,7 @@ static int run_loop(relp_ctx* c, int rule, int64_t max_iters, int tag) {
     int result = RELP_OK;
     int batch = 8;
     for (;;) {
-        if (c->world == 1 && c->use_persistent) {
+        if ((c->world == 1 || c->peer_mode) && c->use_persistent) {
             if (launch_persistent(c, rule, 1 << 20)) return RELP_ERR_CUDA;
         } else {
             for (int b = 0; b < batch; b++) if (enqueue_iteration(c, rule)) return RELP_ERR_COMM;
@@ -616,7 +691,7 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     DState* s = c->h_st;
     memset(s, 0, sizeof(DState));
     s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld; s->n = n; s->nr_art = nr_art;
-    s->phase = 1; s->ncols = nr_art + n; shard_cols(c, s); s->a_int = c->a_int;
+    s->phase = 1; s->ncols = nr_art + n; shard_cols(c, s); s->a_int = c->a_int; c->epoch++;
     s->status = ST_RUNNING; s->last_selected = -1; s->iter = 0; s->iter_limit = ~0ull; s->tag = '1'; s->go = 1;
     s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap; s->k1_min = c->k1_min; s->k1_exit = c->k1_exit;
     init_heap_regions(c, s);
@@ -687,7 +762,7 @@ static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbe
         int cnt = m + 1;
         DBuf<int64_t> all;
         if (all.alloc((size_t)c->world * 2 * cnt)) return RELP_ERR_CUDA;
-        LAUNCH(c, k_recompute_cost_row, grid_for(c, cnt, 2), RELP_THREADS, c->D, c->cost_rows.p, (int)cost_rows.size(), c->D.pn, c->D.pd);
+        LAUNCH(c, k_recompute_cost_row, grid_for(c, cnt, 2), RELP_THREADS, c->D, c->cost_rows.p, (int)cost_rows.size(), c->pnd.p, c->pnd.p + cnt);      // (not D.pn: with the peer transport that lives in the exchange buffer)
         if (comm_allgather(c, c->pnd.p, all.p, 2 * (size_t)cnt * 8)) return RELP_ERR_COMM;
         LAUNCH(c, k_sum_partials, grid_for(c, cnt, 2), RELP_THREADS, c->D, all.p, c->world, cnt, c->zn.p, c->zd.p);
         CUDA_TRY(cudaStreamSynchronize(c->stream));
@@ -797,7 +872,7 @@ static int from_basis(relp_ctx* c, const int32_t* basis_in) {
     DState* s = c->h_st;
     memset(s, 0, sizeof(DState));
     s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld; s->n = n; s->nr_art = 0;
-    s->phase = 2; s->ncols = n; shard_cols(c, s); s->a_int = c->a_int;
+    s->phase = 2; s->ncols = n; shard_cols(c, s); s->a_int = c->a_int; c->epoch++;
     s->status = ST_RUNNING; s->last_selected = -1; s->iter = 0; s->iter_limit = ~0ull; s->tag = 'b'; s->go = 1;
     s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap; s->k1_min = c->k1_min; s->k1_exit = c->k1_exit;
     init_heap_regions(c, s);

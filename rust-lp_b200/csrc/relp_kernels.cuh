@@ -64,6 +64,8 @@ struct DState {
     long long k1_min;              // k_update: T x S from which the Carry update is tiled (dense d: staged through shared memory)
     long long k1_exit;             // persistent loop: T x S from which a dense update is handed to k_update
     int want_wide;                 // persistent loop left with the pivot row ready and the update pending
+    int xflags;                    // peer mode: flags of the last exchange (written by one thread between barriers)
+    unsigned long long xseq;       // peer mode: exchanges done so far (replicated)
     int narrow_skip, narrow_backoff;   // after a pivot that was too big for one CTA, do not try again for a while
     unsigned long long narrow_done;   // iterations completed by CTA 0 alone
     unsigned long long iter, iter_limit;
@@ -76,6 +78,25 @@ struct DState {
 };
 
 struct Cand { Val v; int key; int idx; };
+
+// ---- peer exchange (multi-GPU persistent loop) ----------------------------------------------------
+// Every rank owns one exchange buffer that all its peers map (CUDA IPC over NVLink).  A message is
+// written INTO the receiver's buffer with plain stores, followed by a system-scope fence and a
+// release store of its sequence number; the receiver polls its own memory.  Sequence numbers are
+// (epoch << 40) | xseq with xseq a replicated counter that every rank advances at every exchange, so
+// they never repeat and nothing has to be reset; messages go through a ring of 4 (a sender cannot be
+// more than one exchange ahead of a receiver that has not read yet).
+#define RELP_MAX_WORLD 8
+#define RELP_XNARROW_S 64
+enum { XF_TOOBIG = 1, XF_ERR = 2 };
+struct XSlot { Cand c; int T; int flags; unsigned long long seq; unsigned long long pad[3]; };      // 64 bytes
+struct XRowHdr { int ok, S, W, b_nz; unsigned long long seq; unsigned long long pad; };              // 32 bytes
+struct XNarrowRow { int k[RELP_XNARROW_S]; Val p[RELP_XNARROW_S]; };
+struct XHead { XSlot slot[4][RELP_MAX_WORLD]; XRowHdr rowhdr[4]; XNarrowRow nrow[4]; unsigned long long hello[2][RELP_MAX_WORLD]; };
+struct XPeer {                       // one rank's exchange buffer as mapped in THIS process
+    XHead* head;
+    int64_t* pn; int64_t* pd; int64_t* psn; int64_t* psd; int* slist; uint32_t* pbits;
+};
 
 struct Dev {
     DState* st;
@@ -112,6 +133,10 @@ struct Dev {
     uint32_t* colsum;                         // per column: which blocks of 32 rows MAY be nonzero (bits are only ever set)
     const int* row_art;                       // row -> its artificial column, or -1
     unsigned long long* trace;                // debug: per-CTA arrival time at each barrier (16 slots per CTA)
+    // multi-GPU persistent loop: world > 1 and peers mapped (0 / 1 otherwise)
+    int xworld, xrank; unsigned long long xepoch;
+    uint32_t* xbits;                          // bitmap p_k != 0 of the current pivot row (replicated copy)
+    XPeer xp[RELP_MAX_WORLD];                 // xp[xrank] is this rank's own buffer
 };
 
 #define RELP_THREADS 256          // stage wrappers
@@ -493,7 +518,8 @@ __device__ void stage_update_rc(const Dev& D, const Grid& g, const Inv& I, int r
     const int S = st->S, W = st->W;
     const int off = I.phase == 1 ? I.nr_art : 0;
     Arena ar = persistent(D);
-    const uint32_t* pbits = D.rowbits + (size_t)(r - I.row_lo) * I.wpr;     // p_k != 0 <=> X[r][k] != 0
+    // p_k != 0 <=> X[r][k] != 0; with peers the owner of row r has sent every rank a copy of that row of rowbits
+    const uint32_t* pbits = D.xworld > 1 ? D.xbits : D.rowbits + (size_t)(r - I.row_lo) * I.wpr;
     long long nnz = D.col_ptr[I.n];
     if (S <= RELP_RC_SPARSE_S && (long long)W * 32 <= nnz + 1024
 #ifndef RELP_EMUL
@@ -635,19 +661,21 @@ __device__ void stage_gen_column(const Dev& D, const Grid& g, const Inv& I, int 
 // Stage D -- K1a (owner of row r): p_k = X[r][k] / d_r for k = 0..m, written back to row r and
 // staged in the pivot-row buffer; list of columns with p_k != 0.
 // ---------------------------------------------------------------------------------------------
+// multi: 0 = one GPU; 1 = NCCL path (dense row, summed by an all-reduce); 2 = peer path (the owner
+// writes the row's entries into every rank's exchange buffer, the header follows in k_simplex_loop)
 __device__ void stage_pivot_row(const Dev& D, const Grid& g, const Inv& I, int r, int multi) {
     DState* st = D.st;
     int lr = r - I.row_lo;
     bool owner = lr >= 0 && lr < I.mloc;
-    if (!owner) {   // multi-GPU: contribute zeros to the sum all-reduce that replicates the row
-        for (int k = g.tid; k <= I.m; k += g.nth) { D.pn[k] = 0; D.pd[k] = 0; }
+    if (!owner) {   // NCCL path: contribute zeros to the sum all-reduce that replicates the row
+        if (multi == 1) for (int k = g.tid; k <= I.m; k += g.nth) { D.pn[k] = 0; D.pd[k] = 0; }
         return;
     }
     Val pivot = ld_val(D.dn, D.dd, lr);
     if (pivot.n == 0) { if (g.tid == 0) atomicOr(&st->err, ERR_ZERO_PIVOT); return; }
     Arena ar = persistent(D);
     const size_t ld = I.ld;
-    if (multi) {    // the all-reduce needs p densely
+    if (multi == 1) {    // the all-reduce needs p densely
         for (int k = g.tid; k <= I.m; k += g.nth) {
             size_t e = (size_t)k * ld + lr;
             int64_t x = D.xn[e];
@@ -665,14 +693,34 @@ __device__ void stage_pivot_row(const Dev& D, const Grid& g, const Inv& I, int r
     const uint32_t* rb = D.rowbits + (size_t)lr * I.wpr;
     int len = 0;
     for (int k = g.tid; k <= I.m; k += g.nth) {
-        if (!((rb[k >> 5] >> (k & 31)) & 1u)) continue;
+        if (!((rb[k >> 5] >> (k & 31)) & 1u)) {
+#ifndef RELP_EMUL
+            if (multi == 2 && k == 0) for (int w = 0; w < D.xworld; w++) { D.xp[w].pn[0] = 0; D.xp[w].pd[0] = 1; }   // b_r = 0: bookkeeping reads p_0 everywhere
+#endif
+            continue;
+        }
         size_t e = (size_t)k * ld + lr;
         Val p = val_div(ld_val(D.xn, D.xd, e), pivot, D.heap, ar);
         st_val(D.xn, D.xd, e, p);
-        st_val(D.pn, D.pd, k, p);
-        int s = list_append(&st->S); D.slist[s] = k; D.psn[s] = p.n; D.psd[s] = p.d;
+        int s = list_append(&st->S);
+#ifndef RELP_EMUL
+        if (multi == 2) {
+            if (p.d == 0) atomicOr(&st->err, ERR_PEER_BIG);           // a multi-limb p_k cannot cross GPUs
+            for (int w = 0; w < D.xworld; w++) {                      // own buffer included: D.pn, D.slist ... point into it
+                const XPeer& P = D.xp[w];
+                P.pn[k] = p.n; P.pd[k] = p.d; P.slist[s] = k; P.psn[s] = p.n; P.psd[s] = p.d;
+            }
+        } else
+#endif
+        { st_val(D.pn, D.pd, k, p); D.slist[s] = k; D.psn[s] = p.n; D.psd[s] = p.d; }
         if (k > 0) len += (int)(D.row_ptr[k] - D.row_ptr[k - 1]);
     }
+#ifndef RELP_EMUL
+    if (multi == 2) {   // the row's bitmap (reduced-cost update), then make everything visible before the header goes out
+        for (int w0 = g.tid; w0 < I.wpr; w0 += g.nth) { const uint32_t bits = rb[w0]; for (int w = 0; w < D.xworld; w++) D.xp[w].pbits[w0] = bits; }
+        __threadfence_system();
+    }
+#endif
     if (len) atomicAdd(&st->W, len);
 }
 
@@ -731,7 +779,7 @@ __device__ __forceinline__ void pivot_bookkeeping(const Dev& D, int j, int r, in
         LogEntry e; e.tag = st->tag; e.j = j; e.r = r; e.leaving = leaving; e.T = Tl; e.S = Sl;
         D.log[st->iter] = e;
     }
-    unsigned long long rows = (unsigned long long)(T - 1 + (rc.n != 0));
+    unsigned long long rows = (unsigned long long)((T > 0 ? T - 1 : 0) + (rc.n != 0));     // T = 0: a peer rank without a touched row
     st->sum_T += rows; st->sum_S += (unsigned long long)S; st->sum_TS += rows * (unsigned long long)S;
 }
 
@@ -1040,6 +1088,115 @@ static inline unsigned long long gtime() { return 0; }
 
 #ifndef RELP_EMUL
 // ---------------------------------------------------------------------------------------------
+// Peer exchange primitives (see XHead).  All of them are called by every thread of ONE CTA.
+// ---------------------------------------------------------------------------------------------
+#ifndef RELP_PEER_TIMEOUT_NS
+#define RELP_PEER_TIMEOUT_NS 2000000000ull
+#endif
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+// spin until *flag == want; a peer that never answers costs RELP_PEER_TIMEOUT_NS and an error, not a hang
+__device__ __forceinline__ bool peer_wait(const unsigned long long* flag, unsigned long long want, DState* st) {
+    const unsigned long long t0 = gtime();
+    while (ld_acquire_sys(flag) != want) {
+        if (gtime() - t0 > RELP_PEER_TIMEOUT_NS) { atomicOr(&st->err, ERR_PEER); return false; }
+        __nanosleep(20);
+    }
+    return true;
+}
+__device__ __forceinline__ Cand ldcv_cand(const Cand* c) {
+    Cand o;
+    o.v.n = __ldcv((const long long*)&c->v.n); o.v.d = __ldcv((const long long*)&c->v.d);
+    o.key = __ldcv(&c->key); o.idx = __ldcv(&c->idx);
+    return o;
+}
+
+// All-gather of one ratio-test candidate per rank + (T, flags), reduced identically everywhere.
+// Returns the global winner to every thread; Tmax = largest local T, any = OR of the flags.
+__device__ Cand peer_exchange_cand(const Dev& D, Cand mine, int T, int flags, int& Tmax, int& any) {
+    __shared__ XSlot xs[RELP_MAX_WORLD];
+    DState* st = D.st;
+    __syncthreads();                                    // previous readers of xs / writers of xseq are done
+    const unsigned long long x = *(volatile unsigned long long*)&st->xseq + 1, seq = (D.xepoch << 40) | x;
+    const int ring = (int)(x & 3), w = threadIdx.x;
+    if (mine.idx >= 0 && mine.v.d == 0) flags |= XF_ERR;          // a multi-limb ratio cannot cross GPUs (handle is rank-local)
+    if (st->err) flags |= XF_ERR;
+    if (w < D.xworld) {
+        XSlot* dst = &D.xp[w].head->slot[ring][D.xrank];
+        dst->c = mine; dst->T = T; dst->flags = flags;
+        __threadfence_system();
+        st_release_sys(&dst->seq, seq);
+        const XSlot* src = &D.xp[D.xrank].head->slot[ring][w];
+        XSlot got; got.c = cand_none(); got.T = 0; got.flags = XF_ERR;
+        if (peer_wait(&src->seq, seq, st)) { got.c = ldcv_cand(&src->c); got.T = __ldcv(&src->T); got.flags = __ldcv(&src->flags); }
+        xs[w] = got;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) st->xseq = x;
+    Cand best = cand_none(); Tmax = 0; any = 0;
+    for (int q = 0; q < D.xworld; q++) {
+        any |= xs[q].flags;
+        if (xs[q].T > Tmax) Tmax = xs[q].T;
+        if (!(xs[q].flags & XF_ERR) && cand_better(xs[q].c, best, ARG_RATIO, D.heap)) best = xs[q].c;
+    }
+    if ((any & XF_ERR) && threadIdx.x == 0) atomicOr(&st->err, (mine.idx >= 0 && mine.v.d == 0) ? ERR_PEER_BIG : ERR_PEER);
+    return best;
+}
+
+// First launch of a solve: nobody writes into a peer's ring before every rank has arrived in the new solve
+// (and so has read everything the previous one sent).
+__device__ void peer_hello(const Dev& D) {
+    DState* st = D.st;
+    const unsigned long long seq = D.xepoch << 40;
+    const int w = threadIdx.x, par = (int)(D.xepoch & 1);
+    if (w < D.xworld) {
+        st_release_sys(&D.xp[w].head->hello[par][D.xrank], seq);
+        peer_wait(&D.xp[D.xrank].head->hello[par][w], seq, st);
+    }
+    __syncthreads();
+}
+
+// ring slot of the NEXT exchange (the narrow pivot row's entries are written there before its header)
+__device__ __forceinline__ int peer_next_ring(const Dev& D) {
+    __syncthreads();
+    return (int)((*(volatile unsigned long long*)&D.st->xseq + 1) & 3);
+}
+
+// Pivot-row header: the owner posts (ok, S, W, b_nz) to every peer after the row's entries are on their
+// way (every writer has executed a system fence); the others wait for it.  Returns the header.
+__device__ XRowHdr peer_row_header(const Dev& D, bool owner, int ok, int S, int W, int b_nz) {
+    __shared__ XRowHdr xh;
+    DState* st = D.st;
+    __syncthreads();
+    const unsigned long long x = *(volatile unsigned long long*)&st->xseq + 1, seq = (D.xepoch << 40) | x;
+    const int ring = (int)(x & 3), w = threadIdx.x;
+    if (owner) {
+        if (w < D.xworld && w != D.xrank) {
+            XRowHdr* dst = &D.xp[w].head->rowhdr[ring];
+            dst->ok = ok; dst->S = S; dst->W = W; dst->b_nz = b_nz;
+            __threadfence_system();
+            st_release_sys(&dst->seq, seq);
+        }
+        if (w == 0) { xh.ok = ok; xh.S = S; xh.W = W; xh.b_nz = b_nz; }
+    } else if (w == 0) {
+        const XRowHdr* src = &D.xp[D.xrank].head->rowhdr[ring];
+        xh.ok = -1; xh.S = 0; xh.W = 0; xh.b_nz = 0;
+        if (peer_wait(&src->seq, seq, st)) { xh.ok = __ldcv(&src->ok); xh.S = __ldcv(&src->S); xh.W = __ldcv(&src->W); xh.b_nz = __ldcv(&src->b_nz); }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) st->xseq = x;
+    return xh;
+}
+#endif
+
+#ifndef RELP_EMUL
+// ---------------------------------------------------------------------------------------------
 // Narrow iteration.  While B^-1 is sparse a pivot touches a few dozen Carry elements and a few
 // hundred reduced costs: spreading that over 148 CTAs buys nothing and costs a grid-wide barrier
 // after every stage.  CTA 0 therefore runs column generation, ratio test, pivot row, Carry update
@@ -1083,11 +1240,13 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
     DState* st = D.st;
     const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarps = nt >> 5;
     Grid g0; g0.tid = tid; g0.nth = nt; g0.bid = 0; g0.nb = 1;
+    const bool peers = D.xworld > 1;       // the same LP on several GPUs: this rank holds rows [row_lo, row_lo + mloc)
     const int j = col.idx;
     const Val rc = col.v;
     const ColumnRef c = column_ref(D, I, j);
     const int nent = c.unit_row >= 0 ? 1 : (int)(c.t1 - c.t0);
     const int wsc = I.wsc;
+    // limits that depend on the LP alone: every rank decides the same
     if (wsc > RELP_NARROW_SUMW || nent > RELP_NARROW_ENT || I.wpr > RELP_NARROW_PBW) return 1;
     // (a) which blocks of 32 rows can d = B^-1 a_j touch?   row_idx -> colsum, one entry per thread
     for (int w = tid; w < wsc; w += nt) sm.sum[w] = 0;
@@ -1115,11 +1274,13 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
     }
     __syncthreads();
     NT(1);
-    if (sm.nblk > RELP_NARROW_BLOCKS) return 1;
+    // limits that depend on this rank's rows: alone, give up now; with peers, say so in the exchange
+    bool toobig = sm.nblk > RELP_NARROW_BLOCKS;
+    if (toobig && !peers) return 1;
     // (b) d, the rows with d_i != 0 and the ratio test; only scratch (dn, tlist) is written
     Arena tr = transient(D);
     Cand best = cand_none();
-    for (int q = warp; q < sm.nblk; q += nwarps) {
+    if (!toobig) for (int q = warp; q < sm.nblk; q += nwarps) {
         const int rb = sm.blk[q], li = rb * 32 + lane;
         // b_i and the row's basis column are requested before the column is generated: only rows with
         // d_i > 0 need them, but asking now takes a round trip off the critical path
@@ -1139,44 +1300,91 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
     NT(2);
     Cand row = block_argmin(best, ARG_RATIO, D.heap);       // (block barriers inside)
     NT(3);
-    if (row.idx < 0) { if (tid == 0) commit_row(st, row); return 2; }
     const int T = sm.T;
+    int Tmax = T;
+    if (peers) {
+        int any = 0;
+        row = peer_exchange_cand(D, row, T, (toobig || T > RELP_NARROW_T) ? XF_TOOBIG : 0, Tmax, any);
+        if (any & XF_ERR) return 2;
+        if (any & XF_TOOBIG) return 1;
+    }
+    if (row.idx < 0) { if (tid == 0) commit_row(st, row); return 2; }
     if (T > RELP_NARROW_T) return 1;
     // (c) the pivot row into scratch: p_k = X[r][k] / d_r, its bitmap, and the CSR row of A behind each k
     const int r = row.idx, lr = r - I.row_lo;
-    for (int t = tid; t < T; t += nt) if (sm.tl[t] == lr) sm.pivot = sm.dv[t];
-    __syncthreads();
-    const Val pivot = sm.pivot;
-    if (pivot.n == 0) { if (tid == 0) atomicOr(&st->err, ERR_ZERO_PIVOT); return 2; }
+    const bool owner = lr >= 0 && lr < I.mloc;
     Arena ar = persistent(D);
-    const uint32_t* rbits = D.rowbits + (size_t)lr * I.wpr;
     const size_t ld = I.ld;
-    for (int w = tid; w < I.wpr; w += nt) {          // the row's nonzero columns first: nothing is divided for a row that is too long
-        uint32_t bits = rbits[w];
-        sm.pb[w] = bits;
-        while (bits) {
-            int k = w * 32 + ctz32(bits); bits &= bits - 1;
-            int q = atomicAdd(&sm.S, 1);
-            if (q < RELP_NARROW_S) sm.sl[q] = k;
+    int ok = 1;                                               // 1 go, 0 too big for one CTA, -1 error
+    if (owner) {
+        for (int t = tid; t < T; t += nt) if (sm.tl[t] == lr) sm.pivot = sm.dv[t];
+        __syncthreads();
+        const Val pivot = sm.pivot;
+        if (pivot.n == 0) { if (tid == 0) atomicOr(&st->err, ERR_ZERO_PIVOT); ok = -1; }
+        const uint32_t* rbits = D.rowbits + (size_t)lr * I.wpr;
+        if (ok > 0) for (int w = tid; w < I.wpr; w += nt) {   // the row's nonzero columns first: nothing is divided for a row that is too long
+            uint32_t bits = rbits[w];
+            sm.pb[w] = bits;
+            while (bits) {
+                int k = w * 32 + ctz32(bits); bits &= bits - 1;
+                int q = atomicAdd(&sm.S, 1);
+                if (q < RELP_NARROW_S) sm.sl[q] = k;
+            }
         }
+        __syncthreads();
+        const int S = sm.S;
+        if (ok > 0 && (S > RELP_NARROW_S || (long long)Tmax * S > RELP_NARROW_TS)) ok = 0;
+        if (ok > 0) for (int q = tid; q < S; q += nt) {           // one thread per nonzero column
+            const int k = sm.sl[q];
+            Val x = ld_val(D.xn, D.xd, (size_t)k * ld + lr);
+            long long lo = k > 0 ? D.row_ptr[k - 1] : 0, hi = k > 0 ? D.row_ptr[k] : 0;
+            sm.pv[q] = val_div(x, pivot, D.heap, ar);
+            sm.plo[q] = lo; sm.pre[q] = (int)(hi - lo);
+            atomicAdd(&sm.W, (int)(hi - lo));
+            if (k == 0) sm.b_nz = 1;
+        }
+        __syncthreads();
+        if (ok > 0) {
+            const long long nnz = D.col_ptr[I.n];
+            const bool sparse = S <= RELP_RC_SPARSE_S && (long long)sm.W * 32 <= nnz + 1024;
+            // with peers the reduced costs must go through the CSR path: the other ranks do not hold this row's bitmap
+            if (rc.n != 0 && (sparse ? sm.W > RELP_NARROW_W : (peers || (I.sl_hi - I.sl_lo) > 256))) ok = 0;
+        }
+        if (peers) {
+            const int ring = peer_next_ring(D);
+            if (ok > 0) for (int it = tid; it < S * D.xworld; it += nt) {
+                const int w = it / S, q = it - w * S;
+                if (w == D.xrank) continue;
+                if (sm.pv[q].d == 0) ok = -2;                     // a multi-limb p_k cannot cross GPUs
+                XNarrowRow* dst = &D.xp[w].head->nrow[ring];
+                dst->k[q] = sm.sl[q]; dst->p[q] = sm.pv[q];
+                __threadfence_system();
+            }
+            ok = __syncthreads_or(ok == -2) ? -2 : ok;
+            if (ok == -2 && tid == 0) atomicOr(&st->err, ERR_PEER_BIG);
+            peer_row_header(D, true, ok, S, sm.W, sm.b_nz);
+        }
+    } else {
+        const int ring = peer_next_ring(D);
+        const XRowHdr h = peer_row_header(D, false, 0, 0, 0, 0);
+        ok = h.ok;
+        if (ok > 0) {
+            if (tid == 0) { sm.S = h.S; sm.W = h.W; sm.b_nz = h.b_nz; }
+            const XNarrowRow* src = &D.xp[D.xrank].head->nrow[ring];
+            for (int q = tid; q < h.S; q += nt) {
+                const int k = __ldcv(&src->k[q]);
+                Val p; p.n = __ldcv((const long long*)&src->p[q].n); p.d = __ldcv((const long long*)&src->p[q].d);
+                long long lo = k > 0 ? D.row_ptr[k - 1] : 0, hi = k > 0 ? D.row_ptr[k] : 0;
+                sm.sl[q] = k; sm.pv[q] = p; sm.plo[q] = lo; sm.pre[q] = (int)(hi - lo);
+            }
+        }
+        __syncthreads();
     }
-    __syncthreads();
+    if (ok < 0) { if (peers && tid == 0) atomicOr(&st->err, ERR_PEER); return 2; }
+    if (ok == 0) return 1;
     const int S = sm.S;
-    if (S > RELP_NARROW_S || (long long)T * S > RELP_NARROW_TS) return 1;
-    for (int q = tid; q < S; q += nt) {               // one thread per nonzero column
-        const int k = sm.sl[q];
-        Val x = ld_val(D.xn, D.xd, (size_t)k * ld + lr);
-        long long lo = k > 0 ? D.row_ptr[k - 1] : 0, hi = k > 0 ? D.row_ptr[k] : 0;
-        sm.pv[q] = val_div(x, pivot, D.heap, ar);
-        sm.plo[q] = lo; sm.pre[q] = (int)(hi - lo);
-        atomicAdd(&sm.W, (int)(hi - lo));
-        if (k == 0) sm.b_nz = 1;
-    }
-    __syncthreads();
     const int W = sm.W;
-    const long long nnz = D.col_ptr[I.n];
-    const bool rc_sparse = S <= RELP_RC_SPARSE_S && (long long)W * 32 <= nnz + 1024;
-    if (rc.n != 0 && (rc_sparse ? W > RELP_NARROW_W : (I.sl_hi - I.sl_lo) > 256)) return 1;
+    const bool rc_sparse = S <= RELP_RC_SPARSE_S && (long long)W * 32 <= D.col_ptr[I.n] + 1024;
     NT(4);
     // (d) commit: row r in place and in the pivot-row buffer, then everything that depends on p
     if (tid == 0) {
@@ -1188,7 +1396,7 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
     }
     for (int q = tid; q < S; q += nt) {
         int k = sm.sl[q];
-        st_val(D.xn, D.xd, (size_t)k * ld + lr, sm.pv[q]);
+        if (owner) st_val(D.xn, D.xd, (size_t)k * ld + lr, sm.pv[q]);
         st_val(D.pn, D.pd, k, sm.pv[q]);
         D.slist[q] = k;
     }
@@ -1270,6 +1478,13 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
     const int mode = rule == RULE_DANTZIG ? ARG_DANTZIG : ARG_FIRST;
     // The reduced-cost row is computed once (full pricing pass) and then kept current by every
     // pivot; `rc_valid` is cleared by whatever replaces the cost row or the basis from outside.
+#ifndef RELP_EMUL
+    if (D.xworld > 1 && st->xseq == 0) {
+        if (g.bid == 0) peer_hello(D);
+        GRID_SYNC();
+        if (st->err) return;
+    }
+#endif
     if (!st->rc_valid) {
         stage_price(D, g, I, mode, smem_words, 1);
         GRID_SYNC();
@@ -1337,13 +1552,46 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
         stage_gen_column(D, g, I, col.idx);
         GRID_SYNC();
         t2 = gtime();
-        Cand row = reduce_candidates(D.cand2, g.nb, ARG_RATIO, D.heap);
+        Cand row;
+#ifndef RELP_EMUL
+        if (D.xworld > 1) {
+            // this rank's winner against the other ranks' (CTA 0 talks to the peers, the grid learns the result
+            // through gather[0] after one more barrier)
+            if (g.bid == 0) {
+                Cand mine = reduce_candidates(D.cand2, g.nb, ARG_RATIO, D.heap);
+                int Tmax = 0, any = 0;
+                Cand win = peer_exchange_cand(D, mine, st->T, 0, Tmax, any);
+                if (threadIdx.x == 0) { D.gather[0] = win; st->xflags = any; }
+            }
+            GRID_SYNC();
+            if (st->xflags & XF_ERR) break;
+            row = D.gather[0];
+        } else
+#endif
+        row = reduce_candidates(D.cand2, g.nb, ARG_RATIO, D.heap);
         if (g.tid == 0) commit_row(st, row);
         if (row.idx < 0) break;
         TRACE(6);
-        stage_pivot_row(D, g, I, row.idx, 0);
+        stage_pivot_row(D, g, I, row.idx, D.xworld > 1 ? 2 : 0);
         TRACE(7);
         GRID_SYNC();
+#ifndef RELP_EMUL
+        if (D.xworld > 1) {
+            // the owner's entries are on their way (each writer fenced at system scope before the barrier
+            // above); its CTA 0 now posts the header, every other rank waits for it and adopts S and W
+            if (g.bid == 0) {
+                const int lr = row.idx - I.row_lo;
+                const bool owner = lr >= 0 && lr < I.mloc;
+                const XRowHdr h = peer_row_header(D, owner, st->err ? -1 : 1, st->S, st->W, 0);
+                if (threadIdx.x == 0) {
+                    if (h.ok < 0) atomicOr(&st->err, ERR_PEER);
+                    else if (!owner) { st->S = h.S; st->W = h.W; }
+                }
+            }
+            GRID_SYNC();
+            if (st->err) break;
+        }
+#endif
         TRACE(8);
         t3 = gtime();
 #ifndef RELP_EMUL

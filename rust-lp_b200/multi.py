@@ -57,21 +57,29 @@ class ShardedCarry:
     """The same interface as capi.Carry for the calls a sharded solve needs; every rank calls every
     method (they are collective)."""
 
-    def __init__(self, provider, device=None, heap_words=0, lib_path=None, transport="nccl"):
+    def __init__(self, provider, device=None, heap_words=0, lib_path=None, transport="peer"):
         import torch.distributed as dist
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
         dev = device if device is not None else int(os.environ.get("LOCAL_RANK", self.rank))
         self.c = capi.Carry(provider, device=dev, rank=self.rank, world=self.world, heap_words=heap_words,
                             lib_path=lib_path)
-        self.c.set_option("persistent", 0)
+        self.transport = transport if self.world > 1 else "single"
         if self.world > 1:
-            if transport == "nccl":
+            if transport in ("nccl", "peer"):
                 lib = find_nccl()
                 box = [self.c.comm_unique_id(lib) if self.rank == 0 else None]
                 dist.broadcast_object_list(box, src=0)
                 self.c.attach_comm(box[0], lib)
             else:
                 self.c.attach_comm_callbacks(*gloo_callbacks())
+            if transport == "peer":
+                # exchange buffers mapped into every peer (CUDA IPC): the persistent loop kernel runs on every
+                # rank and talks to its peers by stores over NVLink; NCCL is only used at the phase hand-over
+                handles = [None] * self.world
+                dist.all_gather_object(handles, self.c.peer_export(provider.m))
+                self.c.peer_attach(handles)
+            else:
+                self.c.set_option("persistent", 0)
 
     def solve_relaxation(self, *a, **k):
         return self.c.solve_relaxation(*a, **k)

@@ -21,16 +21,23 @@ WORKER = textwrap.dedent('''
     local = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    for (m, n, k) in [(60, 400, 6), (203, 2000, 20), (2000, 20000, 20)]:
-        pa = synthetic_lp(m, n, k, "tu")
-        o = coracle.COracle(pa); st_o = o.solve(1, 2)
-        sc = multi.ShardedCarry(pa, device=local, heap_words=1 << 22)
-        st = sc.solve_relaxation()
-        assert st == parity.STATUS[st_o], (st, st_o)
-        assert [x[:4] for x in sc.log()] == [x[:4] for x in parity.oracle_log(o)]
-        assert sc.get_objective_function_value() == o.objective()
-        assert sc.current_bfs() == o.current_bfs()
-        sc.close(); del o
+    # "peer": the persistent loop on every rank, exchanges by stores into peer memory (narrow and wide pivots:
+    # the second pass forbids narrow iterations); "nccl": one launch per stage with collectives in between
+    for transport, opts in (("peer", {}), ("peer", {"narrow": 0}), ("nccl", {})):
+        for (m, n, k) in [(60, 400, 6), (203, 2000, 20), (2000, 20000, 20)]:
+            pa = synthetic_lp(m, n, k, "tu")
+            o = coracle.COracle(pa); st_o = o.solve(1, 2)
+            sc = multi.ShardedCarry(pa, device=local, heap_words=1 << 22, transport=transport)
+            for name, value in opts.items():
+                sc.c.set_option(name, value)
+            st = sc.solve_relaxation()
+            assert st == parity.STATUS[st_o], (transport, st, st_o)
+            assert [x[:4] for x in sc.log()] == [x[:4] for x in parity.oracle_log(o)], transport
+            assert sc.get_objective_function_value() == o.objective()
+            assert sc.current_bfs() == o.current_bfs()
+            st2 = sc.solve_relaxation()          # a second solve in the same context (new epoch of the exchange ring)
+            assert st2 == st and sc.get_objective_function_value() == o.objective()
+            sc.close(); del o
     print("rank", dist.get_rank(), "ok", flush=True)
     dist.barrier(); dist.destroy_process_group(); os._exit(0)
 ''') % (ROOT, ROOT)
