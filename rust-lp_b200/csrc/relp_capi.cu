@@ -604,26 +604,27 @@ static int check_cuda(relp_ctx* c) {
 
 static int launch_persistent(relp_ctx* c, int rule, int max_iters) {
 #ifdef RELP_EMUL
-    k_simplex_loop(c->D, rule, max_iters, 0, 0);
+    k_simplex_loop<false>(c->D, rule, max_iters, 0, 0);
     c->launches++;
     return 0;
 #else
     if (c->coop_blocks == 0) {
         int per_sm = 0;
-        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_simplex_loop, RELP_PTHREADS, 0));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_simplex_loop<false>, RELP_PTHREADS, 0));
         if (per_sm < 1) { set_error("persistent kernel does not fit on an SM"); return RELP_ERR_CUDA; }
         c->coop_blocks = c->sm_count;        // one CTA per SM
     }
     int sw = zbits_smem_words(c);
     size_t smem = (size_t)sw * 4;
     if (smem > 40 * 1024 && !c->smem_opt_in) {
-        CUDA_TRY(cudaFuncSetAttribute(k_simplex_loop, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        CUDA_TRY(cudaFuncSetAttribute(k_simplex_loop<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        CUDA_TRY(cudaFuncSetAttribute(k_simplex_loop<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         CUDA_TRY(cudaFuncSetAttribute(k_price, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         c->smem_opt_in = true;
     }
     int narrow = c->use_narrow ? 1 : 0;
     void* args[] = { (void*)&c->D, (void*)&rule, (void*)&max_iters, (void*)&sw, (void*)&narrow };
-    CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_simplex_loop, dim3(c->coop_blocks), dim3(RELP_PTHREADS), args, smem, c->stream));
+    CUDA_TRY(cudaLaunchCooperativeKernel(c->peer_mode ? (void*)k_simplex_loop<true> : (void*)k_simplex_loop<false>, dim3(c->coop_blocks), dim3(RELP_PTHREADS), args, smem, c->stream));
     c->launches++;
     return 0;
 #endif

@@ -89,10 +89,10 @@ struct Cand { Val v; int key; int idx; };
 #define RELP_MAX_WORLD 8
 #define RELP_XNARROW_S 64
 enum { XF_TOOBIG = 1, XF_ERR = 2 };
-struct XSlot { Cand c; int T; int flags; unsigned long long seq; unsigned long long pad[3]; };      // 64 bytes
+struct XSlot { Cand c; int T; int flags; int ok, S, W, b_nz; unsigned long long seq; unsigned long long pad; };      // 64 bytes
 struct XRowHdr { int ok, S, W, b_nz; unsigned long long seq; unsigned long long pad; };              // 32 bytes
 struct XNarrowRow { int k[RELP_XNARROW_S]; Val p[RELP_XNARROW_S]; };
-struct XHead { XSlot slot[4][RELP_MAX_WORLD]; XRowHdr rowhdr[4]; XNarrowRow nrow[4]; unsigned long long hello[2][RELP_MAX_WORLD]; };
+struct XHead { XSlot slot[4][RELP_MAX_WORLD]; XRowHdr rowhdr[4]; XNarrowRow nrow[4][RELP_MAX_WORLD]; unsigned long long hello[2][RELP_MAX_WORLD]; };
 struct XPeer {                       // one rank's exchange buffer as mapped in THIS process
     XHead* head;
     int64_t* pn; int64_t* pd; int64_t* psn; int64_t* psd; int* slist; uint32_t* pbits;
@@ -1103,12 +1103,12 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 }
 // spin until *flag == want; a peer that never answers costs RELP_PEER_TIMEOUT_NS and an error, not a hang
 __device__ __forceinline__ bool peer_wait(const unsigned long long* flag, unsigned long long want, DState* st) {
+    if (ld_acquire_sys(flag) == want) return true;
     const unsigned long long t0 = gtime();
-    while (ld_acquire_sys(flag) != want) {
-        if (gtime() - t0 > RELP_PEER_TIMEOUT_NS) { atomicOr(&st->err, ERR_PEER); return false; }
-        __nanosleep(20);
-    }
-    return true;
+    unsigned spins = 0;
+    while (*(const volatile unsigned long long*)flag != want)
+        if ((++spins & 1023u) == 0 && gtime() - t0 > RELP_PEER_TIMEOUT_NS) { atomicOr(&st->err, ERR_PEER); return false; }
+    return ld_acquire_sys(flag) == want;       // the acquire that orders the payload reads
 }
 __device__ __forceinline__ Cand ldcv_cand(const Cand* c) {
     Cand o;
@@ -1130,8 +1130,7 @@ __device__ Cand peer_exchange_cand(const Dev& D, Cand mine, int T, int flags, in
     if (w < D.xworld) {
         XSlot* dst = &D.xp[w].head->slot[ring][D.xrank];
         dst->c = mine; dst->T = T; dst->flags = flags;
-        __threadfence_system();
-        st_release_sys(&dst->seq, seq);
+        st_release_sys(&dst->seq, seq);            // release: orders this thread's stores above before the flag
         const XSlot* src = &D.xp[D.xrank].head->slot[ring][w];
         XSlot got; got.c = cand_none(); got.T = 0; got.flags = XF_ERR;
         if (peer_wait(&src->seq, seq, st)) { got.c = ldcv_cand(&src->c); got.T = __ldcv(&src->T); got.flags = __ldcv(&src->flags); }
@@ -1162,12 +1161,6 @@ __device__ void peer_hello(const Dev& D) {
     __syncthreads();
 }
 
-// ring slot of the NEXT exchange (the narrow pivot row's entries are written there before its header)
-__device__ __forceinline__ int peer_next_ring(const Dev& D) {
-    __syncthreads();
-    return (int)((*(volatile unsigned long long*)&D.st->xseq + 1) & 3);
-}
-
 // Pivot-row header: the owner posts (ok, S, W, b_nz) to every peer after the row's entries are on their
 // way (every writer has executed a system fence); the others wait for it.  Returns the header.
 __device__ XRowHdr peer_row_header(const Dev& D, bool owner, int ok, int S, int W, int b_nz) {
@@ -1180,7 +1173,6 @@ __device__ XRowHdr peer_row_header(const Dev& D, bool owner, int ok, int S, int 
         if (w < D.xworld && w != D.xrank) {
             XRowHdr* dst = &D.xp[w].head->rowhdr[ring];
             dst->ok = ok; dst->S = S; dst->W = W; dst->b_nz = b_nz;
-            __threadfence_system();
             st_release_sys(&dst->seq, seq);
         }
         if (w == 0) { xh.ok = ok; xh.S = S; xh.W = W; xh.b_nz = b_nz; }
@@ -1232,6 +1224,7 @@ struct NarrowSmem {
     Val pivot;
 };
 
+template <bool PEERS>
 __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int smem_words) {
     __shared__ NarrowSmem sm;
 #if defined(RELP_WTRACE)
@@ -1240,7 +1233,7 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
     DState* st = D.st;
     const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarps = nt >> 5;
     Grid g0; g0.tid = tid; g0.nth = nt; g0.bid = 0; g0.nb = 1;
-    const bool peers = D.xworld > 1;       // the same LP on several GPUs: this rank holds rows [row_lo, row_lo + mloc)
+    constexpr bool peers = PEERS;          // the same LP on several GPUs: this rank holds rows [row_lo, row_lo + mloc)
     const int j = col.idx;
     const Val rc = col.v;
     const ColumnRef c = column_ref(D, I, j);
@@ -1301,26 +1294,23 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
     Cand row = block_argmin(best, ARG_RATIO, D.heap);       // (block barriers inside)
     NT(3);
     const int T = sm.T;
-    int Tmax = T;
-    if (peers) {
-        int any = 0;
-        row = peer_exchange_cand(D, row, T, (toobig || T > RELP_NARROW_T) ? XF_TOOBIG : 0, Tmax, any);
-        if (any & XF_ERR) return 2;
-        if (any & XF_TOOBIG) return 1;
+    if (!peers) {
+        if (row.idx < 0) { if (tid == 0) commit_row(st, row); return 2; }
+        if (T > RELP_NARROW_T) return 1;
     }
-    if (row.idx < 0) { if (tid == 0) commit_row(st, row); return 2; }
-    if (T > RELP_NARROW_T) return 1;
-    // (c) the pivot row into scratch: p_k = X[r][k] / d_r, its bitmap, and the CSR row of A behind each k
-    const int r = row.idx, lr = r - I.row_lo;
-    const bool owner = lr >= 0 && lr < I.mloc;
+    // (c) the pivot row into scratch: p_k = X[r][k] / d_r, its bitmap, and the CSR row of A behind each k.
+    // With peers every rank does this for ITS OWN best row, speculatively, and sends the result along with the
+    // candidate: one exchange per pivot instead of two (the row is a handful of entries here).
     Arena ar = persistent(D);
     const size_t ld = I.ld;
-    int ok = 1;                                               // 1 go, 0 too big for one CTA, -1 error
-    if (owner) {
+    int ok = 1;                                               // 1 go, 0 too big for one CTA, < 0 error
+    const bool have = row.idx >= 0 && !toobig && T <= RELP_NARROW_T;
+    int lr = have ? row.idx - I.row_lo : -1;
+    if (have) {
         for (int t = tid; t < T; t += nt) if (sm.tl[t] == lr) sm.pivot = sm.dv[t];
         __syncthreads();
         const Val pivot = sm.pivot;
-        if (pivot.n == 0) { if (tid == 0) atomicOr(&st->err, ERR_ZERO_PIVOT); ok = -1; }
+        if (pivot.n == 0) { if (!peers && tid == 0) atomicOr(&st->err, ERR_ZERO_PIVOT); ok = -1; }
         const uint32_t* rbits = D.rowbits + (size_t)lr * I.wpr;
         if (ok > 0) for (int w = tid; w < I.wpr; w += nt) {   // the row's nonzero columns first: nothing is divided for a row that is too long
             uint32_t bits = rbits[w];
@@ -1332,13 +1322,13 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
             }
         }
         __syncthreads();
-        const int S = sm.S;
-        if (ok > 0 && (S > RELP_NARROW_S || (long long)Tmax * S > RELP_NARROW_TS)) ok = 0;
-        if (ok > 0) for (int q = tid; q < S; q += nt) {           // one thread per nonzero column
+        const int S0 = sm.S;
+        if (ok > 0 && (S0 > RELP_NARROW_S || (!peers && (long long)T * S0 > RELP_NARROW_TS))) ok = 0;
+        if (ok > 0) for (int q = tid; q < S0; q += nt) {          // one thread per nonzero column
             const int k = sm.sl[q];
             Val x = ld_val(D.xn, D.xd, (size_t)k * ld + lr);
             long long lo = k > 0 ? D.row_ptr[k - 1] : 0, hi = k > 0 ? D.row_ptr[k] : 0;
-            sm.pv[q] = val_div(x, pivot, D.heap, ar);
+            sm.pv[q] = val_div(x, pivot, D.heap, peers ? tr : ar);
             sm.plo[q] = lo; sm.pre[q] = (int)(hi - lo);
             atomicAdd(&sm.W, (int)(hi - lo));
             if (k == 0) sm.b_nz = 1;
@@ -1346,42 +1336,78 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
         __syncthreads();
         if (ok > 0) {
             const long long nnz = D.col_ptr[I.n];
-            const bool sparse = S <= RELP_RC_SPARSE_S && (long long)sm.W * 32 <= nnz + 1024;
+            const bool sparse = S0 <= RELP_RC_SPARSE_S && (long long)sm.W * 32 <= nnz + 1024;
             // with peers the reduced costs must go through the CSR path: the other ranks do not hold this row's bitmap
             if (rc.n != 0 && (sparse ? sm.W > RELP_NARROW_W : (peers || (I.sl_hi - I.sl_lo) > 256))) ok = 0;
         }
-        if (peers) {
-            const int ring = peer_next_ring(D);
-            if (ok > 0) for (int it = tid; it < S * D.xworld; it += nt) {
-                const int w = it / S, q = it - w * S;
-                if (w == D.xrank) continue;
-                if (sm.pv[q].d == 0) ok = -2;                     // a multi-limb p_k cannot cross GPUs
-                XNarrowRow* dst = &D.xp[w].head->nrow[ring];
-                dst->k[q] = sm.sl[q]; dst->p[q] = sm.pv[q];
-                __threadfence_system();
-            }
-            ok = __syncthreads_or(ok == -2) ? -2 : ok;
-            if (ok == -2 && tid == 0) atomicOr(&st->err, ERR_PEER_BIG);
-            peer_row_header(D, true, ok, S, sm.W, sm.b_nz);
+    }
+    if constexpr (PEERS) {
+        __shared__ XSlot xs[RELP_MAX_WORLD];
+        __shared__ int xwin;
+        __syncthreads();
+        const unsigned long long x = *(volatile unsigned long long*)&st->xseq + 1, seq = (D.xepoch << 40) | x;
+        const int ring = (int)(x & 3);
+        const int S0 = have && ok > 0 ? sm.S : 0;
+        for (int it = tid; it < S0 * D.xworld; it += nt) {        // my row's entries into every peer's copy of my lane
+            const int w = it / S0, q = it - w * S0;
+            if (w == D.xrank) continue;
+            if (sm.pv[q].d == 0) ok = -2;                         // a multi-limb p_k cannot cross GPUs
+            XNarrowRow* dst = &D.xp[w].head->nrow[ring][D.xrank];
+            dst->k[q] = sm.sl[q]; dst->p[q] = sm.pv[q];
         }
-    } else {
-        const int ring = peer_next_ring(D);
-        const XRowHdr h = peer_row_header(D, false, 0, 0, 0, 0);
-        ok = h.ok;
-        if (ok > 0) {
-            if (tid == 0) { sm.S = h.S; sm.W = h.W; sm.b_nz = h.b_nz; }
-            const XNarrowRow* src = &D.xp[D.xrank].head->nrow[ring];
-            for (int q = tid; q < h.S; q += nt) {
-                const int k = __ldcv(&src->k[q]);
-                Val p; p.n = __ldcv((const long long*)&src->p[q].n); p.d = __ldcv((const long long*)&src->p[q].d);
-                long long lo = k > 0 ? D.row_ptr[k - 1] : 0, hi = k > 0 ? D.row_ptr[k] : 0;
-                sm.sl[q] = k; sm.pv[q] = p; sm.plo[q] = lo; sm.pre[q] = (int)(hi - lo);
+        if (__syncthreads_or(ok == -2)) ok = -2;                  // (also orders the entries before the release below)
+        if (tid < D.xworld) {
+            int flags = (toobig || T > RELP_NARROW_T) ? XF_TOOBIG : 0;
+            if (row.idx >= 0 && row.v.d == 0) flags |= XF_ERR;    // a multi-limb ratio cannot cross GPUs either
+            if (st->err) flags |= XF_ERR;
+            XSlot* dst = &D.xp[tid].head->slot[ring][D.xrank];
+            dst->c = row; dst->T = T; dst->flags = flags; dst->ok = have ? ok : 0; dst->S = S0; dst->W = sm.W; dst->b_nz = sm.b_nz;
+            st_release_sys(&dst->seq, seq);
+            const XSlot* src = &D.xp[D.xrank].head->slot[ring][tid];
+            XSlot got; got.c = cand_none(); got.T = 0; got.flags = XF_ERR; got.ok = -1; got.S = 0; got.W = 0; got.b_nz = 0;
+            if (peer_wait(&src->seq, seq, st)) {
+                got.c = ldcv_cand(&src->c); got.T = __ldcv(&src->T); got.flags = __ldcv(&src->flags);
+                got.ok = __ldcv(&src->ok); got.S = __ldcv(&src->S); got.W = __ldcv(&src->W); got.b_nz = __ldcv(&src->b_nz);
             }
+            xs[tid] = got;
         }
         __syncthreads();
+        if (tid == 0) {
+            st->xseq = x;
+            int win = -1; Cand best = cand_none();
+            for (int q = 0; q < D.xworld; q++)
+                if (!(xs[q].flags & XF_ERR) && cand_better(xs[q].c, best, ARG_RATIO, D.heap)) { best = xs[q].c; win = q; }
+            xwin = win;
+        }
+        __syncthreads();
+        int any = 0, Tmax = 0;
+        for (int q = 0; q < D.xworld; q++) { any |= xs[q].flags; if (xs[q].T > Tmax) Tmax = xs[q].T; }
+        if (any & XF_ERR) { if (tid == 0) atomicOr(&st->err, (row.idx >= 0 && row.v.d == 0) ? ERR_PEER_BIG : ERR_PEER); return 2; }
+        if (any & XF_TOOBIG) return 1;
+        const int win = xwin;
+        if (win < 0) { if (tid == 0) commit_row(st, cand_none()); return 2; }
+        row = xs[win].c;
+        ok = xs[win].ok;
+        if (ok == -2 && tid == 0) atomicOr(&st->err, ERR_PEER_BIG);
+        if (ok > 0 && (long long)Tmax * xs[win].S > RELP_NARROW_TS) ok = 0;
+        lr = row.idx - I.row_lo;
+        if (ok > 0 && win != D.xrank) {                          // adopt the winner's row
+            __syncthreads();
+            if (tid == 0) { sm.S = xs[win].S; sm.W = xs[win].W; sm.b_nz = xs[win].b_nz; }
+            const XNarrowRow* src = &D.xp[D.xrank].head->nrow[ring][win];
+            for (int q = tid; q < xs[win].S; q += nt) {
+                const int k = __ldcv(&src->k[q]);
+                Val pq; pq.n = __ldcv((const long long*)&src->p[q].n); pq.d = __ldcv((const long long*)&src->p[q].d);
+                long long lo = k > 0 ? D.row_ptr[k - 1] : 0, hi = k > 0 ? D.row_ptr[k] : 0;
+                sm.sl[q] = k; sm.pv[q] = pq; sm.plo[q] = lo; sm.pre[q] = (int)(hi - lo);
+            }
+            __syncthreads();
+        }
     }
     if (ok < 0) { if (peers && tid == 0) atomicOr(&st->err, ERR_PEER); return 2; }
     if (ok == 0) return 1;
+    const int r = row.idx;
+    const bool owner = lr >= 0 && lr < I.mloc;
     const int S = sm.S;
     const int W = sm.W;
     const bool rc_sparse = S <= RELP_RC_SPARSE_S && (long long)W * 32 <= D.col_ptr[I.n] + 1024;
@@ -1471,6 +1497,8 @@ __device__ int narrow_iteration(const Dev& D, const Inv& I, const Cand& col, int
 // The persistent loop: phase_one::primal / phase_two::primal (phase_one.rs:135-169,
 // phase_two.rs:32-50) entirely on the device.  Cooperative launch, one CTA per SM.
 // ---------------------------------------------------------------------------------------------
+// PEERS: the multi-GPU instance (exchanges with the other ranks compiled in); the single-GPU instance carries none of it.
+template <bool PEERS>
 __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int rule, int max_iters, int smem_words, int use_narrow) {
     DState* st = D.st;
     const Grid g = this_grid_dims();
@@ -1479,7 +1507,7 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
     // The reduced-cost row is computed once (full pricing pass) and then kept current by every
     // pivot; `rc_valid` is cleared by whatever replaces the cost row or the basis from outside.
 #ifndef RELP_EMUL
-    if (D.xworld > 1 && st->xseq == 0) {
+    if (PEERS && st->xseq == 0) {
         if (g.bid == 0) peer_hello(D);
         GRID_SYNC();
         if (st->err) return;
@@ -1517,7 +1545,7 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
             if (g.bid == 0) {
                 col = reduce_candidates(D.cand, g.nb, mode, D.heap);
                 if (g.tid == 0) commit_column(st, col, rule);
-                int verdict = col.idx < 0 ? 2 : narrow_iteration(D, I, col, smem_words);
+                int verdict = col.idx < 0 ? 2 : narrow_iteration<PEERS>(D, I, col, smem_words);
                 if (threadIdx.x == 0) {
                     st->narrow_verdict = verdict;
                     if (verdict == 0) { t2 = t3 = t4 = gtime(); }
@@ -1554,7 +1582,7 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
         t2 = gtime();
         Cand row;
 #ifndef RELP_EMUL
-        if (D.xworld > 1) {
+        if constexpr (PEERS) {
             // this rank's winner against the other ranks' (CTA 0 talks to the peers, the grid learns the result
             // through gather[0] after one more barrier)
             if (g.bid == 0) {
@@ -1572,11 +1600,11 @@ __global__ void __launch_bounds__(RELP_PTHREADS, 1) k_simplex_loop(Dev D, int ru
         if (g.tid == 0) commit_row(st, row);
         if (row.idx < 0) break;
         TRACE(6);
-        stage_pivot_row(D, g, I, row.idx, D.xworld > 1 ? 2 : 0);
+        stage_pivot_row(D, g, I, row.idx, PEERS ? 2 : 0);
         TRACE(7);
         GRID_SYNC();
 #ifndef RELP_EMUL
-        if (D.xworld > 1) {
+        if constexpr (PEERS) {
             // the owner's entries are on their way (each writer fenced at system scope before the barrier
             // above); its CTA 0 now posts the header, every other rank waits for it and adopts S and W
             if (g.bid == 0) {
