@@ -1,8 +1,12 @@
-"""One process per GPU: row-sharded Carry, column-sharded pricing.
+"""One process per GPU: row-sharded Carry.
 
-torch.distributed is the plumbing only (rendezvous, exchanging the NCCL unique id, gathering the
-per-rank pieces of the answer); the per-pivot collectives are issued by librelp_b200.so itself on
-its own stream (NCCL), or -- in the CPU tests -- through host callbacks over a gloo group.
+torch.distributed is the plumbing only (rendezvous, exchanging the NCCL unique id and the CUDA IPC
+handles of the exchange buffers, gathering the per-rank pieces of the answer).  Transports:
+  "peer"       the persistent loop kernel on every rank, per-pivot exchanges by stores into peer memory
+               over NVLink (the product path);
+  "nccl"       one launch per stage with NCCL collectives in between, issued by librelp_b200.so on its
+               own stream (the correctness baseline the peer path is checked against);
+  "callbacks"  the same stage-per-launch driver with host-staged collectives over a gloo group (CPU tests).
 """
 import ctypes as C
 import glob
@@ -173,9 +177,13 @@ def bench(args, metric, unit, config, ClockSampler, workload):
                 "e2e": {"value": pivots / e2e_s, "unit": unit, "h2d_bytes_per_step": h2d * world,
                         "d2h_bytes_per_step": 16 + 20 * pa.m, "ms_per_step": 1e3 * e2e_s / args.steps},
                 "gpu_launches": int(launches), "clocks": clk,
-                "note": "one LP solved cooperatively: Carry rows and pricing columns sharded, 2 all-gathers + 1 all-reduce "
-                        "per pivot (NCCL); this LP is latency-bound (DESIGN.md section 4), so more GPUs add collective "
-                        "latency without removing much work"}
+                "transport": sc.transport,
+                "note": "ONE LP solved cooperatively (strong scaling): Carry rows sharded, cost row / reduced-cost row / basis "
+                        "replicated; the persistent loop kernel runs on every rank and exchanges ratio-test candidates and the "
+                        "pivot row by stores into peer memory over NVLink (one exchange per narrow pivot, no NCCL call and no "
+                        "launch per pivot).  This LP is latency-bound (about 20 Carry rows x 3 columns change per pivot, "
+                        "DESIGN.md section 4): sharding removes almost no work and adds one NVLink round per pivot, so "
+                        "pivots/s stays just below the single-GPU figure instead of growing with N"}
         print(json.dumps(line), flush=True)
     sc.close()
     dist.destroy_process_group()
