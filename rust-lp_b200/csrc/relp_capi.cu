@@ -1273,7 +1273,7 @@ int relp_debug_k1_dense(relp_ctx* c, uint64_t seed, int32_t reps, float* ms_pivo
     (void)c; (void)seed; (void)reps; (void)ms_pivot_row; (void)ms_update; (void)T_out; (void)S_out;
     return RELP_ERR_ARGUMENT;
 #else
-    if (!c || !c->carry_ready || c->world != 1 || reps < 1) return RELP_ERR_ARGUMENT;
+    if (!c || !c->carry_ready || reps < 1 || (c->world > 1 && (c->peer_mode || !(c->comm || c->cb_allreduce)))) return RELP_ERR_ARGUMENT;
     CUDA_TRY(cudaSetDevice(c->device));
     cudaEvent_t e0, e1, e2;
     CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1)); CUDA_TRY(cudaEventCreate(&e2));
@@ -1287,7 +1287,11 @@ int relp_debug_k1_dense(relp_ctx* c, uint64_t seed, int32_t reps, float* ms_pivo
         LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'B', 1, 1);
         LAUNCH(c, k_debug_fill_column, c->sm_count, RELP_THREADS, c->D, (unsigned long long)seed + rep + 1, r, j);
         CUDA_TRY(cudaEventRecord(e0, c->stream));
-        LAUNCH(c, k_pivot_row, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D, 0);
+        LAUNCH(c, k_pivot_row, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D, c->world > 1 ? 1 : 0);
+        if (c->world > 1) {      // row-sharded block: the owner's row reaches every rank (NCCL stage path), each rank updates its rows
+            if (comm_allreduce_i64(c, c->pnd.p, 2 * (size_t)(c->m + 1))) return RELP_ERR_COMM;
+            LAUNCH(c, k_build_slist, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D);
+        }
         CUDA_TRY(cudaEventRecord(e1, c->stream));
         if (launch_update(c)) return RELP_ERR_CUDA;
         CUDA_TRY(cudaEventRecord(e2, c->stream));
@@ -1304,7 +1308,7 @@ int relp_debug_k1_dense(relp_ctx* c, uint64_t seed, int32_t reps, float* ms_pivo
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
     if (ms_pivot_row) *ms_pivot_row = (float)(tp / reps);
     if (ms_update) *ms_update = (float)(tu / reps);
-    if (T_out) *T_out = c->mloc - 1;
+    if (T_out) *T_out = c->mloc;
     if (S_out) *S_out = c->m + 1;
     c->carry_ready = false;
     return RELP_OK;
