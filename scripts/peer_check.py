@@ -11,7 +11,7 @@ local = int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 sizes = [(60, 400, 6), (203, 2000, 20), (2000, 20000, 20)]
-for transport, opts in (("peer", {}), ("peer", {"narrow": 0}), ("nccl", {})):
+for transport, opts in (("peer", {}), ("peer", {"narrow": 0}), ("peer", {"narrow": 0, "k1_exit": 1, "k1_min": 1}), ("nccl", {})):
     for (m, n, k) in sizes:
         pa = synthetic_lp(m, n, k, "tu")
         o = coracle.COracle(pa); st_o = o.solve(1, 2)
@@ -26,7 +26,7 @@ for transport, opts in (("peer", {}), ("peer", {"narrow": 0}), ("nccl", {})):
             raise
         dt = time.perf_counter() - t0
         s = sc.stats()
-        print("rank", dist.get_rank(), transport, opts, m, "status", st, "pivots", s.pivots, "narrow", s.narrow_pivots,
+        print("rank", dist.get_rank(), transport, opts, m, "status", st, "pivots", s.pivots, "narrow", s.narrow_pivots, "handoffs", s.wide_handoffs,
               f"{dt*1e3:.1f} ms", flush=True)
         assert st == parity.STATUS[st_o], (transport, st, st_o)
         assert [x[:4] for x in sc.log()] == [x[:4] for x in parity.oracle_log(o)], transport

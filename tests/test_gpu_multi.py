@@ -22,8 +22,9 @@ WORKER = textwrap.dedent('''
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     # "peer": the persistent loop on every rank, exchanges by stores into peer memory (narrow and wide pivots:
-    # the second pass forbids narrow iterations); "nccl": one launch per stage with collectives in between
-    for transport, opts in (("peer", {}), ("peer", {"narrow": 0}), ("nccl", {})):
+    # the second pass forbids narrow iterations, the third also sends every dense update through the hand-over to k_update,
+    # which each rank decides for itself); "nccl": one launch per stage with collectives in between
+    for transport, opts in (("peer", {}), ("peer", {"narrow": 0}), ("peer", {"narrow": 0, "k1_exit": 1, "k1_min": 1}), ("nccl", {})):
         for (m, n, k) in [(60, 400, 6), (203, 2000, 20), (2000, 20000, 20)]:
             pa = synthetic_lp(m, n, k, "tu")
             o = coracle.COracle(pa); st_o = o.solve(1, 2)
