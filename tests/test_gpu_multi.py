@@ -39,6 +39,29 @@ WORKER = textwrap.dedent('''
             st2 = sc.solve_relaxation()          # a second solve in the same context (new epoch of the exchange ring)
             assert st2 == st and sc.get_objective_function_value() == o.objective()
             sc.close(); del o
+    # values that leave the int64 tier cannot cross GPUs: every rank must stop with an error (or every rank must
+    # finish with the oracle's answer if no such value had to cross) -- promptly, never a hang and never a mix
+    import time
+    pa = synthetic_lp(60, 400, 6, "growth")
+    o = coracle.COracle(pa); st_o = o.solve(1, 2)
+    sc = multi.ShardedCarry(pa, device=local, heap_words=1 << 22, transport="peer")
+    t0 = time.time()
+    try:
+        outcome = ("status", sc.solve_relaxation())
+    except capi.RelpError as e:
+        outcome = ("error", e.status)
+    took = time.time() - t0
+    all_out = [None] * dist.get_world_size()
+    dist.all_gather_object(all_out, outcome)
+    assert len(set(x[0] for x in all_out)) == 1, all_out
+    assert took < 20, took
+    if outcome[0] == "status":
+        assert outcome[1] == parity.STATUS[st_o] and sc.get_objective_function_value() == o.objective()
+    else:
+        assert all(x[1] in (capi.ERR_LIMB_CAPACITY, capi.ERR_COMM) for x in all_out), all_out
+        assert any(x[1] == capi.ERR_LIMB_CAPACITY for x in all_out), all_out
+    print("rank", dist.get_rank(), "growth:", outcome, round(took, 2), "s", flush=True)
+    sc.close(); del o
     print("rank", dist.get_rank(), "ok", flush=True)
     dist.barrier(); dist.destroy_process_group(); os._exit(0)
 ''') % (ROOT, ROOT)
