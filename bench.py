@@ -137,7 +137,8 @@ def cpu_sample(pa, pivots):
     o.advance(pivots)
     dt = time.perf_counter() - t0
     done = o.nr_pivots
-    return done / dt if dt > 0 else 0.0, done, dt
+    log = [(chr(int(t)), int(j), int(r), int(l), int(T), int(S)) for (t, j, r, l, T, S) in o.log()]
+    return done / dt if dt > 0 else 0.0, done, dt, log
 
 
 def run_reference(args):
@@ -150,7 +151,7 @@ def run_reference(args):
         cpu_sample(pa, max(2, sample // 8))
     tot_p, tot_t = 0, 0.0
     for _ in range(args.steps):
-        _, done, dt = cpu_sample(pa, sample)
+        _, done, dt, _ = cpu_sample(pa, sample)
         tot_p += done; tot_t += dt
     v = tot_p / tot_t
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
@@ -201,6 +202,7 @@ def run_single(args):
     launches = s.kernel_launches - launches0
     clk = clocks.stop()
     objective = c.get_objective_function_value()
+    gpu_log = c.log()
     # ---- e2e: host buffers in, result out, wall clock ----------------------------------------------
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -245,7 +247,10 @@ def run_single(args):
               "note": "algorithmic = w (2 T S + S + T), w = 16 (SURVEY 8(d)); the kernel leaves unchanged denominators "
                       "unwritten (24 B per element on integer data)"}
     # ---- CPU baseline (oracle, 1 core, bounded sample) ----------------------------------------------
-    cpu_v, cpu_done, cpu_dt = cpu_sample(pa, args.cpu_pivots)
+    cpu_v, cpu_done, cpu_dt, cpu_log = cpu_sample(pa, args.cpu_pivots)
+    # the oracle's sample doubles as a parity check at the full size: same pivots (phase, entering column, row,
+    # leaving column, T, S) as the GPU solve took
+    prefix_same = gpu_log[:len(cpu_log)] == cpu_log
     line = {"metric": METRIC, "value": pivots / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "exact rational, int64/int64 tier (multi-limb escalation armed, 0 elements escalated)"
@@ -273,6 +278,8 @@ def run_single(args):
             "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": 1, "kind": "port",
                              "sample": f"first {cpu_done} pivots of the same LP, {cpu_dt:.1f} s (oracle/simplex.cpp, single "
                                        "thread like the reference)"}}
+    line["parity_prefix"] = {"pivots": len(cpu_log), "identical_to_oracle": bool(prefix_same),
+                             "what": "pivot log (phase, entering column, row, leaving column, T, S) of the timed solve vs the oracle's sample"}
     if k1:
         line["roofline_k1_dense"] = k1
     print(json.dumps(line), flush=True)
