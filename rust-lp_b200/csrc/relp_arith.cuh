@@ -120,9 +120,59 @@ RELP_HD uint64_t abs64(int64_t x) { return x < 0 ? (uint64_t)0 - (uint64_t)x : (
 // The general (rational) case is a separate, non-inlined function: it is long (three gcds, 128-bit
 // divisions) and the persistent kernel calls fma from dozens of places -- inlined everywhere it made
 // the kernel a megabyte of code that no instruction cache holds.  The integer case stays inline.
+// 32-bit binary GCD (same algorithm as gcd64 on half-width registers)
+RELP_HD uint32_t gcd32(uint32_t a, uint32_t b) {
+    if (a == 0) return b;
+    if (b == 0) return a;
+    if (a == 1 || b == 1) return 1;
+    int sh = ctz32(a | b);
+    a >>= ctz32(a);
+    do {
+        b >>= ctz32(b);
+        if (a > b) { uint32_t t = a; a = b; b = t; }
+        b -= a;
+    } while (b);
+    return a << sh;
+}
+
 RELP_HDN bool small_fma_rational(const Val& x, const Val& a, const Val& b, int s, Val* out) {
     // canonical product tn/td of a*b (cross-reduce, then multiply)
     uint64_t an = abs64(a.n), bn = abs64(b.n);
+    // All six operands below 2^31 and the cross-reduced product too (the usual case while values are small): the
+    // same computation in 32-bit gcds and 64-bit products -- no 128-bit arithmetic, and nothing can overflow.
+    if (((an | bn | abs64(x.n) | (uint64_t)a.d | (uint64_t)b.d | (uint64_t)x.d) >> 31) == 0) {
+        const uint32_t g1 = b.d == 1 ? 1u : gcd32((uint32_t)an, (uint32_t)b.d);
+        const uint32_t g2 = a.d == 1 ? 1u : gcd32((uint32_t)bn, (uint32_t)a.d);
+        // (a division by 1 is the common case and costs a reciprocal on the quarter-rate XU pipe: skip it)
+        const uint32_t an1 = g1 == 1 ? (uint32_t)an : (uint32_t)an / g1, bd1 = g1 == 1 ? (uint32_t)b.d : (uint32_t)b.d / g1;
+        const uint32_t bn1 = g2 == 1 ? (uint32_t)bn : (uint32_t)bn / g2, ad1 = g2 == 1 ? (uint32_t)a.d : (uint32_t)a.d / g2;
+        const uint64_t tn = (uint64_t)an1 * bn1;
+        const uint64_t td = (uint64_t)ad1 * bd1;
+        if (((tn | td) >> 31) == 0) {
+            const bool tneg = ((a.n < 0) != (b.n < 0)) != (s < 0);
+            if (x.n == 0) { *out = make_small(tneg ? -(int64_t)tn : (int64_t)tn, (int64_t)td); return true; }
+            const uint32_t xd = (uint32_t)x.d, tdd = (uint32_t)td;
+            const uint32_t g = (xd == 1 || tdd == 1) ? 1u : gcd32(xd, tdd);
+            const uint32_t xdg = g == 1 ? xd : xd / g, tdg = g == 1 ? tdd : tdd / g;
+            const int64_t p = x.n * (int64_t)tdg;                  // |.| < 2^62
+            const int64_t q = (int64_t)tn * (int64_t)xdg;          // < 2^62
+            int64_t num = tneg ? p - q : p + q;                    // |.| < 2^63
+            if (num == 0) { *out = val_zero(); return true; }
+            uint64_t den = (uint64_t)xdg * tdd;                    // < 2^62
+            if (g > 1) {                                           // gcd(num, den) = gcd(num, g)  (Knuth 4.5.1)
+                const uint64_t na = num < 0 ? (uint64_t)0 - (uint64_t)num : (uint64_t)num;
+                const uint32_t g3 = gcd32((na >> 32) == 0 ? (uint32_t)na % g : (uint32_t)(na % g), g);
+                if (g3 > 1) {
+                    if ((na >> 32) == 0 && (den >> 32) == 0) {     // 32-bit quotients when they fit
+                        const uint32_t qn = (uint32_t)na / g3;
+                        num = num < 0 ? -(int64_t)qn : (int64_t)qn; den = (uint32_t)den / g3;
+                    } else { num /= (int64_t)g3; den /= g3; }
+                }
+            }
+            *out = make_small(num, (int64_t)den);
+            return true;
+        }
+    }
     uint64_t g1 = b.d == 1 ? 1 : gcd64(an, (uint64_t)b.d);
     uint64_t g2 = a.d == 1 ? 1 : gcd64(bn, (uint64_t)a.d);
     u128 tn = (u128)(an / g1) * (bn / g2);

@@ -101,6 +101,7 @@ struct relp_ctx {
     // peer transport (multi-GPU persistent loop): this rank's exchange buffer and the peers' as mapped here
     DBuf<unsigned char> xbuf; void* peer_base[RELP_MAX_WORLD] = {}; bool peer_mode = false; int peer_max_m = 0;
     unsigned long long epoch = 0;
+    int k1_bench_frac = 0;          // option "k1_bench_frac": relp_debug_k1_dense fills the block with general rationals
     long long k1_exit = 8 << 20;    // option "k1_exit": T x S from which the persistent loop hands a dense update to k_update
     long long k1_min = 300000;      // option "k1_min": T x S from which the wide Carry update is tiled / staged
     DState* h_st = nullptr;       // pinned mirror
@@ -1225,7 +1226,8 @@ int relp_set_option(relp_ctx* c, const char* name, int64_t value) {
     if (!strcmp(name, "persistent")) { c->use_persistent = value != 0; return RELP_OK; }
     if (!strcmp(name, "narrow")) { c->use_narrow = value != 0; return RELP_OK; }
     if (!strcmp(name, "k1_min")) { c->k1_min = value; return RELP_OK; }
-    if (!strcmp(name, "k1_exit")) { c->k1_exit = value; return RELP_OK; }     // takes effect when the Carry is next created
+    if (!strcmp(name, "k1_exit")) { c->k1_exit = value; return RELP_OK; }
+    if (!strcmp(name, "k1_bench_frac")) { c->k1_bench_frac = value != 0; return RELP_OK; }     // takes effect when the Carry is next created
     if (!strcmp(name, "coop_blocks")) { c->coop_blocks = (int)value; return RELP_OK; }   // debug: CTAs of the persistent kernel
     if (!strcmp(name, "trace")) {      // debug: per-CTA barrier arrival times of the last iteration
         if (value) { if (c->trace.alloc(16 * 4096)) return RELP_ERR_CUDA; cudaMemset(c->trace.p, 0, 16 * 4096 * 8); }
@@ -1240,26 +1242,34 @@ void* relp_stream(relp_ctx* c) { return c ? (void*)c->stream : nullptr; }
 // and a dense generated column with d_r = 1, so that one pivot-row + update pair is a full-size rank-1
 // update (T = local rows, S = m + 1).  Times the two kernels with CUDA events.  The Carry is garbage
 // afterwards: set the problem up again before solving.
-__global__ void k_debug_fill_planes(Dev D, unsigned long long seed) {
+__global__ void k_debug_fill_planes(Dev D, unsigned long long seed, int frac) {
     DState* st = D.st;
     const size_t ld = st->ld, total = (size_t)(st->m + 1) * ld;
     for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
         unsigned long long h = (e + seed) * 0x9E3779B97F4A7C15ull; h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
         int64_t v = (int64_t)(h % 1000) + 100;      // wide enough that x - d p = 0 is rare, as in a filled-in B^-1
         if (h & 1024) v = -v;
-        if ((int)(e % ld) >= st->mloc) v = 0;
-        D.xn[e] = v; D.xd[e] = 1;
+        int64_t den = 1;
+        if (frac) {      // general rationals: small prime denominators, numerator coprime to it (canonical form)
+            const int64_t dens[4] = {2, 3, 5, 7};
+            den = dens[(h >> 40) & 3];
+            if (v % den == 0) v += v > 0 ? 1 : -1;
+        }
+        if ((int)(e % ld) >= st->mloc) { v = 0; den = 1; }
+        D.xn[e] = v; D.xd[e] = den;
     }
 }
-__global__ void k_debug_fill_column(Dev D, unsigned long long seed, int r, int j) {
+__global__ void k_debug_fill_column(Dev D, unsigned long long seed, int r, int j, int frac) {
     DState* st = D.st;
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
     for (int li = tid; li < st->mloc; li += gridDim.x * blockDim.x) {
         unsigned long long h = (li + seed) * 0xD6E8FEB86659FD93ull; h ^= h >> 31;
         int64_t v = (int64_t)(h % 3) + 1;
         if (h & 8) v = -v;
+        int64_t den = 1;
+        if (frac && li != r - st->row_lo) { den = (h >> 20) % 3 == 0 ? 11 : 13; }      // d_i = +-{1,2,3} / {11,13}
         if (li == r - st->row_lo) v = 1;
-        D.dn[li] = v; D.dd[li] = 1; D.tlist[li] = li;
+        D.dn[li] = v; D.dd[li] = den; D.tlist[li] = li;
     }
     if (tid == 0) {
         st->T = st->mloc; st->S = 0; st->W = 0; st->wl_count = 0; st->r = r; st->j = j;
@@ -1282,10 +1292,10 @@ int relp_debug_k1_dense(relp_ctx* c, uint64_t seed, int32_t reps, float* ms_pivo
     const int j = c->h_st->ncols - 1;
     for (int rep = -1; rep < reps; rep++) {          // rep -1: warm-up, not timed
         const int r = (int)((seed + 7919ull * (rep + 1)) % (uint64_t)c->m);
-        LAUNCH(c, k_debug_fill_planes, c->sm_count * 8, RELP_THREADS, c->D, (unsigned long long)seed + rep + 1);
+        LAUNCH(c, k_debug_fill_planes, c->sm_count * 8, RELP_THREADS, c->D, (unsigned long long)seed + rep + 1, c->k1_bench_frac);
         LAUNCH(c, k_build_pattern, c->sm_count * 8, RELP_THREADS, c->D);
         LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'B', 1, 1);
-        LAUNCH(c, k_debug_fill_column, c->sm_count, RELP_THREADS, c->D, (unsigned long long)seed + rep + 1, r, j);
+        LAUNCH(c, k_debug_fill_column, c->sm_count, RELP_THREADS, c->D, (unsigned long long)seed + rep + 1, r, j, c->k1_bench_frac);
         CUDA_TRY(cudaEventRecord(e0, c->stream));
         LAUNCH(c, k_pivot_row, grid_for(c, c->m + 1, 2), RELP_THREADS, c->D, c->world > 1 ? 1 : 0);
         if (c->world > 1) {      // row-sharded block: the owner's row reaches every rank (NCCL stage path), each rank updates its rows

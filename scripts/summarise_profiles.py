@@ -77,6 +77,20 @@ k1n = kernel_summary(os.path.join(G, "k1_dense.ncu-rep"), {
 json.dump(k1n, open(os.path.join(P, f"k1_dense_{R}.json"), "w"), indent=1)
 bench["roofline"]["traffic"] = loop["dram_bytes_per_launch"]
 json.dump(bench, open(os.path.join(P, f"bench_{R}.json"), "w"))
+if os.path.exists(os.path.join(G, "k1_frac.ncu-rep")):      # the same update on general rationals (integer-pipe bound) + measured integer peaks
+    kf = kernel_summary(os.path.join(G, "k1_frac.ncu-rep"), {
+        "kernel": "k_update on general rationals",
+        "command": "ncu --set full --clock-control none --import-source on -k regex:k_update$ -s 1 -c 1 python scripts/k1_dense.py 20000 4 \"\" 1",
+        "note": "same block, entries with denominators 2,3,5,7 and d_i over 11,13: every element takes small_fma_rational (three 64-bit gcds, 128-bit products and divisions)",
+        "cuda_event_timing_without_ncu": json.loads(open(os.path.join(G, "k1_frac_plain.log")).read().strip().splitlines()[-1])})
+    d, _ = raw(os.path.join(G, "k1_frac.ncu-rep"))
+    kf["xu_pipe_pct_of_peak_active"] = num(d, "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active")
+    kf["threads_per_warp_instruction"] = num(d, "smsp__thread_inst_executed_per_inst_executed.ratio")
+    kf["thread_instructions_per_element"] = kf["warp_instructions"] * kf["threads_per_warp_instruction"] / (20000.0 * 20001.0)
+    kf["thread_instructions_per_s_under_ncu"] = kf["warp_instructions"] * kf["threads_per_warp_instruction"] / (kf["gpu_time_ms_under_ncu"] * 1e-3)
+    if os.path.exists(os.path.join(G, "int_peak.jsonl")):
+        kf["measured_integer_peaks (scripts/micro/int_peak.cu)"] = [json.loads(l) for l in open(os.path.join(G, "int_peak.jsonl"))]
+    json.dump(kf, open(os.path.join(P, f"k1_dense_rational_{R}.json"), "w"), indent=1)
 if os.path.exists(os.path.join(G, "netlib_times.jsonl")):
     shutil.copy(os.path.join(G, "netlib_times.jsonl"), os.path.join(P, f"netlib_times_{R}.jsonl"))
 for n in (2, 4, 8):

@@ -138,7 +138,7 @@ def test_canonical_form_kats(L):
     L.t_fma(a, b, one, -1, out); assert (out[0], out[1]) == (0, 1)
 
 
-@pytest.mark.parametrize("bits,seed", [(40, 0), (64, 1), (64, 2), (130, 3), (500, 4), (500, 5)])
+@pytest.mark.parametrize("bits,seed", [(12, 6), (20, 7), (31, 8), (40, 0), (64, 1), (64, 2), (130, 3), (500, 4), (500, 5)])
 def test_fma_div_cmp_random(L, bits, seed):
     rnd = random.Random(seed)
     out = (C.c_int64 * 2)()
