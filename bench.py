@@ -246,6 +246,15 @@ def run_single(args):
               "moved_bytes": (8 + 8 + 8) * T * S,
               "note": "algorithmic = w (2 T S + S + T), w = 16 (SURVEY 8(d)); the kernel leaves unchanged denominators "
                       "unwritten (24 B per element on integer data)"}
+        # the same update on general rationals (every element through small_fma_rational): integer-pipe work
+        c.set_option("k1_bench_frac", 1)
+        c.create_for_partially_artificial(pa.piv_rows, pa.piv_cols)
+        _, ms_rat, T, S = c.debug_k1_dense(seed=20260101, reps=3)
+        c.set_option("k1_bench_frac", 0)
+        k1["general_rationals"] = {"ms_update": ms_rat, "elements_per_s": T * S / (ms_rat * 1e-3), "bound": "integer pipes",
+                                   "algorithmic_GBps": W_BYTES * (2 * T * S + S + T) / (ms_rat * 1e-3) / 1e9,
+                                   "note": "entries with denominators 2,3,5,7, d_i over 11,13; pipe utilisation (ncu) and the integer "
+                                           "peaks measured on this GPU are in profiles/k1_dense_rational_r01.json"}
     # ---- CPU baseline (oracle, 1 core, bounded sample) ----------------------------------------------
     cpu_v, cpu_done, cpu_dt, cpu_log = cpu_sample(pa, args.cpu_pivots)
     # the oracle's sample doubles as a parity check at the full size: same pivots (phase, entering column, row,

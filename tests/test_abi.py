@@ -24,6 +24,14 @@ def test_header_symbols_match_binding_list():
     assert declared == set(capi.SYMBOLS)
 
 
+def test_rust_sys_crate_names_every_symbol():
+    """integration/rust/relp-b200-sys (never compiled: no Rust toolchain here) declares exactly the header's symbols"""
+    src = open(os.path.join(ROOT, "integration", "rust", "relp-b200-sys", "src", "lib.rs")).read()
+    block = src[src.index('extern "C" {'):]
+    declared = set(re.findall(r"pub fn (relp_[a-z0-9_]+)\s*\(", block[:block.index("\n}\n")]))
+    assert declared == set(capi.SYMBOLS)
+
+
 def test_library_exports_every_symbol(lib):
     for s in capi.SYMBOLS:
         assert hasattr(lib, s), s
