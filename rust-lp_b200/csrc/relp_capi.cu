@@ -92,6 +92,9 @@ struct relp_ctx {
     DBuf<int64_t> xn, xd, zn, zd, an_d, ad_d, cn_d, cd_d, rhsn_d, rhsd_d, dn, dd, pnd, psnd, tmpn, tmpd, sell_an, sell_ad;
     DBuf<long long> col_ptr_d, sell_ptr; DBuf<uint32_t> zbits; DBuf<int> row_idx_d, sell_row, basis, art_row, tlist, slist, cost_rows, scratch_i;
     DBuf<unsigned char> in_basis;
+    // grow-only scratch of calls that run once per solve / per read-back (a cudaMalloc + cudaFree pair per call costs a
+    // device-wide synchronisation, and much more once peers have mapped this device's memory)
+    DBuf<int64_t> exp_n, exp_d, hand_all; DBuf<long long> csr_cursor;
     DBuf<int64_t> rn, rd; DBuf<long long> row_ptr_d; DBuf<int4> csr_ent; DBuf<int> row_art; DBuf<uint32_t> colbits, rowbits, colsum; DBuf<unsigned> claim;   // reduced-cost row, nonzero pattern
     size_t wl_cap = 0;
     DBuf<int2> worklist; DBuf<Cand> cand, cand2, gather; DBuf<LogEntry> log; DBuf<unsigned long long> trace;
@@ -203,7 +206,7 @@ __global__ void k_csr_fill(int n, const long long* col_ptr, const int* row_idx, 
 static int build_csr(relp_ctx* c, long long nnz) {
     int m = c->m, n = c->n;
     if (nnz >= (1ll << 31)) { set_error("more than 2^31 - 1 matrix entries"); return RELP_ERR_ARGUMENT; }
-    DBuf<long long> cursor;
+    DBuf<long long>& cursor = c->csr_cursor;
     if (c->row_ptr_d.alloc(m + 1) || c->csr_ent.alloc(nnz) || cursor.alloc(m + 1)) return RELP_ERR_CUDA;
     CUDA_TRY(cudaMemsetAsync(c->row_ptr_d.p, 0, (size_t)(m + 1) * sizeof(long long), c->stream));
     LAUNCH(c, k_csr_count, clampi((nnz + 255) / 256, 1, c->sm_count * 8), 256, n, c->col_ptr_d.p, c->row_idx_d.p, c->row_ptr_d.p);
@@ -762,7 +765,7 @@ static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbe
     } else {
         // each rank sums over its rows into pn|pd, the partials are all-gathered and added exactly
         int cnt = m + 1;
-        DBuf<int64_t> all;
+        DBuf<int64_t>& all = c->hand_all;
         if (all.alloc((size_t)c->world * 2 * cnt)) return RELP_ERR_CUDA;
         LAUNCH(c, k_recompute_cost_row, grid_for(c, cnt, 2), RELP_THREADS, c->D, c->cost_rows.p, (int)cost_rows.size(), c->pnd.p, c->pnd.p + cnt);      // (not D.pn: with the peer transport that lives in the exchange buffer)
         if (comm_allgather(c, c->pnd.p, all.p, 2 * (size_t)cnt * 8)) return RELP_ERR_COMM;
@@ -966,7 +969,7 @@ static int read_block_impl(relp_ctx* c, const int64_t* sn, const int64_t* sd, lo
     size_t total = (size_t)nrows * ncols;
     if (limb_used) *limb_used = 0;
     if (total == 0) return RELP_OK;
-    DBuf<int64_t> on, od;
+    DBuf<int64_t>& on = c->exp_n; DBuf<int64_t>& od = c->exp_d;
     if (on.alloc(total) || od.alloc(total)) return RELP_ERR_CUDA;
     if (!keep_transient) LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
     if (sync_state(c)) return RELP_ERR_CUDA;
