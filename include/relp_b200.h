@@ -209,6 +209,33 @@ int relp_stats_get(relp_ctx*, relp_stats* out);
 /* Redundant rows found by the artificial clean-up of the last solve (phase_one.rs:223-260). */
 int relp_rows_removed(relp_ctx*, int32_t* out, int32_t cap);
 
+/* ---- allocation-free variant ---------------------------------------------------------------------
+ * relp_ratio_test_static has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  It is the K4 ratio test of relp_ratio_test -- argmin over rows with
+ * d_i > 0 of b_i / d_i, ties to the smaller basis column, the rule of tableau/mod.rs:221-247 -- as a
+ * context-free call that allocates nothing: no cudaMalloc, no cudaFree, no allocating library routine.
+ * The per-block candidates of the reduction live in a file-scope `static __device__` array of the library
+ * (one candidate per 1024 rows, 24 KB + a 256-byte header; every GPU that loads the library holds it
+ * until the process exits), hence the limit m <= RELP_STATIC_MAX_ROWS: a larger m is refused with
+ * RELP_ERR_ARGUMENT and a message in relp_last_error().
+ *   b_num/b_den, d_num/d_den : DEVICE pointers, m int64 each, canonical rationals of the int64 tier
+ *                              (den >= 1; a den <= 0, i.e. a multi-limb handle, gives status
+ *                              RELP_ERR_LIMB_CAPACITY in result[1] -- use the context API for those)
+ *   basis                    : DEVICE pointer, m int32 (basis column of every row)
+ *   result                   : DEVICE pointer, 2 int32: result[0] = pivot row or -1,
+ *                              result[1] = RELP_OK / RELP_UNBOUNDED (no row with d_i > 0) / error
+ *   stream                   : cudaStream_t the work is enqueued on (NULL = the default stream)
+ * The call only enqueues (a 256-byte memset of the scratch header and one kernel) and returns; the caller
+ * synchronises the stream before reading `result`.  The current device must be the one the pointers
+ * belong to; its copy of the scratch is looked up once per device (cudaGetSymbolAddress), at the first call.
+ * ALL calls on one GPU share that scratch array, which keeps the previous call's contents: the header is
+ * cleared by every call, but two calls that overlap on the GPU (different streams, or different host
+ * threads without ordering between them) race on it and give undefined results.  Serialise them. */
+#define RELP_STATIC_MAX_ROWS (1 << 20)
+int relp_ratio_test_static(const int64_t* b_num, const int64_t* b_den, const int64_t* d_num, const int64_t* d_den,
+                           const int32_t* basis, int32_t m, int32_t* result, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

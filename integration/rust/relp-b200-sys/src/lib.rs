@@ -97,6 +97,10 @@ extern "C" {
     pub fn relp_read_log(ctx: *mut relp_ctx, first: i64, count: i64, out: *mut relp_iter_log) -> c_int;
     pub fn relp_stats_get(ctx: *mut relp_ctx, out: *mut relp_stats) -> c_int;
     pub fn relp_rows_removed(ctx: *mut relp_ctx, out: *mut i32, cap: i32) -> c_int;
+    /// No counterpart in the reference: context-free K4 ratio test on DEVICE
+    /// pointers that allocates nothing; m <= 2^20; result = [row or -1, status] in device memory, read after a stream sync
+    pub fn relp_ratio_test_static(b_num: *const i64, b_den: *const i64, d_num: *const i64, d_den: *const i64,
+                                  basis: *const i32, m: i32, result: *mut i32, stream: *mut c_void) -> c_int;
 }
 
 /// One entry of a rat array -> the reference's `RationalBig` payload.  `den > 0`: the int64 tier, value `num / den`.

@@ -28,7 +28,7 @@ SYMBOLS = [
     "relp_iterate", "relp_solve_relaxation", "relp_solve_continue", "relp_solve_to_handover",
     "relp_dims", "relp_read_basis", "relp_read_block", "relp_read_carry", "relp_read_b",
     "relp_read_minus_pi", "relp_read_minus_objective", "relp_read_column", "relp_log_size",
-    "relp_read_log", "relp_stats_get", "relp_rows_removed",
+    "relp_read_log", "relp_stats_get", "relp_rows_removed", "relp_ratio_test_static",
 ]
 
 
@@ -106,6 +106,8 @@ def load_library(path=None):
     L.relp_read_log.argtypes = [vp, i64, i64, vp]
     L.relp_stats_get.argtypes = [vp, vp]
     L.relp_rows_removed.argtypes = [vp, vp, i32]
+    if hasattr(L, "relp_ratio_test_static"):
+        L.relp_ratio_test_static.argtypes = [vp, vp, vp, vp, vp, i32, vp, vp]
     _libs[path] = L
     return L
 

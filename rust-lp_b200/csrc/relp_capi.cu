@@ -1335,3 +1335,118 @@ int relp_debug_trace(relp_ctx* c, uint64_t* out, int32_t n_ctas) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// relp_ratio_test_static (include/relp_b200.h): the K4 ratio test as a context-free call that allocates
+// nothing.  No counterpart in the reference; added for callers
+// that cannot call cudaMalloc.  The scratch that the two-level argmin needs (one candidate per block,
+// an arrival counter and an error word) lives in a file-scope static __device__ array.  In HOST code
+// the array's name is only a stand-in for the symbol, not a device address: the address of this
+// device's copy is looked up with cudaGetSymbolAddress (once per device) and passed to the kernel.
+// ---------------------------------------------------------------------------------------------
+#ifndef RELP_EMUL
+#include <mutex>
+
+#define RELP_STATIC_BLOCK_THREADS 256
+#define RELP_STATIC_ROWS_PER_BLOCK 1024
+#define RELP_STATIC_MAX_BLOCKS (RELP_STATIC_MAX_ROWS / RELP_STATIC_ROWS_PER_BLOCK)
+
+struct StaticScratch {
+    unsigned arrived;                        // blocks that have posted their candidate; must start at 0
+    int flags;                               // ERR_* bits raised by any block; must start at 0
+    int pad[62];                             // header = 256 bytes (what every call clears)
+    Cand cand[RELP_STATIC_MAX_BLOCKS];       // one partial winner per block of 1024 rows
+};
+static_assert(sizeof(StaticScratch) % 8 == 0, "scratch is declared in 8-byte words");
+static __device__ __align__(256) unsigned long long g_static_scratch[sizeof(StaticScratch) / 8];
+
+__global__ void __launch_bounds__(RELP_STATIC_BLOCK_THREADS)
+k_ratio_test_static(const int64_t* __restrict__ bn, const int64_t* __restrict__ bd, const int64_t* __restrict__ dn,
+                    const int64_t* __restrict__ dd, const int* __restrict__ basis, int m, StaticScratch* sc, int* result) {
+    __shared__ int is_last;
+    Cand best = cand_none();
+    bool bad = false;
+    const int base = blockIdx.x * RELP_STATIC_ROWS_PER_BLOCK;
+#pragma unroll
+    for (int q = 0; q < RELP_STATIC_ROWS_PER_BLOCK / RELP_STATIC_BLOCK_THREADS; q++) {
+        const int i = base + q * RELP_STATIC_BLOCK_THREADS + threadIdx.x;
+        if (i >= m) continue;
+        const Val d = ld_val(dn, dd, i);
+        if (d.d <= 0) { bad = true; continue; }                 // multi-limb handle: not this entry point's tier
+        if (d.n <= 0) continue;                                 // only rows with d_i > 0 take part (tableau/mod.rs:226)
+        const Val b = ld_val(bn, bd, i);
+        if (b.d <= 0) { bad = true; continue; }
+        Cand c;
+        // b_i / d_i for comparison only: the unreduced quotient when it fits (as val_ratio), else the reduced one
+        const i128 qn = (i128)b.n * d.d, qd = (i128)b.d * d.n;
+        if (qn <= RELP_I64_MAX && qn >= -RELP_I64_MAX && qd <= RELP_I64_MAX) c.v = make_small((int64_t)qn, (int64_t)qd);
+        else if (!small_div_general(b, d, &c.v)) { bad = true; continue; }
+        c.idx = i; c.key = basis[i];
+        if (cand_better(c, best, ARG_RATIO, nullptr)) best = c;  // int64 tier only: the limb heap is never consulted
+    }
+    if (bad) atomicOr(&sc->flags, (int)ERR_LIMB_CAPACITY);
+    best = block_argmin(best, ARG_RATIO, nullptr);
+    if (threadIdx.x == 0) {
+        sc->cand[blockIdx.x] = best;
+        __threadfence();                                         // the candidate (and the flag) before the ticket
+        is_last = atomicAdd(&sc->arrived, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    // the last block to arrive reduces every block's winner (L2 loads: other SMs wrote them)
+    Cand w = cand_none();
+    for (int q = threadIdx.x; q < (int)gridDim.x; q += blockDim.x) {
+        Cand c;
+        c.v.n = __ldcg((const long long*)&sc->cand[q].v.n); c.v.d = __ldcg((const long long*)&sc->cand[q].v.d);
+        c.key = __ldcg(&sc->cand[q].key); c.idx = __ldcg(&sc->cand[q].idx);
+        if (cand_better(c, w, ARG_RATIO, nullptr)) w = c;
+    }
+    w = block_argmin(w, ARG_RATIO, nullptr);
+    if (threadIdx.x == 0) {
+        const int flags = atomicOr(&sc->flags, 0);
+        result[0] = flags ? -1 : w.idx;
+        result[1] = flags ? (int)RELP_ERR_LIMB_CAPACITY : (w.idx < 0 ? (int)RELP_UNBOUNDED : (int)RELP_OK);
+        sc->arrived = 0; sc->flags = 0;                          // leave the header clean for the next call
+    }
+}
+#endif
+
+extern "C" int relp_ratio_test_static(const int64_t* b_num, const int64_t* b_den, const int64_t* d_num, const int64_t* d_den,
+                                      const int32_t* basis, int32_t m, int32_t* result, void* stream) {
+    if (!b_num || !b_den || !d_num || !d_den || !basis || !result || m < 0) {
+        set_error("relp_ratio_test_static: NULL pointer or negative m"); return RELP_ERR_ARGUMENT;
+    }
+    if (m > RELP_STATIC_MAX_ROWS) {
+        set_error("relp_ratio_test_static: m = " + std::to_string(m) + " exceeds RELP_STATIC_MAX_ROWS = " +
+                  std::to_string((int)RELP_STATIC_MAX_ROWS) + " (the static scratch holds one candidate per 1024 rows); "
+                  "use relp_ratio_test on a context for larger problems");
+        return RELP_ERR_ARGUMENT;
+    }
+#ifdef RELP_EMUL
+    (void)stream; set_error("relp_ratio_test_static needs a GPU"); return RELP_ERR_ARGUMENT;
+#else
+    enum { MAX_DEVICES = 64 };
+    static StaticScratch* scratch_of[MAX_DEVICES] = {};
+    static std::mutex mu;
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEVICES) { set_error("relp_ratio_test_static: device ordinal out of range"); return RELP_ERR_ARGUMENT; }
+    StaticScratch* sc;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!scratch_of[dev]) {      // set-up, once per device, with that device current
+            void* p = nullptr;
+            CUDA_TRY(cudaGetSymbolAddress(&p, g_static_scratch));
+            scratch_of[dev] = (StaticScratch*)p;
+        }
+        sc = scratch_of[dev];
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const int blocks = std::max(1, cdiv(m, RELP_STATIC_ROWS_PER_BLOCK));
+    CUDA_TRY(cudaMemsetAsync(sc, 0, 256, s));                    // arrived = 0, flags = 0 whatever the last call left
+    k_ratio_test_static<<<blocks, RELP_STATIC_BLOCK_THREADS, 0, s>>>(b_num, b_den, d_num, d_den, basis, m, sc, result);
+    CUDA_TRY(cudaPeekAtLastError());
+    return RELP_OK;
+#endif
+}
