@@ -103,6 +103,10 @@ int relp_debug_trace(relp_ctx*, uint64_t* out /* n_ctas x 16 */, int32_t n_ctas)
  * T = m - 1 rows, S = m + 1 columns) with CUDA events.  The Carry is invalid afterwards. */
 int relp_debug_k1_dense(relp_ctx*, uint64_t seed, int32_t reps, float* ms_pivot_row, float* ms_update,
                         int64_t* T_out, int64_t* S_out);
+/* Self-check of that update: the same fabricated block and pivot updated by the staged path (bulk copies into the
+ * shared-memory ring) and, from the same fill, by the element-wise path the oracle-parity tests cover; the planes and
+ * the pattern bitmap are compared on the device.  *mismatches must be 0.  The Carry is invalid afterwards. */
+int relp_debug_k1_verify(relp_ctx*, uint64_t seed, int64_t* mismatches, int64_t* elements);
 
 /* Multi-GPU only: attach an NCCL communicator (ncclComm_t, created by the caller from
  * torch.distributed's rendezvous) used for the per-pivot pivot-row broadcast and the two
@@ -127,7 +131,12 @@ int relp_attach_comm_callbacks(relp_ctx*, relp_allgather_fn, relp_allreduce_fn, 
 /* ---- input: MatrixProvider (matrix_provider/mod.rs:37-136) ---------------------------------- */
 /* CSC of ALL provider columns, virtual slack columns materialised (matrix_data.rs:308-348),
  * cost_value(j) with None == 0 (matrix_data.rs:350-357), right_hand_side() >= 0 (:359-371).
- * Host pointers; copied to the device (the e2e timed region of bench.py includes this copy). */
+ * Host pointers; copied to the device (the e2e timed region of bench.py includes this copy).
+ * The arrays are validated (RELP_ERR_ARGUMENT + relp_last_error otherwise): no NULL pointer; col_ptr[0] == 0 and
+ * non-decreasing; 0 <= row_idx < m; every value, cost and right-hand side canonical (den >= 1, gcd(num, den) == 1,
+ * num != INT64_MIN -- the encoding reserves den == 0 and den < 0, see above); rhs >= 0.
+ * The loaded provider is immutable for the caller: a solve that removes redundant rows works on a filtered copy,
+ * and the next Carry constructor on the same context puts the loaded provider back (no reload needed). */
 int relp_load_matrix(relp_ctx*, int32_t m, int32_t n,
                      const int64_t* col_ptr, const int32_t* row_idx,
                      const int64_t* val_num, const int64_t* val_den,

@@ -45,6 +45,7 @@ extern "C" {
     pub fn relp_debug_trace(ctx: *mut relp_ctx, out: *mut u64, n_ctas: i32) -> c_int;
     pub fn relp_debug_k1_dense(ctx: *mut relp_ctx, seed: u64, reps: i32, ms_pivot_row: *mut f32, ms_update: *mut f32,
                                t_out: *mut i64, s_out: *mut i64) -> c_int;
+    pub fn relp_debug_k1_verify(ctx: *mut relp_ctx, seed: u64, mismatches: *mut i64, elements: *mut i64) -> c_int;
     pub fn relp_comm_unique_id(id128: *mut c_void, nccl_lib: *const c_char) -> c_int;
     pub fn relp_attach_comm(ctx: *mut relp_ctx, id128: *const c_void, nccl_lib: *const c_char) -> c_int;
     pub fn relp_peer_export(ctx: *mut relp_ctx, max_m: i32, handle64: *mut c_void) -> c_int;

@@ -21,7 +21,7 @@ FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
 
 # every symbol include/relp_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
-    "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_debug_k1_dense", "relp_comm_unique_id",
+    "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_debug_k1_dense", "relp_debug_k1_verify", "relp_comm_unique_id",
     "relp_attach_comm", "relp_attach_comm_callbacks", "relp_peer_export", "relp_peer_attach", "relp_load_matrix", "relp_carry_create_partially_artificial",
     "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_carry_from_basis", "relp_price",
     "relp_generate_column", "relp_ratio_test", "relp_change_basis", "relp_generate_element",
@@ -77,6 +77,8 @@ def load_library(path=None):
     L.relp_debug_trace.argtypes = [vp, vp, i32]
     if hasattr(L, "relp_debug_k1_dense"):      # absent from A/B builds of older sources only
         L.relp_debug_k1_dense.argtypes = [vp, C.c_uint64, i32, vp, vp, vp, vp]
+    if hasattr(L, "relp_debug_k1_verify"):
+        L.relp_debug_k1_verify.argtypes = [vp, C.c_uint64, vp, vp]
     L.relp_comm_unique_id.argtypes = [vp, C.c_char_p]
     L.relp_attach_comm.argtypes = [vp, vp, C.c_char_p]
     L.relp_attach_comm_callbacks.argtypes = [vp, ALLGATHER_FN, ALLREDUCE_FN, vp]
@@ -202,6 +204,12 @@ class Carry:
         t, s_ = C.c_int64(), C.c_int64()
         self._chk(self.L.relp_debug_k1_dense(self.h, seed, reps, C.byref(a), C.byref(b), C.byref(t), C.byref(s_)))
         return a.value, b.value, t.value, s_.value
+
+    def debug_k1_verify(self, seed=1):
+        """Dense K1 self-check (staged path vs element-wise path on the same fabricated block): (mismatches, elements)."""
+        bad, n = C.c_int64(-1), C.c_int64(0)
+        self._chk(self.L.relp_debug_k1_verify(self.h, seed, C.byref(bad), C.byref(n)))
+        return bad.value, n.value
 
     def close(self):
         if getattr(self, "h", None):

@@ -12,6 +12,7 @@ Semantics kept from the reference:
 Deviation (documented): an RHS entry on the objective row is an error in the reference ("Row not
 known"); here it is accepted as minus the objective constant when `strict=False`.
 """
+import re
 from fractions import Fraction as Fr
 
 FIXED_FIELDS = [(0, 1), (1, 3), (4, 12), (14, 22), (24, 36), (39, 47), (49, 61)]   # parse/fixed.rs:120-128
@@ -38,15 +39,47 @@ class MPS:
         self.objective_constant = Fr(0)
 
 
+_I64_MAX = 2 ** 63 - 1
+_RUST_INT = re.compile(r"[+-]?[0-9]+\Z")
+
+
+def _rust_i64(text, part):
+    """`text.parse::<i64>()` as number/parse.rs:98-108 uses it: an empty part is 0; otherwise ASCII digits with one
+    optional sign, within the i64 range -- nothing else (no exponent, no '/', no '_', no blanks)."""
+    if text == "":
+        return 0
+    if not _RUST_INT.match(text):
+        raise MPSError(f"Failed to parse {part} {text!r} as i64")
+    v = int(text)
+    if not -_I64_MAX - 1 <= v <= _I64_MAX:
+        raise MPSError(f"{part} {text!r} does not fit i64")
+    return v
+
+
+def parse_raw(text):
+    """`Raw::try_from` (number/parse.rs:88-121): (negative?, integer, decimal_steps_from_right).  Refuses exactly
+    what the reference refuses (scientific notation, fractions, separators, numbers beyond i64)."""
+    if text == "":
+        raise MPSError("empty number")                      # the reference slices text[0..1] and panics
+    negative = text[0] == "-"
+    if negative:
+        text = text[1:]
+    dot = text.find(".")
+    if dot < 0:
+        return negative, _rust_i64(text, "entire value"), 0
+    from_right = len(text) - dot - 1
+    if from_right > 18:
+        raise MPSError(f"{text!r}: 10^{from_right} does not fit i64")
+    integer = _rust_i64(text[:dot], "integer part") * 10 ** from_right + _rust_i64(text[dot + 1:], "mantissa part")
+    if not -_I64_MAX - 1 <= integer <= _I64_MAX:
+        raise MPSError(f"{text!r} does not fit i64")
+    return negative, integer, from_right
+
+
 def parse_number(text):
-    """number/parse.rs: exact decimal -> reduced rational."""
-    t = text.strip()
-    if not t:
-        raise MPSError("empty number")
-    try:
-        return Fr(t)
-    except (ValueError, ZeroDivisionError) as e:
-        raise MPSError(f"cannot parse number {text!r}") from e
+    """`<Rational64 as Parse>::parse` (number/parse.rs:44-67): exact decimal -> reduced rational."""
+    negative, integer, from_right = parse_raw(text.strip())
+    return Fr(-integer if negative else integer, 10 ** from_right)
 
 
 def _fields(line, fixed):

@@ -168,3 +168,59 @@ def check_from_basis(pa, lib_path, pivots_before=3, rule2=2):
     assert c.current_bfs() == o2.current_bfs()
     c.close()
     return True
+
+
+def check_reuse_after_row_removal(pa_deficient, pa_other, lib_path):
+    """a context that removed redundant rows (smaller planes, filtered provider) must (a) solve the
+    SAME loaded LP again to the same answer without a reload and (b) take a different, larger LP afterwards."""
+    o = coracle.COracle(pa_deficient); st_o = o.solve(1, 2)
+    c = capi.Carry(pa_deficient, heap_words=1 << 22, lib_path=lib_path)
+    for _ in range(2):                       # second round: no reload in between
+        assert c.solve_relaxation() == STATUS[st_o]
+        assert c.rows_removed() != [] and o.m < pa_deficient.m
+        assert c.log() == oracle_log(o)
+        assert_same_carry(c, o, "rank-deficient LP")
+    o2 = coracle.COracle(pa_other); st2 = o2.solve(1, 2)
+    c.load_matrix(pa_other)
+    assert c.solve_relaxation() == STATUS[st2]
+    assert c.log() == oracle_log(o2)
+    assert_same_carry(c, o2, "LP loaded after a rank-deficient one")
+    c.close()
+
+
+def check_load_validation(pa, lib_path):
+    """relp_load_matrix refuses what the kernels would misread: bad denominators, non-canonical
+    fractions, INT64_MIN, row indices out of range, decreasing col_ptr, negative right-hand side, NULL."""
+    import copy
+    c = capi.Carry(pa, heap_words=1 << 20, lib_path=lib_path)
+
+    def refused(mutate, what):
+        q = copy.deepcopy(pa)
+        mutate(q)
+        try:
+            c.load_matrix(q)
+        except capi.RelpError as e:
+            assert e.status == capi.ERR_ARGUMENT and what in str(e), str(e)
+            return
+        raise AssertionError("accepted: " + what)
+
+    def setv(name, idx, v):
+        def f(q):
+            getattr(q, name)[idx] = v
+        return f
+    refused(setv("val_den", 0, 0), "denominator")
+    refused(setv("val_den", 1, -3), "denominator")
+    refused(setv("cost_den", 0, 0), "cost")
+    refused(setv("rhs_den", 0, -1), "rhs")
+    refused(setv("rhs_num", 0, -1), "rhs < 0")
+    refused(setv("val_num", 0, -2 ** 63), "INT64_MIN")
+    refused(setv("row_idx", 0, pa.m), "row_idx")
+    refused(setv("row_idx", 0, -1), "row_idx")
+    refused(setv("col_ptr", 1, int(pa.col_ptr[2]) + 1), "col_ptr")
+
+    def noncanon(q):
+        q.val_num[0] *= 2; q.val_den[0] *= 2
+    refused(noncanon, "lowest terms")
+    c.load_matrix(pa)                        # and the context is still usable
+    assert c.solve_relaxation() in (capi.OPTIMAL, capi.UNBOUNDED, capi.INFEASIBLE)
+    c.close()

@@ -154,3 +154,13 @@ def test_from_basis_singular(lib):
                 c.from_basis(list(comb))
             break
     c.close()
+
+
+def test_context_reuse_after_row_removal(lib):
+    lp = feasible_lp(5, 3, 1, 3, 2, 10, frac=True, dup_rows=2)
+    other = feasible_lp(9, 4, 1, 4, 2, 16, frac=False)
+    parity.check_reuse_after_row_removal(pa_from_lp(lp), pa_from_lp(other), lib)
+
+
+def test_load_matrix_validation(lib):
+    parity.check_load_validation(pa_from_lp(feasible_lp(3, 3, 1, 3, 2, 10, frac=True)), lib)

@@ -151,3 +151,28 @@ def test_full_size_properties():
     assert c2.solve_relaxation() == capi.OPTIMAL
     assert c2.log() == log1
     c2.close()
+
+
+def test_context_reuse_after_row_removal():
+    lp = feasible_lp(5, 3, 1, 3, 2, 10, frac=True, dup_rows=2)
+    other = feasible_lp(9, 4, 1, 4, 2, 16, frac=False)
+    parity.check_reuse_after_row_removal(pa_from_lp(lp), pa_from_lp(other), LIB)
+
+
+def test_load_matrix_validation():
+    parity.check_load_validation(pa_from_lp(feasible_lp(3, 3, 1, 3, 2, 10, frac=True)), LIB)
+
+
+@pytest.mark.parametrize("m,frac", [(2500, 0), (9000, 0), (9000, 1)])
+def test_dense_update_ring_at_scale(m, frac):
+    """update_dense_tma where its pipeline turns over: ld = 2528 / 9024 rows = 3 / 9 row tiles with a
+    partial last one, S = m + 1 columns => 25 / 273 tiles per CTA through the 6-stage ring (empty-barrier waits, parity
+    flips, d_i reloads at every row-tile change), on integers and on general rationals.  The result is compared on the
+    device with the element-wise path (the one every oracle-parity test above exercises) run on the same fill."""
+    pa = synthetic_lp(m, 2 * m, 20, "tu")
+    c = capi.Carry(pa, heap_words=1 << 22)
+    c.set_option("k1_bench_frac", frac)
+    c.create_for_partially_artificial()
+    bad, n = c.debug_k1_verify(seed=20260101 + m)
+    assert n == m * (m + 1) and bad == 0, (bad, n)
+    c.close()
