@@ -107,6 +107,12 @@ int relp_debug_k1_dense(relp_ctx*, uint64_t seed, int32_t reps, float* ms_pivot_
  * shared-memory ring) and, from the same fill, by the element-wise path the oracle-parity tests cover; the planes and
  * the pattern bitmap are compared on the device.  *mismatches must be 0.  The Carry is invalid afterwards. */
 int relp_debug_k1_verify(relp_ctx*, uint64_t seed, int64_t* mismatches, int64_t* elements);
+/* Test hook for the device arithmetic (data/number_types/rational/big/wrapping.rs:47-311 is what it replaces): `count`
+ * independent operations, one per thread, through the kernels' own front ends: op 0: x + s a b, 1: x / a, 2: sign(x - a);
+ * op 3: x + s a b with every operation done by the 32 lanes of its warp together (the cooperative tier, relp_wcb.cuh).
+ * operands = six arrays of `count` int64 (xn xd an ad bn bd), rat-array encoding over limbs_in; results as a rat array. */
+int relp_debug_rat_op(relp_ctx*, int op, int32_t count, const int64_t* operands, const uint32_t* limbs_in, size_t limb_words,
+                      int s, int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used);
 
 /* Multi-GPU only: attach an NCCL communicator (ncclComm_t, created by the caller from
  * torch.distributed's rendezvous) used for the per-pivot pivot-row broadcast and the two

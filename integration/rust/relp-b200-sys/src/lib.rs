@@ -46,6 +46,8 @@ extern "C" {
     pub fn relp_debug_k1_dense(ctx: *mut relp_ctx, seed: u64, reps: i32, ms_pivot_row: *mut f32, ms_update: *mut f32,
                                t_out: *mut i64, s_out: *mut i64) -> c_int;
     pub fn relp_debug_k1_verify(ctx: *mut relp_ctx, seed: u64, mismatches: *mut i64, elements: *mut i64) -> c_int;
+    pub fn relp_debug_rat_op(ctx: *mut relp_ctx, op: c_int, count: i32, operands: *const i64, limbs_in: *const u32, limb_words: usize,
+                             s: c_int, num: *mut i64, den: *mut i64, limbs: *mut u32, limb_cap: usize, limb_used: *mut usize) -> c_int;
     pub fn relp_comm_unique_id(id128: *mut c_void, nccl_lib: *const c_char) -> c_int;
     pub fn relp_attach_comm(ctx: *mut relp_ctx, id128: *const c_void, nccl_lib: *const c_char) -> c_int;
     pub fn relp_peer_export(ctx: *mut relp_ctx, max_m: i32, handle64: *mut c_void) -> c_int;

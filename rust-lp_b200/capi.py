@@ -21,7 +21,7 @@ FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
 
 # every symbol include/relp_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
-    "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_debug_k1_dense", "relp_debug_k1_verify", "relp_comm_unique_id",
+    "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_debug_k1_dense", "relp_debug_k1_verify", "relp_debug_rat_op", "relp_comm_unique_id",
     "relp_attach_comm", "relp_attach_comm_callbacks", "relp_peer_export", "relp_peer_attach", "relp_load_matrix", "relp_carry_create_partially_artificial",
     "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_carry_from_basis", "relp_price",
     "relp_generate_column", "relp_ratio_test", "relp_change_basis", "relp_generate_element",
@@ -79,6 +79,8 @@ def load_library(path=None):
         L.relp_debug_k1_dense.argtypes = [vp, C.c_uint64, i32, vp, vp, vp, vp]
     if hasattr(L, "relp_debug_k1_verify"):
         L.relp_debug_k1_verify.argtypes = [vp, C.c_uint64, vp, vp]
+    if hasattr(L, "relp_debug_rat_op"):
+        L.relp_debug_rat_op.argtypes = [vp, C.c_int, i32, vp, vp, sz, C.c_int, vp, vp, vp, sz, vp]
     L.relp_comm_unique_id.argtypes = [vp, C.c_char_p]
     L.relp_attach_comm.argtypes = [vp, vp, C.c_char_p]
     L.relp_attach_comm_callbacks.argtypes = [vp, ALLGATHER_FN, ALLREDUCE_FN, vp]
@@ -204,6 +206,43 @@ class Carry:
         t, s_ = C.c_int64(), C.c_int64()
         self._chk(self.L.relp_debug_k1_dense(self.h, seed, reps, C.byref(a), C.byref(b), C.byref(t), C.byref(s_)))
         return a.value, b.value, t.value, s_.value
+
+    def debug_rat_op(self, op, xs, as_, bs, s=1):
+        """Device arithmetic test hook: op 0: x + s a b, 1: x / a, 2: sign(x - a), 3: x + s a b by whole warps; returns the
+        list of results (Fractions; ints for op 2), each computed by one GPU thread through val_fma / val_div / val_cmp."""
+        count = len(xs)
+        ops = np.zeros((6, count), np.int64)
+        limbs = []
+
+        def enc(row, k, f):
+            f = Fr(f)
+            n, d = f.numerator, f.denominator
+            if abs(n) <= 2 ** 63 - 1 and d <= 2 ** 63 - 1:
+                ops[row, k], ops[row + 1, k] = n, d
+                return
+            a = abs(n); nl = []; dl = []
+            while a:
+                nl.append(a & 0xffffffff); a >>= 32
+            while d:
+                dl.append(d & 0xffffffff); d >>= 32
+            ops[row, k], ops[row + 1, k] = len(limbs), 0
+            limbs.extend([len(nl) | len(dl) << 14 | (0x80000000 if n < 0 else 0)] + nl + dl)
+        for k in range(count):
+            enc(0, k, xs[k]); enc(2, k, as_[k]); enc(4, k, bs[k] if bs is not None else 0)
+        lin = np.array(limbs if limbs else [0], np.uint32)
+        n = np.zeros(count, np.int64); d = np.zeros(count, np.int64)
+        cap = max(1 << 16, 8 * len(limbs) + 1024)
+        while True:
+            lout = np.zeros(cap, np.uint32); used = C.c_size_t(0)
+            st = self.L.relp_debug_rat_op(self.h, op, count, _p(ops), _p(lin), len(limbs), s, _p(n), _p(d), _p(lout), cap, C.byref(used))
+            if st == ERR_ARGUMENT and used.value > cap:
+                cap = int(used.value) * 2
+                continue
+            self._chk(st)
+            break
+        if op == 2:
+            return [int(v) for v in n]
+        return decode_rats(n, d, lout)
 
     def debug_k1_verify(self, seed=1):
         """Dense K1 self-check (staged path vs element-wise path on the same fabricated block): (mismatches, elements)."""

@@ -29,9 +29,11 @@
 #endif
 
 #ifndef RELP_OPL
-#define RELP_OPL 64              // max 32-bit limbs of a stored numerator or denominator (2048 bits)
+#define RELP_OPL 64              // operands up to this many limbs may be handled by ONE thread (fixed-size stack buffers);
+                                 // longer ones go to the cooperative routines of relp_wcb.cuh, which have no fixed size
 #endif
 #define RELP_TL (3 * RELP_OPL + 2)   // max limbs of an intermediate
+#define RELP_MAX_LIMBS 0x3fff        // what the header's 14-bit length fields can say (512 Kbit); the limb heap is the real bound
 
 namespace relp {
 
@@ -43,13 +45,25 @@ struct Val { int64_t n; int64_t d; };
 enum { ERR_NONE = 0, ERR_LIMB_CAPACITY = 1, ERR_HEAP_EXHAUSTED = 2, ERR_ZERO_PIVOT = 4, ERR_PEER = 8, ERR_PEER_BIG = 16 };
 
 // Bump allocator over a region [*top, limit) of the limb heap.
+// Scratch for the temporaries of the cooperative multi-limb operations (relp_wcb.cuh): one slab per resident warp
+// (taken with a lock word for the duration of an operation) and, behind it, the transient region of the heap.
+// Lives in memory (one per context); only the slow paths ever read it.
+struct ScratchExt {
+    uint32_t* wslab = nullptr; unsigned wslab_words = 0; int* wlock = nullptr; int wslots = 0;
+    unsigned long long* scr_top = nullptr; unsigned long long scr_limit = 0; int* err = nullptr;
+    int coop_from = RELP_OPL;    // operands longer than this many limbs leave the per-thread routines for the cooperative ones
+    unsigned long long heap_words = 0;   // size of the limb heap (sanity checks of handles in the cooperative entry points)
+    int dbg = 0;                 // first failed sanity check (0 = none): see w_check
+};
 struct Arena {
-    unsigned long long* top;
-    unsigned long long limit;
-    int* err;                    // sticky error bits (ERR_*)
+    unsigned long long* top = nullptr;
+    unsigned long long limit = 0;
+    int* err = nullptr;          // sticky error bits (ERR_*)
+    const ScratchExt* ext = nullptr;
 };
 
 RELP_HD void set_err(int* err, int bit) {
+    if (!err) return;
 #if defined(__CUDA_ARCH__)
     atomicOr(err, bit);
 #else
@@ -547,7 +561,7 @@ RELP_HD Val store_val(int sign, const uint32_t* num, int nn, const uint32_t* den
         if (a <= 0x7fffffffffffffffULL && b <= 0x7fffffffffffffffULL)
             return make_small(sign < 0 ? -(int64_t)a : (int64_t)a, (int64_t)b);
     }
-    if (nn > RELP_OPL || nd > RELP_OPL) { set_err(ar.err, ERR_LIMB_CAPACITY); return val_zero(); }
+    if (nn > RELP_MAX_LIMBS || nd > RELP_MAX_LIMBS) { set_err(ar.err, ERR_LIMB_CAPACITY); return val_zero(); }
     long long off = arena_alloc(ar, 1u + nn + nd);
     if (off < 0) return val_zero();
     uint32_t* p = heap + off;
@@ -589,7 +603,7 @@ RELP_HD int div_keep(uint32_t* q, const uint32_t* a, int na, const uint32_t* g, 
 // the sum needs gcd(x.d, t.d) and -- only when that is not 1 -- one gcd against it.  No gcd ever sees
 // the full-size numerator and denominator of the unreduced result, which is what made the plain
 // "compute, then reduce" version spend 98 % of its time in one 3x-length binary GCD.
-RELP_HDN Val big_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) {
+RELP_HDN Val big_fma_thread(const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) {
     Ref rx, ra, rb;
     ref_load(rx, x, heap); ref_load(ra, a, heap); ref_load(rb, b, heap);
     if (ra.sign == 0 || rb.sign == 0) return copy_val(x, heap, ar);
@@ -659,7 +673,7 @@ RELP_HDN Val big_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* 
 
 // out = x / y (y != 0) for arbitrary tiers: (x.n / g1)(y.d / g2) / ((x.d / g2)(y.n / g1)), g1 = gcd(x.n, y.n),
 // g2 = gcd(y.d, x.d) -- in lowest terms without a gcd of the products.
-RELP_HDN Val big_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar) {
+RELP_HDN Val big_div_thread(const Val& x, const Val& y, uint32_t* heap, const Arena& ar) {
     Ref rx, ry;
     ref_load(rx, x, heap); ref_load(ry, y, heap);
     if (rx.sign == 0) return val_zero();
@@ -682,7 +696,7 @@ RELP_HDN Val big_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar
 }
 
 // sign(x - y) for arbitrary tiers.
-RELP_HDN int big_cmp(const Val& x, const Val& y, const uint32_t* heap) {
+RELP_HDN int big_cmp_thread(const Val& x, const Val& y, const uint32_t* heap) {
     Ref rx, ry;
     ref_load(rx, x, heap); ref_load(ry, y, heap);
     if (rx.sign != ry.sign) return rx.sign < ry.sign ? -1 : 1;
@@ -692,6 +706,306 @@ RELP_HDN int big_cmp(const Val& x, const Val& y, const uint32_t* heap) {
     int nr = mag_mul(r, ry.num, ry.nn, rx.den, rx.nd);
     int c = mag_cmp(l, nl, r, nr);
     return rx.sign > 0 ? c : -c;
+}
+
+}  // namespace relp
+#include "relp_wcb.cuh"
+namespace relp {
+
+// ------------------------------------------------------------------------------------------
+// Cooperative tier: the same three operations on operands of any length, by a group of lanes
+// ------------------------------------------------------------------------------------------
+#if defined(__CUDACC__) && !defined(RELP_EMUL)
+struct WarpGroup {      // all 32 lanes of a warp, converged by the caller (one-dimensional blocks, a multiple of 32 threads)
+    __device__ int rank() const { return (int)(threadIdx.x & 31u); }
+    __device__ int size() const { return 32; }
+    __device__ void sync() const { __syncwarp(); }
+    __device__ uint32_t ballot(bool p) const { return __ballot_sync(0xffffffffu, p); }
+    template <class T> __device__ T shfl(T v, int src) const { return __shfl_sync(0xffffffffu, v, src); }
+    template <class T> __device__ T shfl_up(T v, int d) const { return __shfl_up_sync(0xffffffffu, v, d); }
+};
+#endif
+
+// The limb heap's first words are never a value (offset 0 is not a handle): words 2..3 hold the address of an
+// Arena that describes where scratch may be taken (set by the owner of the heap, null = nowhere).  Comparisons
+// have no arena argument; this is how big_cmp finds room for its two cross products when they are long.
+RELP_HD const ScratchExt* heap_scratch(const uint32_t* heap) {
+    const uint64_t a = (uint64_t)heap[2] | ((uint64_t)heap[3] << 32);
+    return (const ScratchExt*)(uintptr_t)a;
+}
+
+template <class G> struct WOp {          // scratch of one cooperative operation
+    WScratch<G> sc; int slot; bool locked;
+};
+template <class G> RELP_HD void wop_begin(const G& g, WOp<G>& op, uint32_t* heap, const Arena& ar) {
+    op.sc.slab = nullptr; op.sc.cap = 0; op.sc.used = 0; op.sc.heap = heap; op.slot = -1; op.locked = false;
+    op.sc.fallback = ar;
+    const ScratchExt* x = ar.ext;
+    if (x && x->scr_top) { op.sc.fallback.top = x->scr_top; op.sc.fallback.limit = x->scr_limit; }
+#if defined(__CUDA_ARCH__) && !defined(RELP_EMUL)
+    if (g.size() == 32 && x && x->wslab && x->wslots > 0) {      // a whole warp: its slab (%warpid is unique within a CTA only, hence the lock)
+        unsigned smid, warpid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        asm volatile("mov.u32 %0, %%warpid;" : "=r"(warpid));
+        const int slot = (int)((smid * 64u + warpid) % (unsigned)x->wslots);
+        int got = 0;
+        if (g.rank() == 0) got = atomicCAS(&x->wlock[slot], 0, 1) == 0;
+        got = g.shfl(got, 0);
+        if (got) { op.sc.slab = x->wslab + (size_t)slot * x->wslab_words; op.sc.cap = x->wslab_words; op.slot = slot; op.locked = true; }
+    }
+#endif
+    (void)g;
+}
+template <class G> RELP_HD void wop_end(const G& g, WOp<G>& op, const Arena& ar) {
+#if defined(__CUDA_ARCH__) && !defined(RELP_EMUL)
+    if (op.locked) { g.sync(); if (g.rank() == 0) atomicExch(&ar.ext->wlock[op.slot], 0); }
+#endif
+    (void)g; (void)op; (void)ar;
+}
+
+// store a canonical value (every lane holds the same lengths; the limbs are in memory)
+RELP_W Val w_store(const G& g, int sign, const uint32_t* num, int nn, const uint32_t* den, int nd, uint32_t* heap, const Arena& ar) {
+    if (nn == 0) return val_zero();
+    if (nn <= 2 && nd <= 2) {
+        const uint64_t a = num[0] | (nn > 1 ? (uint64_t)num[1] << 32 : 0), b = den[0] | (nd > 1 ? (uint64_t)den[1] << 32 : 0);
+        if (a <= 0x7fffffffffffffffULL && b <= 0x7fffffffffffffffULL) return make_small(sign < 0 ? -(int64_t)a : (int64_t)a, (int64_t)b);
+    }
+    if (nn > RELP_MAX_LIMBS || nd > RELP_MAX_LIMBS) { set_err(ar.err, ERR_LIMB_CAPACITY); return val_zero(); }
+    long long off = 0;
+    if (g.rank() == 0) off = arena_alloc(ar, 1u + nn + nd);
+    off = g.shfl(off, 0);
+    if (off < 0) return val_zero();
+    uint32_t* p = heap + off;
+    if (g.rank() == 0) p[0] = (uint32_t)nn | ((uint32_t)nd << 14) | (sign < 0 ? 0x80000000u : 0u);
+    for (int i = g.rank(); i < nn; i += g.size()) p[1 + i] = num[i];
+    for (int i = g.rank(); i < nd; i += g.size()) p[1 + nn + i] = den[i];
+    g.sync();
+    Val v; v.n = off; v.d = 0;
+    return v;
+}
+RELP_W Val w_copy_val(const G& g, const Val& v, uint32_t* heap, const Arena& ar) {
+    if (v.d != 0) return v;
+    const unsigned w = big_words(heap, v);
+    long long off = 0;
+    if (g.rank() == 0) off = arena_alloc(ar, w);
+    off = g.shfl(off, 0);
+    if (off < 0) return val_zero();
+    for (unsigned i = g.rank(); i < w; i += g.size()) heap[off + i] = heap[v.n + i];
+    g.sync();
+    Val o; o.n = off; o.d = 0;
+    return o;
+}
+
+// gcd(p, q) of two magnitudes that must stay intact, into scratch; *gp points at it, returns its limbs.
+// gcd = 1 is recognised without any work when either operand is 1 (*gp = nullptr then, and 1 is returned).
+RELP_W int w_gcd_of(const G& g, WScratch<G>& sc, const uint32_t* p, int np, const uint32_t* q, int nq, uint32_t** gp) {
+    *gp = nullptr;
+    if ((np == 1 && p[0] == 1) || (nq == 1 && q[0] == 1)) return 1;
+    const int cap = (np > nq ? np : nq) + 3;
+    uint32_t* u = sc.take(g, cap); uint32_t* v = sc.take(g, cap);
+    uint32_t* t1 = sc.take(g, cap); uint32_t* t2 = sc.take(g, cap); uint32_t* t3 = sc.take(g, cap);
+    if (!u || !v || !t1 || !t2 || !t3) return -1;
+    w_copy(g, u, p, np); w_copy(g, v, q, nq);
+    const int ng = w_gcd(g, u, np, v, nq, t1, t2, t3, gp);
+    if (ng == 1 && (*gp)[0] == 1) *gp = nullptr;
+    return ng;
+}
+// p / d exactly into fresh scratch (p stays intact); d == nullptr means 1: the operand itself is returned
+RELP_W const uint32_t* w_quot(const G& g, WScratch<G>& sc, const uint32_t* p, int np, const uint32_t* d, int nd, int* nout) {
+    if (!d) { *nout = np; return p; }
+    uint32_t* out = sc.take(g, np + 1); uint32_t* cp = sc.take(g, np + 1);
+    uint32_t* dt = sc.take(g, nd + 1); uint32_t* pt = sc.take(g, nd + 2);
+    if (!out || !cp || !dt || !pt) { *nout = -1; return nullptr; }
+    w_copy(g, cp, p, np);
+    *nout = w_divexact(g, out, cp, np, d, nd, dt, pt);
+    return out;
+}
+
+// Sanity of an operand before a cooperative operation walks it: a handle must lie inside the heap and its header must
+// describe limbs that do too.  A violation is reported (ERR_PEER bit + a location code in ext->dbg), not followed.
+RELP_HD bool w_check(const Val& v, const uint32_t* heap, const Arena& ar, int where) {
+    if (v.d != 0) return v.d > 0;
+    const ScratchExt* x = ar.ext;
+    if (!x || !x->heap_words) return true;
+    bool ok = v.n >= 16 && (unsigned long long)v.n < x->heap_words;
+    if (ok) { const uint32_t h = heap[v.n]; const unsigned nn = h & 0x3fff, nd = (h >> 14) & 0x3fff; ok = nn >= 1 && nd >= 1 && (unsigned long long)v.n + 1 + nn + nd <= x->heap_words; }
+    if (!ok) { set_err(ar.err, ERR_PEER); const_cast<ScratchExt*>(x)->dbg = where; }
+    return ok;
+}
+
+// out = x + s * a * b, cooperative (same steps as big_fma_thread: Knuth 4.5.1 / mpq)
+RELP_W Val wcb_fma(const G& g, const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) {
+    if (!w_check(x, heap, ar, 1) || !w_check(a, heap, ar, 2) || !w_check(b, heap, ar, 3)) return val_zero();
+    Ref rx, ra, rb;
+    ref_load(rx, x, heap); ref_load(ra, a, heap); ref_load(rb, b, heap);
+    if (ra.sign == 0 || rb.sign == 0) return w_copy_val(g, x, heap, ar);
+    WOp<G> op; wop_begin(g, op, heap, ar);
+    WScratch<G>& sc = op.sc;
+    Val out = val_zero();
+    bool fail = false;
+    do {
+        uint32_t* gp; int ng, n1, n2, m1, m2;
+        // t = a * b in lowest terms: (a.n / g1)(b.n / g2) / ((a.d / g2)(b.d / g1))
+        ng = w_gcd_of(g, sc, ra.num, ra.nn, rb.den, rb.nd, &gp); if (ng < 0) { fail = true; break; }
+        const uint32_t* f1 = w_quot(g, sc, ra.num, ra.nn, gp, ng, &n1);
+        const uint32_t* f2 = w_quot(g, sc, rb.den, rb.nd, gp, ng, &n2);
+        ng = w_gcd_of(g, sc, rb.num, rb.nn, ra.den, ra.nd, &gp); if (ng < 0) { fail = true; break; }
+        const uint32_t* h1 = w_quot(g, sc, rb.num, rb.nn, gp, ng, &m1);
+        const uint32_t* h2 = w_quot(g, sc, ra.den, ra.nd, gp, ng, &m2);
+        if (n1 < 0 || n2 < 0 || m1 < 0 || m2 < 0) { fail = true; break; }
+        uint32_t* tn = sc.take(g, n1 + m1 + 1); uint32_t* td = sc.take(g, n2 + m2 + 1);
+        if (!tn || !td) { fail = true; break; }
+        const int ntn = w_mul(g, tn, f1, n1, h1, m1), ntd = w_mul(g, td, h2, m2, f2, n2);
+        const int st = ra.sign * rb.sign * s;
+        if (rx.sign == 0) { out = w_store(g, st, tn, ntn, td, ntd, heap, ar); break; }
+        // x + t: d1 = gcd(x.d, t.d)
+        uint32_t* d1; const int nd1 = w_gcd_of(g, sc, rx.den, rx.nd, td, ntd, &d1); if (nd1 < 0) { fail = true; break; }
+        int nxq, ntq;
+        const uint32_t* xq = w_quot(g, sc, rx.den, rx.nd, d1, nd1, &nxq);
+        const uint32_t* tq = w_quot(g, sc, td, ntd, d1, nd1, &ntq);
+        if (nxq < 0 || ntq < 0) { fail = true; break; }
+        const int npq = (rx.nn + ntq > ntn + nxq ? rx.nn + ntq : ntn + nxq) + 2;     // P also receives P + Q or |P - Q|
+        uint32_t* P = sc.take(g, npq); uint32_t* Q = sc.take(g, npq);
+        if (!P || !Q) { fail = true; break; }
+        int np = w_mul(g, P, rx.num, rx.nn, tq, ntq), nq = w_mul(g, Q, tn, ntn, xq, nxq);
+        int sign;
+        if (rx.sign == st) { np = w_add(g, P, P, np, Q, nq); sign = st; }
+        else {
+            const int c = w_cmp(g, P, np, Q, nq);
+            if (c == 0) break;                                        // exact cancellation: zero
+            if (c > 0) { np = w_sub(g, P, P, np, Q, nq); sign = rx.sign; }
+            else { np = w_sub(g, P, Q, nq, P, np); sign = st; }
+        }
+        if (!d1) {      // coprime denominators: (x.n t.d + t.n x.d) / (x.d t.d) is in lowest terms
+            uint32_t* den = sc.take(g, rx.nd + ntd + 1); if (!den) { fail = true; break; }
+            const int nden = w_mul(g, den, rx.den, rx.nd, td, ntd);
+            out = w_store(g, sign, P, np, den, nden, heap, ar);
+            break;
+        }
+        // d2 = gcd(num, d1); result (num / d2) / ((x.d / d1)(t.d / d2))
+        uint32_t* d2; const int nd2 = w_gcd_of(g, sc, P, np, d1, nd1, &d2); if (nd2 < 0) { fail = true; break; }
+        int nnum, ntd2;
+        const uint32_t* num = w_quot(g, sc, P, np, d2, nd2, &nnum);
+        const uint32_t* td2 = w_quot(g, sc, td, ntd, d2, nd2, &ntd2);
+        if (nnum < 0 || ntd2 < 0) { fail = true; break; }
+        uint32_t* den = sc.take(g, nxq + ntd2 + 1); if (!den) { fail = true; break; }
+        const int nden = w_mul(g, den, xq, nxq, td2, ntd2);
+        out = w_store(g, sign, num, nnum, den, nden, heap, ar);
+    } while (false);
+    if (fail) set_err(ar.err, ERR_HEAP_EXHAUSTED);
+    wop_end(g, op, ar);
+    return out;
+}
+
+// out = x / y (y != 0), cooperative
+RELP_W Val wcb_div(const G& g, const Val& x, const Val& y, uint32_t* heap, const Arena& ar) {
+    if (!w_check(x, heap, ar, 4) || !w_check(y, heap, ar, 5)) return val_zero();
+    Ref rx, ry;
+    ref_load(rx, x, heap); ref_load(ry, y, heap);
+    if (rx.sign == 0) return val_zero();
+    WOp<G> op; wop_begin(g, op, heap, ar);
+    WScratch<G>& sc = op.sc;
+    Val out = val_zero();
+    bool fail = false;
+    do {
+        uint32_t* gp; int ng, n1, n2, m1, m2;
+        ng = w_gcd_of(g, sc, rx.num, rx.nn, ry.num, ry.nn, &gp); if (ng < 0) { fail = true; break; }
+        const uint32_t* f1 = w_quot(g, sc, rx.num, rx.nn, gp, ng, &n1);
+        const uint32_t* f2 = w_quot(g, sc, ry.num, ry.nn, gp, ng, &n2);
+        ng = w_gcd_of(g, sc, ry.den, ry.nd, rx.den, rx.nd, &gp); if (ng < 0) { fail = true; break; }
+        const uint32_t* h1 = w_quot(g, sc, ry.den, ry.nd, gp, ng, &m1);
+        const uint32_t* h2 = w_quot(g, sc, rx.den, rx.nd, gp, ng, &m2);
+        if (n1 < 0 || n2 < 0 || m1 < 0 || m2 < 0) { fail = true; break; }
+        uint32_t* num = sc.take(g, n1 + m1 + 1); uint32_t* den = sc.take(g, n2 + m2 + 1);
+        if (!num || !den) { fail = true; break; }
+        const int nn = w_mul(g, num, f1, n1, h1, m1), nd = w_mul(g, den, h2, m2, f2, n2);
+        out = w_store(g, rx.sign * ry.sign, num, nn, den, nd, heap, ar);
+    } while (false);
+    if (fail) set_err(ar.err, ERR_HEAP_EXHAUSTED);
+    wop_end(g, op, ar);
+    return out;
+}
+
+// sign(x - y), cooperative; `scr` says where the two cross products may live
+RELP_W int wcb_cmp(const G& g, const Val& x, const Val& y, const uint32_t* heap, const Arena& scr) {
+    Ref rx, ry;
+    ref_load(rx, x, heap); ref_load(ry, y, heap);
+    if (rx.sign != ry.sign) return rx.sign < ry.sign ? -1 : 1;
+    if (rx.sign == 0) return 0;
+    // lengths decide most comparisons: |x.n y.d| has nn + nd or nn + nd - 1 limbs
+    const int ll = rx.nn + ry.nd, lr = ry.nn + rx.nd;
+    if (ll > lr + 1) return rx.sign > 0 ? 1 : -1;
+    if (lr > ll + 1) return rx.sign > 0 ? -1 : 1;
+    WOp<G> op; wop_begin(g, op, const_cast<uint32_t*>(heap), scr);
+    int c = 0;
+    uint32_t* l = op.sc.take(g, ll + 1); uint32_t* r = op.sc.take(g, lr + 1);
+    if (!l || !r) set_err(scr.err, ERR_HEAP_EXHAUSTED);
+    else {
+        const int nl = w_mul(g, l, rx.num, rx.nn, ry.den, ry.nd), nr = w_mul(g, r, ry.num, ry.nn, rx.den, rx.nd);
+        c = w_cmp(g, l, nl, r, nr);
+    }
+    wop_end(g, op, scr);
+    return rx.sign > 0 ? c : -c;
+}
+
+// ---- the multi-limb entry points: per-thread routines for short operands, the cooperative ones beyond ----
+RELP_HD int ref_max_limbs(const Val& v, const uint32_t* heap) {
+    if (v.d != 0) return 2;
+    const uint32_t h = heap[v.n];
+    const int nn = (int)(h & 0x3fff), nd = (int)((h >> 14) & 0x3fff);
+    return nn > nd ? nn : nd;
+}
+RELP_HD int imax3(int a, int b, int c) { return a > b ? (a > c ? a : c) : (b > c ? b : c); }
+
+#ifdef RELP_WCB_TRACE
+#include <cstdio>
+static void relp_wcb_trace(const char* op, const Val& x, const Val& a, const Val& b, int s, const uint32_t* heap) {
+    static FILE* f = fopen("/root/repo/gpurun_out/wcb_trace.txt", "w");
+    fprintf(f, "%s s=%d", op, s);
+    const Val* vs[3] = {&x, &a, &b};
+    for (int q = 0; q < 3; q++) {
+        Ref r; ref_load(r, *vs[q], heap);
+        fprintf(f, " | sign %d num", r.sign);
+        for (int i = 0; i < r.nn; i++) fprintf(f, " %08x", r.num[i]);
+        fprintf(f, " den");
+        for (int i = 0; i < r.nd; i++) fprintf(f, " %08x", r.den[i]);
+    }
+    fprintf(f, "\n"); fflush(f);
+}
+#endif
+// From arbitrary (divergent) code a long operation is done by the calling lane alone, with the cooperative routines
+// on a group of one: correct everywhere, no fixed size.  The stages that have many long operations call wcb_fma /
+// wcb_div themselves with a converged WarpGroup (stage_update_big, relp_kernels.cuh).
+// (An earlier version let whatever lanes had arrived together -- cooperative_groups::coalesced_threads() -- share each
+// operation: right in a plain kernel, but inside the stages, where lanes arrive from loops with different trip counts,
+// it hung or faulted on the device, while the same code on one lane per operation passed every test.)
+RELP_HDN Val big_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) {
+    const int thr = (ar.ext && ar.ext->coop_from < RELP_OPL) ? ar.ext->coop_from : RELP_OPL;
+    if (imax3(ref_max_limbs(x, heap), ref_max_limbs(a, heap), ref_max_limbs(b, heap)) <= thr) return big_fma_thread(x, a, b, s, heap, ar);
+#ifdef RELP_WCB_TRACE
+    relp_wcb_trace("fma", x, a, b, s, heap);
+#endif
+    return wcb_fma(SoloGroup(), x, a, b, s, heap, ar);
+}
+
+RELP_HDN Val big_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar) {
+    const int thr = (ar.ext && ar.ext->coop_from < RELP_OPL) ? ar.ext->coop_from : RELP_OPL;
+    const int mx = ref_max_limbs(x, heap), my = ref_max_limbs(y, heap);
+    if ((mx > my ? mx : my) <= thr) return big_div_thread(x, y, heap, ar);
+#ifdef RELP_WCB_TRACE
+    relp_wcb_trace("div", x, y, y, 0, heap);
+#endif
+    return wcb_div(SoloGroup(), x, y, heap, ar);
+}
+
+RELP_HDN int big_cmp(const Val& x, const Val& y, const uint32_t* heap) {
+    const int mx = ref_max_limbs(x, heap), my = ref_max_limbs(y, heap);
+    if ((mx > my ? mx : my) <= RELP_OPL) return big_cmp_thread(x, y, heap);
+    const ScratchExt* ext = heap_scratch(heap);
+    Arena scr;                            // no result is stored: only the scratch provider matters
+    scr.ext = ext;
+    if (ext) { scr.top = ext->scr_top; scr.limit = ext->scr_limit; scr.err = ext->err; }
+    return wcb_cmp(SoloGroup(), x, y, heap, scr);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -108,6 +108,8 @@ struct relp_ctx {
     long long wide_handoffs = 0;
     // peer transport (multi-GPU persistent loop): this rank's exchange buffer and the peers' as mapped here
     DBuf<unsigned char> xbuf; void* peer_base[RELP_MAX_WORLD] = {}; bool peer_mode = false; int peer_max_m = 0;
+    // cooperative multi-limb tier: scratch slabs (one per resident warp slot), their locks, and the Arena that big_cmp finds through the heap
+    DBuf<uint32_t> wslab; DBuf<int> wlock; DBuf<ScratchExt> scr_ext; unsigned wslab_words = 2048; int coop_from = RELP_OPL;
     unsigned long long epoch = 0;
     int k1_bench_frac = 0;          // option "k1_bench_frac": relp_debug_k1_dense fills the block with general rationals
     long long k1_exit = 8 << 20;    // option "k1_exit": T x S from which the persistent loop hands a dense update to k_update
@@ -152,10 +154,10 @@ static int push_state(relp_ctx* c) {
 }
 static int err_status(const DState* s) {
     if (s->err & ERR_ZERO_PIVOT) { set_error("Pivot value can't be zero"); return RELP_ERR_ZERO_PIVOT; }
-    if (s->err & ERR_LIMB_CAPACITY) { set_error("a numerator/denominator exceeded RELP_OPL limbs"); return RELP_ERR_LIMB_CAPACITY; }
+    if (s->err & ERR_LIMB_CAPACITY) { set_error("a numerator/denominator exceeded 16383 limbs (the header's length field)"); return RELP_ERR_LIMB_CAPACITY; }
     if (s->err & ERR_HEAP_EXHAUSTED) { set_error("limb heap exhausted: create the context with a larger heap_words"); return RELP_ERR_HEAP_EXHAUSTED; }
     if (s->err & ERR_PEER_BIG) { set_error("a multi-limb value would have to cross GPUs (ratio or pivot row): solve this LP on one GPU"); return RELP_ERR_LIMB_CAPACITY; }
-    if (s->err & ERR_PEER) { set_error("peer exchange: a rank reported an error or did not answer in time"); return RELP_ERR_COMM; }
+    if (s->err & ERR_PEER) { set_error("peer exchange: a rank reported an error or did not answer in time (or a cooperative multi-limb operation met an invalid handle)"); return RELP_ERR_COMM; }
     return 0;
 }
 
@@ -283,6 +285,7 @@ relp_ctx* relp_create(int device, int rank, int world, uint64_t heap_words) {
     }
     memset(c->h_st, 0, sizeof(DState));
     memset(&c->D, 0, sizeof(Dev));
+    cudaMemset(c->heap.p, 0, 64);          // words 0..15 are never a value; 2..3 = address of the scratch Arena (null so far)
     return c;
 }
 
@@ -492,6 +495,7 @@ static void wire_dev(relp_ctx* c) {
     D.rn = c->rn.p; D.rd = c->rd.p; D.row_ptr = c->row_ptr_d.p; D.csr_ent = c->csr_ent.p;
     D.colbits = c->colbits.p; D.rowbits = c->rowbits.p; D.colsum = c->colsum.p; D.claim = c->claim.p; D.row_art = c->row_art.p;
     wire_peers(c);
+    D.ext = c->scr_ext.p;
     D.gather = c->gather.p; D.log = c->log.p; D.log_cap = (long long)c->log.n; D.trace = c->trace.p; D.zbits = c->zbits.p;
 }
 
@@ -519,6 +523,26 @@ static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
     if (c->worklist.alloc(c->wl_cap)) return RELP_ERR_CUDA;
     if (c->cand.alloc(MAX_PARTIAL_BLOCKS) || c->cand2.alloc(MAX_PARTIAL_BLOCKS) || c->gather.alloc(c->world + 1)) return RELP_ERR_CUDA;
     if (!c->log.p && c->log.alloc(1 << 20)) return RELP_ERR_CUDA;
+    if (!c->wslab.p) {
+        const size_t slots = (size_t)c->sm_count * 64;
+        if (c->wslab.alloc(slots * c->wslab_words) || c->wlock.alloc(slots) || c->scr_ext.alloc(1)) return RELP_ERR_CUDA;
+    }
+    CUDA_TRY(cudaMemsetAsync(c->wlock.p, 0, c->wlock.n * sizeof(int), c->stream));
+    return 0;
+}
+
+// The scratch description every slow path reads (Arena::ext) and big_cmp finds through words 2..3 of the heap
+// (relp_arith.cuh heap_scratch).  Written whenever the heap regions are (re)defined or an option changes.
+static int publish_scratch_arena(relp_ctx* c, const DState* s) {
+    ScratchExt a;
+    a.wslab = c->wslab.p; a.wslab_words = c->wslab_words; a.wlock = c->wlock.p; a.wslots = c->wslab.p ? c->sm_count * 64 : 0;
+    a.scr_top = &c->st.p->tr_top; a.scr_limit = s->tr_limit; a.err = &c->st.p->err; a.coop_from = c->coop_from;
+    a.heap_words = c->heap_words;
+    CUDA_TRY(cudaMemcpyAsync(c->scr_ext.p, &a, sizeof(a), cudaMemcpyHostToDevice, c->stream));
+    const uint64_t addr = (uint64_t)(uintptr_t)c->scr_ext.p;
+    uint32_t words[4] = { 0u, 0u, (uint32_t)addr, (uint32_t)(addr >> 32) };
+    CUDA_TRY(cudaMemcpyAsync(c->heap.p, words, sizeof(words), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
     return 0;
 }
 
@@ -756,6 +780,7 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap; s->k1_min = c->k1_min; s->k1_exit = c->k1_exit;
     init_heap_regions(c, s);
     if (push_state(c)) return RELP_ERR_CUDA;
+    if (publish_scratch_arena(c, s)) return RELP_ERR_CUDA;
     {   // row -> artificial column
         std::vector<int> ra(m, -1);
         for (int a = 0; a < nr_art; a++) ra[c->art_rows_h[a]] = a;
@@ -945,6 +970,7 @@ static int from_basis(relp_ctx* c, const int32_t* basis_in) {
     s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap; s->k1_min = c->k1_min; s->k1_exit = c->k1_exit;
     init_heap_regions(c, s);
     if (push_state(c)) return RELP_ERR_CUDA;
+    if (publish_scratch_arena(c, s)) return RELP_ERR_CUDA;
     wire_dev(c);
     LAUNCH(c, k_init_planes, c->sm_count * 8, RELP_THREADS, c->D, c->rhsn_d.p, c->rhsd_d.p);
     CUDA_TRY(cudaMemsetAsync(c->colbits.p, 0, ((size_t)(m + 1) * (c->ld / 32)) * 4, c->stream));
@@ -1072,8 +1098,8 @@ static int solve_continue(relp_ctx* c, int64_t max_pivots) {
         if (c->stage == 1) {
             if (st == RELP_UNBOUNDED) { c->stage = 3; c->final_status = RELP_ERR_PHASE1_UNBOUNDED; return c->final_status; }
             // phase 1 finished: feasible iff the artificial objective is exactly zero (phase_one.rs:146-167)
-            int64_t on, od; size_t used = 0; uint32_t limbs[2 * RELP_OPL + 2];
-            int rc = read_block_impl(c, c->zn.p, c->zd.p, 1, 1, 1, 1, &on, &od, limbs, sizeof(limbs) / 4, &used);
+            int64_t on, od; size_t used = 0; std::vector<uint32_t> limbs(2 * RELP_MAX_LIMBS + 2);
+            int rc = read_block_impl(c, c->zn.p, c->zd.p, 1, 1, 1, 1, &on, &od, limbs.data(), limbs.size(), &used);
             if (rc) return rc;
             if (!(on == 0 && od == 1)) { c->stage = 3; c->final_status = RELP_INFEASIBLE; return RELP_INFEASIBLE; }
             rc = remove_artificial_basis_variables(c);
@@ -1293,6 +1319,8 @@ int relp_set_option(relp_ctx* c, const char* name, int64_t value) {
     if (!strcmp(name, "k1_min")) { c->k1_min = value; return RELP_OK; }
     if (!strcmp(name, "k1_exit")) { c->k1_exit = value; return RELP_OK; }
     if (!strcmp(name, "k1_bench_frac")) { c->k1_bench_frac = value != 0; return RELP_OK; }     // takes effect when the Carry is next created
+    if (!strcmp(name, "coop_from")) { c->coop_from = (int)std::max<int64_t>(1, std::min<int64_t>(value, RELP_OPL)); if (c->carry_ready && c->scr_ext.p) { if (sync_state(c) || publish_scratch_arena(c, c->h_st)) return RELP_ERR_CUDA; } return RELP_OK; }   // limbs from which operations are cooperative
+    if (!strcmp(name, "wslab_words")) { c->wslab_words = (unsigned)std::max<int64_t>(64, value); c->wslab.release(); return RELP_OK; }   // takes effect when the Carry is next created
     if (!strcmp(name, "coop_blocks")) { c->coop_blocks = (int)value; return RELP_OK; }   // debug: CTAs of the persistent kernel
     if (!strcmp(name, "trace")) {      // debug: per-CTA barrier arrival times of the last iteration
         if (value) { if (c->trace.alloc(16 * 4096)) return RELP_ERR_CUDA; cudaMemset(c->trace.p, 0, 16 * 4096 * 8); }
@@ -1455,6 +1483,65 @@ int relp_debug_k1_verify(relp_ctx* c, uint64_t seed, int64_t* mismatches, int64_
     c->carry_ready = false;
     return RELP_OK;
 #endif
+}
+
+// Direct test hook for the exact arithmetic AS IT RUNS IN KERNELS (tests/test_gpu_arith.py): `count` independent
+// operations, one per thread of ordinary 256-thread blocks, through the same front ends the stages use (val_fma /
+// val_div / val_cmp) -- so neighbouring lanes with long operands meet in the cooperative routines of relp_wcb.cuh
+// with whatever lanes happen to be there, exactly as in a solve.  Operands are rat arrays over `limbs_in`.
+__global__ void k_debug_rat_op(Dev D, int op, int count, const int64_t* in, unsigned long long base, int s, int64_t* on, int64_t* od) {
+    Arena ar = transient(D);
+#ifndef RELP_EMUL
+    const WarpGroup wg;
+#endif
+    const int nth = gridDim.x * blockDim.x, rounds = (count + nth - 1) / nth;
+    for (int rd = 0; rd < rounds; rd++) {              // the same trip count for every thread: op 3 needs whole warps
+        const int t = rd * nth + blockIdx.x * blockDim.x + threadIdx.x;
+        const bool have = t < count;
+        Val v[3];
+        for (int q = 0; q < 3; q++) {
+            v[q] = val_zero();
+            if (have) { v[q].n = in[(size_t)(2 * q) * count + t]; v[q].d = in[(size_t)(2 * q + 1) * count + t]; if (v[q].d == 0) v[q].n += (int64_t)base; }
+        }
+        Val out = val_zero();
+        if (op == 3) {          // x + s a b, every operation by the 32 lanes of its warp together (the way stage_update_big does)
+#ifndef RELP_EMUL
+            unsigned need = __ballot_sync(0xffffffffu, have);
+            while (need) {
+                const int r = ctz32(need); need &= need - 1;
+                Val X[3];
+                for (int q = 0; q < 3; q++) { X[q].n = __shfl_sync(0xffffffffu, v[q].n, r); X[q].d = __shfl_sync(0xffffffffu, v[q].d, r); }
+                const Val o = wcb_fma(wg, X[0], X[1], X[2], s, D.heap, ar);
+                if ((int)(threadIdx.x & 31) == r) out = o;
+            }
+#endif
+        } else if (have) {
+            if (op == 0) out = val_fma(v[0], v[1], v[2], s, D.heap, ar);
+            else if (op == 1) out = val_div(v[0], v[1], D.heap, ar);
+            else out = make_small(val_cmp(v[0], v[1], D.heap), 1);
+        }
+        if (have) { on[t] = out.n; od[t] = out.d; }
+    }
+}
+
+int relp_debug_rat_op(relp_ctx* c, int op, int32_t count, const int64_t* operands /* 6 x count: xn xd an ad bn bd */,
+                      const uint32_t* limbs_in, size_t limb_words, int s,
+                      int64_t* num, int64_t* den, uint32_t* limbs, size_t limb_cap, size_t* limb_used) {
+    if (!c || !c->carry_ready || count < 1 || !operands || !num || !den || op < 0 || op > 3) return RELP_ERR_ARGUMENT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    DBuf<int64_t> in, on, od;
+    if (in.alloc((size_t)6 * count) || on.alloc(count) || od.alloc(count)) return RELP_ERR_CUDA;
+    LAUNCH(c, k_reset_transient, 1, 1, c->st.p);
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    const unsigned long long base = c->h_st->tr_top;
+    if (base + limb_words + 16 > c->h_st->tr_limit) { set_error("operands do not fit the transient region: larger heap_words"); return RELP_ERR_HEAP_EXHAUSTED; }
+    if (limb_words) CUDA_TRY(cudaMemcpyAsync(c->heap.p + base, limbs_in, limb_words * 4, cudaMemcpyHostToDevice, c->stream));
+    c->h_st->tr_top = base + limb_words;
+    if (push_state(c)) return RELP_ERR_CUDA;
+    CUDA_TRY(cudaMemcpyAsync(in.p, operands, (size_t)6 * count * 8, cudaMemcpyHostToDevice, c->stream));
+    LAUNCH(c, k_debug_rat_op, clampi(cdiv(count, 256), 1, c->sm_count * 4), 256, c->D, op, (int)count, in.p, base, s, on.p, od.p);
+    if (check_cuda(c)) return RELP_ERR_CUDA;
+    return read_block_impl(c, on.p, od.p, 1, 1, count, 1, num, den, limbs, limb_cap, limb_used, true);
 }
 
 int relp_debug_trace(relp_ctx* c, uint64_t* out, int32_t n_ctas) {

@@ -136,6 +136,7 @@ struct Dev {
     // multi-GPU persistent loop: world > 1 and peers mapped (0 / 1 otherwise)
     int xworld, xrank; unsigned long long xepoch;
     uint32_t* xbits;                          // bitmap p_k != 0 of the current pivot row (replicated copy)
+    const ScratchExt* ext;                    // scratch of the cooperative multi-limb operations (slabs + locks), in device memory
     XPeer xp[RELP_MAX_WORLD];                 // xp[xrank] is this rank's own buffer
 };
 
@@ -151,6 +152,9 @@ struct Dev {
 #define RELP_CHG 8                // column generation: B^-1 column reads in flight per row
 #endif
 #define RELP_MAXWARPS 32
+#ifndef RELP_COOP_FEW
+#define RELP_COOP_FEW 12              // stage_update_big with few queued elements: operations longer than this many limbs are shared by the warp
+#endif
 
 struct Grid { int tid, nth, bid, nb; };
 #if !defined(RELP_EMUL) && defined(RELP_WTRACE)
@@ -175,11 +179,12 @@ __device__ __forceinline__ Inv load_inv(const DState* st) {
     I.wsc = (I.wpc + 31) >> 5;                        // words per column of colsum
     return I;
 }
+// (a.ext: where the cooperative multi-limb operations take their temporaries -- relp_wcb.cuh)
 __device__ __forceinline__ Arena transient(const Dev& D) {
-    Arena a; a.top = &D.st->tr_top; a.limit = D.st->tr_limit; a.err = &D.st->err; return a;
+    Arena a; a.top = &D.st->tr_top; a.limit = D.st->tr_limit; a.err = &D.st->err; a.ext = D.ext; return a;
 }
 __device__ __forceinline__ Arena persistent(const Dev& D) {
-    Arena a; a.top = &D.st->pool_top; a.limit = D.st->pool_limit; a.err = &D.st->err; return a;
+    Arena a; a.top = &D.st->pool_top; a.limit = D.st->pool_limit; a.err = &D.st->err; a.ext = D.ext; return a;
 }
 __device__ __forceinline__ bool halted(const DState* st) {
     return st->status != ST_RUNNING || st->err != 0 || st->iter >= st->iter_limit;
@@ -1003,11 +1008,16 @@ __device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, i
     }
 }
 
-// Stage F -- K1c: the queued elements in the multi-limb tier.
+// Stage F -- K1c: the queued elements in the multi-limb tier.  Every warp takes 32 consecutive entries of the queue:
+// elements whose operands are short (<= `coop_from` limbs, at most RELP_OPL) are done by their own lane with the
+// per-thread routines; the long ones are then done one after the other by the WHOLE warp (relp_wcb.cuh: limbs across
+// lanes, carries by ballot, Lehmer steps on the leading limbs) -- the warp is converged here by construction, and a
+// long operation's latency is what the stage waits for when few elements are queued.
 __device__ void stage_update_big(const Dev& D, const Grid& g, const Inv& I) {
     DState* st = D.st;
     const int n = st->wl_count < st->wl_cap ? st->wl_count : st->wl_cap; const size_t ld = I.ld;
     Arena ar = persistent(D);
+#ifdef RELP_EMUL
     for (int w = g.tid; w < n; w += g.nth) {
         int2 it = D.worklist[w];
         size_t e = (size_t)it.y * ld + it.x;
@@ -1016,6 +1026,43 @@ __device__ void stage_update_big(const Dev& D, const Grid& g, const Inv& I) {
         st_val(D.xn, D.xd, e, out);
         if ((x.n != 0) != (out.n != 0)) pattern_set(D, I, it.x, it.y, out.n != 0);
     }
+#else
+    if (n == 0) return;
+    const int lane = threadIdx.x & 31, nwarps = g.nth >> 5;
+    // few elements for the machine: a long operation done by one thread is what everybody waits for -- share them earlier
+    int thr = D.ext->coop_from < RELP_OPL ? D.ext->coop_from : RELP_OPL;
+    if (n <= 2 * nwarps && thr > RELP_COOP_FEW) thr = RELP_COOP_FEW;
+    const WarpGroup wg;
+    for (int base = (g.tid >> 5) * 32; base < n; base += nwarps * 32) {       // the same trip count for the 32 lanes of a warp
+        const int w = base + lane;
+        const bool have = w < n;
+        int2 it = make_int2(0, 0);
+        size_t e = 0;
+        Val x = val_zero(), dv = val_zero(), pv = val_zero(), out = val_zero();
+        bool lng = false;
+        if (have) {
+            it = D.worklist[w];
+            e = (size_t)it.y * ld + it.x;
+            x = ld_val(D.xn, D.xd, e); dv = ld_val(D.dn, D.dd, it.x); pv = ld_val(D.pn, D.pd, it.y);
+            lng = imax3(ref_max_limbs(x, D.heap), ref_max_limbs(dv, D.heap), ref_max_limbs(pv, D.heap)) > thr;
+            if (!lng) out = big_fma_thread(x, dv, pv, -1, D.heap, ar);
+        }
+        unsigned need = __ballot_sync(0xffffffffu, have && lng);
+        while (need) {
+            const int r = ctz32(need); need &= need - 1;
+            Val X, A, B;
+            X.n = __shfl_sync(0xffffffffu, x.n, r); X.d = __shfl_sync(0xffffffffu, x.d, r);
+            A.n = __shfl_sync(0xffffffffu, dv.n, r); A.d = __shfl_sync(0xffffffffu, dv.d, r);
+            B.n = __shfl_sync(0xffffffffu, pv.n, r); B.d = __shfl_sync(0xffffffffu, pv.d, r);
+            const Val o = wcb_fma(wg, X, A, B, -1, D.heap, ar);
+            if (lane == r) out = o;
+        }
+        if (have) {
+            st_val(D.xn, D.xd, e, out);
+            if ((x.n != 0) != (out.n != 0)) pattern_set(D, I, it.x, it.y, out.n != 0);
+        }
+    }
+#endif
 }
 
 // one thread, after stage F has completed everywhere

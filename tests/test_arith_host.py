@@ -21,10 +21,10 @@ OUT = os.path.join(ROOT, "tests", "native", "_build", "libarith_host_test.so")
 @pytest.fixture(scope="module")
 def L():
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
-    deps = [SRC, os.path.join(INC, "relp_arith.cuh")]
+    deps = [SRC, os.path.join(INC, "relp_arith.cuh"), os.path.join(INC, "relp_wcb.cuh")]
     if not os.path.exists(OUT) or any(os.path.getmtime(d) > os.path.getmtime(OUT) for d in deps):
         subprocess.check_call(["g++", "-O1", "-g", "-std=c++17", "-fPIC", "-shared", "-fsanitize=undefined",
-                               "-fno-sanitize-recover=undefined", "-I", INC, "-x", "c++", SRC, "-o", OUT])
+                               "-fno-sanitize-recover=undefined", "-I", INC, "-x", "c++", SRC, "-o", OUT, "-lpthread"])
     lib = C.CDLL(OUT)
     lib.t_gcd64.restype = C.c_uint64
     lib.t_gcd64.argtypes = [C.c_uint64, C.c_uint64]
@@ -161,12 +161,122 @@ def test_fma_div_cmp_random(L, bits, seed):
         assert L.t_err() == 0
 
 
-def test_limb_capacity_is_reported(L):
+def test_no_fixed_limb_capacity(L):
+    """RationalBig is unbounded (rational/big/mod.rs:17-29), so a value longer than what ONE thread
+    handles (RELP_OPL limbs) is not an error: the cooperative routines take over, through the same front ends."""
     L.t_reset()
     opl = L.t_opl()
     big = Fr(2 ** (32 * opl - 1) + 1, 3)
     v = mk(L, big)
     out = (C.c_int64 * 2)()
-    L.t_fma(mk(L, 0), v, v, 1, out)          # square needs 2*opl limbs -> capacity error, not garbage
-    assert L.t_err() & 1
+    L.t_fma(mk(L, 0), v, v, 1, out)          # the square has 2 * opl limbs
+    assert L.t_err() == 0 and rd(L, out) == big * big
+    w = mk(L, Fr(7 ** 900, 5 ** 700))        # 2527 / 1626 bits
+    L.t_fma(out, w, v, -1, out)
+    assert L.t_err() == 0 and rd(L, out) == big * big - Fr(7 ** 900, 5 ** 700) * big
+    L.t_div(out, w, out)
+    assert rd(L, out) == (big * big - Fr(7 ** 900, 5 ** 700) * big) / Fr(7 ** 900, 5 ** 700)
+    val, wf = rd(L, out), Fr(7 ** 900, 5 ** 700)
+    assert L.t_cmp(out, w) == (val > wf) - (val < wf) and L.t_cmp(w, out) == (wf > val) - (wf < val) and L.t_cmp(w, w) == 0
     L.t_reset()
+
+
+# ---- cooperative tier (relp_wcb.cuh): the templates run on S host threads behind a barrier -----------------
+W_OPS = {"add": 0, "sub": 1, "mul": 2, "mod": 3, "gcd": 4, "divexact": 5, "mul1": 6, "shl": 7, "shr": 8, "cmp": 9}
+
+
+def w_op(L, S, op, a, b):
+    aa, pa, na = _limbs_arg(a); bb, pb, nb = _limbs_arg(b)
+    out = np.zeros(2 * (na + nb) + 16 + (b // 32 if op == "shl" else 0), dtype=np.uint32)
+    n = L.t_w_op(S, W_OPS[op], pa, na, pb, nb, out.ctypes.data_as(C.c_void_p))
+    return n if op == "cmp" else _from_limbs(out, n)
+
+
+def _rnd_big(rnd, bits):
+    style = rnd.randrange(6)
+    if style == 0:
+        return (1 << bits) - 1                                   # all ones: carries ripple through every lane
+    if style == 1:
+        return 1 << (bits - 1)                                   # a single bit: borrows ripple
+    if style == 2:
+        return (((1 << bits) - 1) ^ (rnd.getrandbits(bits) & rnd.getrandbits(bits) & rnd.getrandbits(bits))) or 1   # mostly ones
+    if style == 3:
+        return rnd.getrandbits(bits) & ~((1 << rnd.randrange(bits)) - 1) | 1 << (bits - 1)                    # low zeros
+    return rnd.getrandbits(bits) | 1 << (bits - 1)
+
+
+@pytest.mark.parametrize("S", [1, 2, 3, 5, 8, 17, 32])
+def test_wcb_primitives(L, S):
+    """every pass of relp_wcb.cuh against Python integers, for group sizes that divide the lengths and that do not:
+    carry-lookahead across lanes and across chunks, column-sum multiplication, Knuth-D remainder with add-back,
+    Lehmer gcd, Jebelean exact division, shifts"""
+    rnd = random.Random(100 + S)
+    sizes = [1, 31, 32, 33, 63, 64, 65, 96, 127, 128, 129, 255, 256, 300, 511, 777, 1024, 1025, 2049, 3000]
+    for it in range(90 if S > 8 else 160):
+        ba, bb = rnd.choice(sizes), rnd.choice(sizes)
+        a, b = _rnd_big(rnd, ba), _rnd_big(rnd, bb)
+        assert w_op(L, S, "add", a, b) == a + b
+        hi, lo = max(a, b), min(a, b)
+        assert w_op(L, S, "sub", hi, lo) == hi - lo
+        assert w_op(L, S, "sub", hi, hi) == 0
+        assert w_op(L, S, "mul", a, b) == a * b
+        m1 = rnd.choice([1, 2, 0xffffffff, rnd.getrandbits(32) | 1])
+        assert w_op(L, S, "mul1", a, m1) == a * m1
+        sh = rnd.choice([1, 5, 31, 32, 33, 64, 100])
+        assert w_op(L, S, "shl", a, sh) == a << sh
+        if sh < ba:
+            assert w_op(L, S, "shr", a, sh) == a >> sh
+        assert w_op(L, S, "cmp", a, b) == (a > b) - (a < b)
+        assert w_op(L, S, "cmp", a, a) == 0
+        if a >= b:
+            assert w_op(L, S, "mod", a, b) == a % b
+        mode = it % 5
+        g = 1
+        if mode == 1:
+            g = rnd.getrandbits(rnd.choice([1, 31, 32, 64, 100, 300])) + 1
+        elif mode == 2:
+            g = 1 << rnd.randint(1, 70)
+        elif mode == 3:
+            a = b * (rnd.getrandbits(rnd.choice([1, 32, 33, 70])) + 1)
+        elif mode == 4:            # quotient digits at the 2^32 - 1 boundary / add-back candidates
+            b = (1 << bb) - rnd.getrandbits(min(20, bb)) - 1 if bb > 1 else 1
+            a = b * ((1 << 32) - 1) + rnd.getrandbits(max(bb - 1, 1))
+            assert w_op(L, S, "mod", a, b) == a % b
+        a2, b2 = a * g, b * g
+        assert w_op(L, S, "gcd", a2, b2) == math.gcd(a2, b2), (hex(a2), hex(b2))
+        d = math.gcd(a2, b2)
+        assert w_op(L, S, "divexact", a2, d) == a2 // d
+        q = rnd.getrandbits(rnd.choice([1, 32, 64, 200])) + 1
+        assert w_op(L, S, "divexact", a2 * q, q) == a2
+
+
+@pytest.mark.parametrize("S,bits,seed", [(1, 500, 1), (4, 130, 2), (32, 500, 3), (32, 3000, 4), (7, 3000, 5)])
+def test_wcb_rationals(L, S, bits, seed):
+    """wcb_fma / wcb_div / wcb_cmp (the cooperative versions of the three rational operations) against Fraction"""
+    rnd = random.Random(seed)
+    out = (C.c_int64 * 2)()
+
+    def big_frac():
+        nb = rnd.choice([1, 40, 64, 65, 200, bits])
+        db = rnd.choice([0, 1, 33, 64, 100, bits])
+        n = rnd.getrandbits(nb) * rnd.choice([1, -1])
+        if rnd.random() < 0.08:
+            n = 0
+        return Fr(n, rnd.getrandbits(db) + 1 if db else 1)
+
+    for it in range(40 if bits > 1000 else 120):
+        if it % 20 == 0:
+            L.t_reset()
+        x, a, b = big_frac(), big_frac(), big_frac()
+        if rnd.random() < 0.3:       # cancellations and shared factors
+            x = a * b * rnd.choice([1, -1]) if rnd.random() < 0.5 else x * Fr(a.denominator, max(1, b.denominator))
+        vx, va, vb = mk(L, x), mk(L, a), mk(L, b)
+        s = rnd.choice([1, -1])
+        L.t_w_fma(S, vx, va, vb, s, out)
+        assert rd(L, out) == x + s * a * b, (x, a, b, s)
+        if b != 0:
+            L.t_w_div(S, vx, vb, out)
+            assert rd(L, out) == x / b
+        assert L.t_w_cmp(S, vx, va) == (x > a) - (x < a)
+        assert L.t_w_cmp(S, vx, vx) == 0
+        assert L.t_err() == 0

@@ -176,3 +176,17 @@ def test_dense_update_ring_at_scale(m, frac):
     bad, n = c.debug_k1_verify(seed=20260101 + m)
     assert n == m * (m + 1) and bad == 0, (bad, n)
     c.close()
+
+
+@pytest.mark.parametrize("persistent", [True, False])
+def test_cooperative_multi_limb_tier_in_solves(persistent):
+    """option coop_from = 2: every operation on values beyond two limbs takes the arbitrary-length routines of
+    relp_wcb.cuh instead of the fixed-size per-thread ones -- whole warps in the Carry update's multi-limb stage, one
+    lane elsewhere -- same pivots, same Carry as the oracle"""
+    opts = {"coop_from": 2}
+    s, o = parity.check_full_solve(pa_from_lp(feasible_lp(0, 10, 2, 10, 6, 40, frac=True, maxval=9, density=0.4)), LIB,
+                                   expect_escalation=True, options=opts, persistent=persistent, heap_words=1 << 25)
+    assert o.max_bits() > 128
+    parity.check_full_solve(synthetic_lp(80, 400, 10, "growth"), LIB, expect_escalation=True, options=opts, persistent=persistent,
+                            heap_words=1 << 25)
+    parity.check_full_solve(pa_from_lp(feasible_lp(5, 3, 1, 3, 2, 10, frac=True, dup_rows=1)), LIB, options=opts, persistent=persistent)
