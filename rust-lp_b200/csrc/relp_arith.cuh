@@ -28,6 +28,16 @@
 #define RELP_HDN
 #endif
 
+// The headers can be compiled twice into one library: RELP_NS names the namespace of this copy.  relp_fastloop.cu
+// builds the persistent loop kernel with RELP_NO_WCB: the same code WITHOUT the arbitrary-length tier behind it (that
+// tier's call graph costs the hot int64 path 20 % -- measured -- through register allocation and code layout), for as
+// long as no stored value is longer than RELP_LONG_TRIGGER limbs; then the copy with the full tier takes over.
+#ifndef RELP_NS
+#define RELP_NS relp
+#endif
+#ifndef RELP_LONG_TRIGGER
+#define RELP_LONG_TRIGGER 12     // a stored numerator / denominator longer than this raises DState::long_seen (Arena::flag)
+#endif
 #ifndef RELP_OPL
 #define RELP_OPL 64              // operands up to this many limbs may be handled by ONE thread (fixed-size stack buffers);
                                  // longer ones go to the cooperative routines of relp_wcb.cuh, which have no fixed size
@@ -35,7 +45,7 @@
 #define RELP_TL (3 * RELP_OPL + 2)   // max limbs of an intermediate
 #define RELP_MAX_LIMBS 0x3fff        // what the header's 14-bit length fields can say (512 Kbit); the limb heap is the real bound
 
-namespace relp {
+namespace RELP_NS {
 
 typedef unsigned __int128 u128;
 typedef __int128 i128;
@@ -50,16 +60,23 @@ enum { ERR_NONE = 0, ERR_LIMB_CAPACITY = 1, ERR_HEAP_EXHAUSTED = 2, ERR_ZERO_PIV
 // Lives in memory (one per context); only the slow paths ever read it.
 struct ScratchExt {
     uint32_t* wslab = nullptr; unsigned wslab_words = 0; int* wlock = nullptr; int wslots = 0;
-    unsigned long long* scr_top = nullptr; unsigned long long scr_limit = 0; int* err = nullptr;
+    unsigned long long* scr_top = nullptr; unsigned long long scr_limit = 0; int* err = nullptr; int* flag = nullptr;
     int coop_from = RELP_OPL;    // operands longer than this many limbs leave the per-thread routines for the cooperative ones
     unsigned long long heap_words = 0;   // size of the limb heap (sanity checks of handles in the cooperative entry points)
     int dbg = 0;                 // first failed sanity check (0 = none): see w_check
 };
+// The limb heap's first words are never a value (offset 0 is not a handle): words 2..3 hold the address of the
+// ScratchExt of the heap's owner (null = none).  The slow paths find it there, so that the Arena every stage carries
+// in registers stays three words, and comparisons -- which have no arena argument -- find room for long cross products.
+RELP_HD const ScratchExt* heap_scratch(const uint32_t* heap) {
+    const uint64_t a = (uint64_t)heap[2] | ((uint64_t)heap[3] << 32);
+    return (const ScratchExt*)(uintptr_t)a;
+}
 struct Arena {
     unsigned long long* top = nullptr;
     unsigned long long limit = 0;
     int* err = nullptr;          // sticky error bits (ERR_*)
-    const ScratchExt* ext = nullptr;
+    int* flag = nullptr;         // set to 1 when a value longer than RELP_LONG_TRIGGER limbs is stored (DState::long_seen)
 };
 
 RELP_HD void set_err(int* err, int bit) {
@@ -562,6 +579,7 @@ RELP_HD Val store_val(int sign, const uint32_t* num, int nn, const uint32_t* den
             return make_small(sign < 0 ? -(int64_t)a : (int64_t)a, (int64_t)b);
     }
     if (nn > RELP_MAX_LIMBS || nd > RELP_MAX_LIMBS) { set_err(ar.err, ERR_LIMB_CAPACITY); return val_zero(); }
+    if ((nn > RELP_LONG_TRIGGER || nd > RELP_LONG_TRIGGER) && ar.flag) *ar.flag = 1;      // "long values exist"
     long long off = arena_alloc(ar, 1u + nn + nd);
     if (off < 0) return val_zero();
     uint32_t* p = heap + off;
@@ -708,9 +726,10 @@ RELP_HDN int big_cmp_thread(const Val& x, const Val& y, const uint32_t* heap) {
     return rx.sign > 0 ? c : -c;
 }
 
-}  // namespace relp
+#ifndef RELP_NO_WCB
+}  // namespace RELP_NS
 #include "relp_wcb.cuh"
-namespace relp {
+namespace RELP_NS {
 
 // ------------------------------------------------------------------------------------------
 // Cooperative tier: the same three operations on operands of any length, by a group of lanes
@@ -726,21 +745,17 @@ struct WarpGroup {      // all 32 lanes of a warp, converged by the caller (one-
 };
 #endif
 
-// The limb heap's first words are never a value (offset 0 is not a handle): words 2..3 hold the address of an
-// Arena that describes where scratch may be taken (set by the owner of the heap, null = nowhere).  Comparisons
-// have no arena argument; this is how big_cmp finds room for its two cross products when they are long.
-RELP_HD const ScratchExt* heap_scratch(const uint32_t* heap) {
-    const uint64_t a = (uint64_t)heap[2] | ((uint64_t)heap[3] << 32);
-    return (const ScratchExt*)(uintptr_t)a;
-}
+
 
 template <class G> struct WOp {          // scratch of one cooperative operation
-    WScratch<G> sc; int slot; bool locked;
+    WScratch<G> sc; int slot; bool locked; const ScratchExt* ext;
 };
 template <class G> RELP_HD void wop_begin(const G& g, WOp<G>& op, uint32_t* heap, const Arena& ar) {
     op.sc.slab = nullptr; op.sc.cap = 0; op.sc.used = 0; op.sc.heap = heap; op.slot = -1; op.locked = false;
     op.sc.fallback = ar;
-    const ScratchExt* x = ar.ext;
+    op.sc.fallback.flag = nullptr;
+    const ScratchExt* x = heap_scratch(heap);
+    op.ext = x;
     if (x && x->scr_top) { op.sc.fallback.top = x->scr_top; op.sc.fallback.limit = x->scr_limit; }
 #if defined(__CUDA_ARCH__) && !defined(RELP_EMUL)
     if (g.size() == 32 && x && x->wslab && x->wslots > 0) {      // a whole warp: its slab (%warpid is unique within a CTA only, hence the lock)
@@ -758,7 +773,7 @@ template <class G> RELP_HD void wop_begin(const G& g, WOp<G>& op, uint32_t* heap
 }
 template <class G> RELP_HD void wop_end(const G& g, WOp<G>& op, const Arena& ar) {
 #if defined(__CUDA_ARCH__) && !defined(RELP_EMUL)
-    if (op.locked) { g.sync(); if (g.rank() == 0) atomicExch(&ar.ext->wlock[op.slot], 0); }
+    if (op.locked) { g.sync(); if (g.rank() == 0) atomicExch(&op.ext->wlock[op.slot], 0); }
 #endif
     (void)g; (void)op; (void)ar;
 }
@@ -776,7 +791,10 @@ RELP_W Val w_store(const G& g, int sign, const uint32_t* num, int nn, const uint
     off = g.shfl(off, 0);
     if (off < 0) return val_zero();
     uint32_t* p = heap + off;
-    if (g.rank() == 0) p[0] = (uint32_t)nn | ((uint32_t)nd << 14) | (sign < 0 ? 0x80000000u : 0u);
+    if (g.rank() == 0) {
+        p[0] = (uint32_t)nn | ((uint32_t)nd << 14) | (sign < 0 ? 0x80000000u : 0u);
+        if ((nn > RELP_LONG_TRIGGER || nd > RELP_LONG_TRIGGER) && ar.flag) *ar.flag = 1;
+    }
     for (int i = g.rank(); i < nn; i += g.size()) p[1 + i] = num[i];
     for (int i = g.rank(); i < nd; i += g.size()) p[1 + nn + i] = den[i];
     g.sync();
@@ -825,7 +843,7 @@ RELP_W const uint32_t* w_quot(const G& g, WScratch<G>& sc, const uint32_t* p, in
 // describe limbs that do too.  A violation is reported (ERR_PEER bit + a location code in ext->dbg), not followed.
 RELP_HD bool w_check(const Val& v, const uint32_t* heap, const Arena& ar, int where) {
     if (v.d != 0) return v.d > 0;
-    const ScratchExt* x = ar.ext;
+    const ScratchExt* x = heap_scratch(heap);
     if (!x || !x->heap_words) return true;
     bool ok = v.n >= 16 && (unsigned long long)v.n < x->heap_words;
     if (ok) { const uint32_t h = heap[v.n]; const unsigned nn = h & 0x3fff, nd = (h >> 14) & 0x3fff; ok = nn >= 1 && nd >= 1 && (unsigned long long)v.n + 1 + nn + nd <= x->heap_words; }
@@ -973,6 +991,21 @@ static void relp_wcb_trace(const char* op, const Val& x, const Val& a, const Val
     fprintf(f, "\n"); fflush(f);
 }
 #endif
+#else   // RELP_NO_WCB: the copy of this header without the arbitrary-length tier (relp_fastloop.cu)
+RELP_HD int ref_max_limbs(const Val& v, const uint32_t* heap) {
+    if (v.d != 0) return 2;
+    const uint32_t h = heap[v.n];
+    const int nn = (int)(h & 0x3fff), nd = (int)((h >> 14) & 0x3fff);
+    return nn > nd ? nn : nd;
+}
+RELP_HD int imax3(int a, int b, int c) { return a > b ? (a > c ? a : c) : (b > c ? b : c); }
+// operands beyond RELP_OPL limbs cannot occur while DState::long_seen is clear (see RELP_LONG_TRIGGER); if one does,
+// the per-thread routines report ERR_LIMB_CAPACITY and the host repeats the solve with the full tier
+RELP_HD Val big_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) { return big_fma_thread(x, a, b, s, heap, ar); }
+RELP_HD Val big_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar) { return big_div_thread(x, y, heap, ar); }
+RELP_HD int big_cmp(const Val& x, const Val& y, const uint32_t* heap) { return big_cmp_thread(x, y, heap); }
+#endif
+#ifndef RELP_NO_WCB
 // From arbitrary (divergent) code a long operation is done by the calling lane alone, with the cooperative routines
 // on a group of one: correct everywhere, no fixed size.  The stages that have many long operations call wcb_fma /
 // wcb_div themselves with a converged WarpGroup (stage_update_big, relp_kernels.cuh).
@@ -980,7 +1013,8 @@ static void relp_wcb_trace(const char* op, const Val& x, const Val& a, const Val
 // operation: right in a plain kernel, but inside the stages, where lanes arrive from loops with different trip counts,
 // it hung or faulted on the device, while the same code on one lane per operation passed every test.)
 RELP_HDN Val big_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* heap, const Arena& ar) {
-    const int thr = (ar.ext && ar.ext->coop_from < RELP_OPL) ? ar.ext->coop_from : RELP_OPL;
+    const ScratchExt* ext = heap_scratch(heap);
+    const int thr = (ext && ext->coop_from < RELP_OPL) ? ext->coop_from : RELP_OPL;
     if (imax3(ref_max_limbs(x, heap), ref_max_limbs(a, heap), ref_max_limbs(b, heap)) <= thr) return big_fma_thread(x, a, b, s, heap, ar);
 #ifdef RELP_WCB_TRACE
     relp_wcb_trace("fma", x, a, b, s, heap);
@@ -989,7 +1023,8 @@ RELP_HDN Val big_fma(const Val& x, const Val& a, const Val& b, int s, uint32_t* 
 }
 
 RELP_HDN Val big_div(const Val& x, const Val& y, uint32_t* heap, const Arena& ar) {
-    const int thr = (ar.ext && ar.ext->coop_from < RELP_OPL) ? ar.ext->coop_from : RELP_OPL;
+    const ScratchExt* ext = heap_scratch(heap);
+    const int thr = (ext && ext->coop_from < RELP_OPL) ? ext->coop_from : RELP_OPL;
     const int mx = ref_max_limbs(x, heap), my = ref_max_limbs(y, heap);
     if ((mx > my ? mx : my) <= thr) return big_div_thread(x, y, heap, ar);
 #ifdef RELP_WCB_TRACE
@@ -1003,10 +1038,10 @@ RELP_HDN int big_cmp(const Val& x, const Val& y, const uint32_t* heap) {
     if ((mx > my ? mx : my) <= RELP_OPL) return big_cmp_thread(x, y, heap);
     const ScratchExt* ext = heap_scratch(heap);
     Arena scr;                            // no result is stored: only the scratch provider matters
-    scr.ext = ext;
     if (ext) { scr.top = ext->scr_top; scr.limit = ext->scr_limit; scr.err = ext->err; }
     return wcb_cmp(SoloGroup(), x, y, heap, scr);
 }
+#endif   // RELP_NO_WCB
 
 // ------------------------------------------------------------------------------------------
 // Tier-dispatching front ends
@@ -1052,4 +1087,4 @@ RELP_HD Val val_ratio(const Val& b, const Val& d, uint32_t* heap, const Arena& a
     return val_div(b, d, heap, ar);
 }
 
-}  // namespace relp
+}  // namespace RELP_NS

@@ -105,6 +105,7 @@ struct relp_ctx {
     DBuf<int2> worklist; DBuf<Cand> cand, cand2, gather; DBuf<LogEntry> log; DBuf<unsigned long long> trace;
     int n_slices = 0, a_int = 1, coop_blocks = 0, last_ratio_blocks = 1;
     bool use_persistent = true, use_narrow = true, smem_opt_in = false, upd_opt_in = false;
+    bool long_mode = false;          // a value longer than RELP_LONG_TRIGGER limbs has been stored in this solve: loop copy with the full tier
     long long wide_handoffs = 0;
     // peer transport (multi-GPU persistent loop): this rank's exchange buffer and the peers' as mapped here
     DBuf<unsigned char> xbuf; void* peer_base[RELP_MAX_WORLD] = {}; bool peer_mode = false; int peer_max_m = 0;
@@ -495,7 +496,7 @@ static void wire_dev(relp_ctx* c) {
     D.rn = c->rn.p; D.rd = c->rd.p; D.row_ptr = c->row_ptr_d.p; D.csr_ent = c->csr_ent.p;
     D.colbits = c->colbits.p; D.rowbits = c->rowbits.p; D.colsum = c->colsum.p; D.claim = c->claim.p; D.row_art = c->row_art.p;
     wire_peers(c);
-    D.ext = c->scr_ext.p;
+    D.ext = c->scr_ext.p; D.allow_long = 1;      // every kernel of this file contains the full tier
     D.gather = c->gather.p; D.log = c->log.p; D.log_cap = (long long)c->log.n; D.trace = c->trace.p; D.zbits = c->zbits.p;
 }
 
@@ -536,7 +537,7 @@ static int alloc_carry(relp_ctx* c, int m, int ncols_max) {
 static int publish_scratch_arena(relp_ctx* c, const DState* s) {
     ScratchExt a;
     a.wslab = c->wslab.p; a.wslab_words = c->wslab_words; a.wlock = c->wlock.p; a.wslots = c->wslab.p ? c->sm_count * 64 : 0;
-    a.scr_top = &c->st.p->tr_top; a.scr_limit = s->tr_limit; a.err = &c->st.p->err; a.coop_from = c->coop_from;
+    a.scr_top = &c->st.p->tr_top; a.scr_limit = s->tr_limit; a.err = &c->st.p->err; a.flag = &c->st.p->long_seen; a.coop_from = c->coop_from;
     a.heap_words = c->heap_words;
     CUDA_TRY(cudaMemcpyAsync(c->scr_ext.p, &a, sizeof(a), cudaMemcpyHostToDevice, c->stream));
     const uint64_t addr = (uint64_t)(uintptr_t)c->scr_ext.p;
@@ -571,6 +572,7 @@ __global__ void k_set_pivot(DState* st, int j, int r, int set_zero_rc) {
     if (set_zero_rc) st->rc = make_small(0, 1);
 }
 __global__ void k_reset_transient(DState* st) { st->tr_top = st->tr_base; }
+__global__ void k_clear_want_long(DState* st) { st->want_long = 0; st->go = !(st->status != ST_RUNNING || st->err != 0 || st->iter >= st->iter_limit); }
 
 // shared-memory words for the -pi bitmap (0: too large, kernels test the global bitmap)
 static int zbits_smem_words(relp_ctx* c) {
@@ -684,6 +686,15 @@ static int check_cuda(relp_ctx* c) {
     return 0;
 }
 
+#ifndef RELP_EMUL
+extern "C" {     // relp_fastloop.cu: the persistent loop compiled without the arbitrary-length tier
+int relp_fast_loop_occupancy(int* per_sm);
+int relp_fast_loop_smem_optin(int bytes);
+int relp_fast_loop_launch(int peers, const void* dev, size_t dev_bytes, int rule, int max_iters, int smem_words, int use_narrow,
+                          int blocks, size_t smem_bytes, void* stream);
+}
+#endif
+
 static int launch_persistent(relp_ctx* c, int rule, int max_iters) {
 #ifdef RELP_EMUL
     k_simplex_loop<false>(c->D, rule, max_iters, 0, 0);
@@ -694,6 +705,8 @@ static int launch_persistent(relp_ctx* c, int rule, int max_iters) {
         int per_sm = 0;
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_simplex_loop<false>, RELP_PTHREADS, 0));
         if (per_sm < 1) { set_error("persistent kernel does not fit on an SM"); return RELP_ERR_CUDA; }
+        CUDA_TRY((cudaError_t)relp_fast_loop_occupancy(&per_sm));
+        if (per_sm < 1) { set_error("persistent kernel (fast copy) does not fit on an SM"); return RELP_ERR_CUDA; }
         c->coop_blocks = c->sm_count;        // one CTA per SM
     }
     int sw = zbits_smem_words(c);
@@ -702,9 +715,16 @@ static int launch_persistent(relp_ctx* c, int rule, int max_iters) {
         CUDA_TRY(cudaFuncSetAttribute(k_simplex_loop<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         CUDA_TRY(cudaFuncSetAttribute(k_simplex_loop<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         CUDA_TRY(cudaFuncSetAttribute(k_price, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        CUDA_TRY((cudaError_t)relp_fast_loop_smem_optin(160 * 1024));
         c->smem_opt_in = true;
     }
     int narrow = c->use_narrow ? 1 : 0;
+    if (!c->long_mode) {         // no long values yet: the copy of the loop without the arbitrary-length tier (relp_fastloop.cu)
+        CUDA_TRY((cudaError_t)relp_fast_loop_launch(c->peer_mode ? 1 : 0, &c->D, sizeof(Dev), rule, max_iters, sw, narrow, c->coop_blocks, smem, c->stream));
+        c->launches++;
+        return 0;
+    }
+    c->D.allow_long = 1;
     void* args[] = { (void*)&c->D, (void*)&rule, (void*)&max_iters, (void*)&sw, (void*)&narrow };
     CUDA_TRY(cudaLaunchCooperativeKernel(c->peer_mode ? (void*)k_simplex_loop<true> : (void*)k_simplex_loop<false>, dim3(c->coop_blocks), dim3(RELP_PTHREADS), args, smem, c->stream));
     c->launches++;
@@ -731,6 +751,11 @@ static int run_loop(relp_ctx* c, int rule, int64_t max_iters, int tag) {
         if (sync_state(c)) return RELP_ERR_CUDA;
         const DState* s = c->h_st;
         if (s->err) { result = err_status(s); break; }
+        if (s->want_long) {      // a long value has been stored: from here on the copy of the loop with the arbitrary-length tier
+            c->long_mode = true;
+            LAUNCH(c, k_clear_want_long, 1, 1, c->st.p);
+            continue;
+        }
         if (s->want_wide) {      // the persistent loop left with a large dense update pending (see k_simplex_loop)
             if (launch_update(c)) return RELP_ERR_CUDA;
             LAUNCH(c, k_update_big, c->sm_count * 2, 128, c->D);
@@ -797,7 +822,7 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     LAUNCH(c, k_build_zbits, grid_for(c, (m + 31) / 32), RELP_THREADS, c->D);
     if (check_cuda(c)) return RELP_ERR_CUDA;
     CUDA_TRY(cudaStreamSynchronize(c->stream));
-    c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0;
+    c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0; c->long_mode = false;
     return RELP_OK;
 }
 
@@ -1004,7 +1029,7 @@ static int from_basis(relp_ctx* c, const int32_t* basis_in) {
     LAUNCH(c, k_gather_planes, c->sm_count * 8, RELP_THREADS, c->xn.p, c->xd.p, c->ld, nxn.p, nxd.p, c->ld, m, m + 1, where.p, kc.p);
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     c->xn.swap(nxn); c->xd.swap(nxd);
-    c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0; c->phase = 1;   // handover_common expects phase-1 numbering + nr_art (0)
+    c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0; c->long_mode = false; c->phase = 1;   // handover_common expects phase-1 numbering + nr_art (0)
     std::vector<int> basis(basis_in, basis_in + m);
     rc = handover_common(c, basis, true);
     if (rc) return rc;

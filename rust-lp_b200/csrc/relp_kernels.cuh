@@ -35,7 +35,7 @@
 #endif
 #include "relp_arith.cuh"
 
-namespace relp {
+namespace RELP_NS {
 
 enum { RULE_FIRST = 0, RULE_FIRST_MEMORY = 1, RULE_DANTZIG = 2 };
 enum { ARG_DANTZIG = 0, ARG_FIRST = 1, ARG_RATIO = 2 };
@@ -75,6 +75,9 @@ struct DState {
     unsigned long long escalated, sum_T, sum_S, sum_TS, pool_peak, compactions;
     unsigned long long stage_ns[NSTAGE];                  // persistent kernel: time per stage (globaltimer)
     Val rc;
+    // (appended, so that the words the loop reads every iteration stay where they were)
+    int long_seen;                 // a value longer than RELP_LONG_TRIGGER limbs has been stored (Arena::flag points here)
+    int want_long;                 // persistent loop (copy without the arbitrary-length tier) left because long_seen is set
 };
 
 struct Cand { Val v; int key; int idx; };
@@ -137,6 +140,7 @@ struct Dev {
     int xworld, xrank; unsigned long long xepoch;
     uint32_t* xbits;                          // bitmap p_k != 0 of the current pivot row (replicated copy)
     const ScratchExt* ext;                    // scratch of the cooperative multi-limb operations (slabs + locks), in device memory
+    int allow_long;                           // this launch's code contains the arbitrary-length tier (else the loop leaves when long_seen)
     XPeer xp[RELP_MAX_WORLD];                 // xp[xrank] is this rank's own buffer
 };
 
@@ -179,12 +183,11 @@ __device__ __forceinline__ Inv load_inv(const DState* st) {
     I.wsc = (I.wpc + 31) >> 5;                        // words per column of colsum
     return I;
 }
-// (a.ext: where the cooperative multi-limb operations take their temporaries -- relp_wcb.cuh)
 __device__ __forceinline__ Arena transient(const Dev& D) {
-    Arena a; a.top = &D.st->tr_top; a.limit = D.st->tr_limit; a.err = &D.st->err; a.ext = D.ext; return a;
+    Arena a; a.top = &D.st->tr_top; a.limit = D.st->tr_limit; a.err = &D.st->err; a.flag = &D.st->long_seen; return a;
 }
 __device__ __forceinline__ Arena persistent(const Dev& D) {
-    Arena a; a.top = &D.st->pool_top; a.limit = D.st->pool_limit; a.err = &D.st->err; a.ext = D.ext; return a;
+    Arena a; a.top = &D.st->pool_top; a.limit = D.st->pool_limit; a.err = &D.st->err; a.flag = &D.st->long_seen; return a;
 }
 __device__ __forceinline__ bool halted(const DState* st) {
     return st->status != ST_RUNNING || st->err != 0 || st->iter >= st->iter_limit;
@@ -1013,11 +1016,15 @@ __device__ void stage_update(const Dev& D, const Grid& g, const Inv& I, int j, i
 // per-thread routines; the long ones are then done one after the other by the WHOLE warp (relp_wcb.cuh: limbs across
 // lanes, carries by ballot, Lehmer steps on the leading limbs) -- the warp is converged here by construction, and a
 // long operation's latency is what the stage waits for when few elements are queued.
+#ifdef RELP_NO_WCB
 __device__ void stage_update_big(const Dev& D, const Grid& g, const Inv& I) {
+#else
+__device__ __noinline__ void stage_update_big(const Dev& D, const Grid& g, const Inv& I) {
+#endif
     DState* st = D.st;
     const int n = st->wl_count < st->wl_cap ? st->wl_count : st->wl_cap; const size_t ld = I.ld;
     Arena ar = persistent(D);
-#ifdef RELP_EMUL
+#if defined(RELP_EMUL) || defined(RELP_NO_WCB)
     for (int w = g.tid; w < n; w += g.nth) {
         int2 it = D.worklist[w];
         size_t e = (size_t)it.y * ld + it.x;
@@ -1071,6 +1078,7 @@ __device__ void end_of_iteration(const Dev& D) {
     st->escalated += (unsigned long long)st->wl_count;
     st->iter++;
     st->go = !halted(st);
+    if (st->long_seen && !D.allow_long && st->go) { st->go = 0; st->want_long = 1; }     // hand over to the copy with the full tier
     st->tr_top = st->tr_base;
     st->T = 0; st->S = 0; st->wl_count = 0; st->W = 0;
     unsigned long long used = st->pool_top - st->pool_base;
@@ -1982,4 +1990,4 @@ __global__ void k_export(Dev D, const int64_t* sn, const int64_t* sd, long long 
     }
 }
 
-}  // namespace relp
+}  // namespace RELP_NS

@@ -19,7 +19,7 @@
 // checks them against Python integers before they ever run in a kernel.
 #pragma once
 
-namespace relp {
+namespace RELP_NS {
 
 struct SoloGroup {
     RELP_HD int rank() const { return 0; }
@@ -420,4 +420,4 @@ RELP_W int w_divexact(const G& g, uint32_t* q, uint32_t* a, int na, const uint32
     return w_trim(g, q, nq);
 }
 
-}  // namespace relp
+}  // namespace RELP_NS

@@ -116,16 +116,17 @@ class ShardedCarry:
         self.c.close()
 
 
-def bench(args, metric, unit, config, ClockSampler, workload):
-    """`bench.py --gpus N` under torchrun: ONE LP solved cooperatively by N GPUs (strong scaling)."""
+def bench(args, B):
+    """`bench.py --gpus N` under torchrun: ONE LP solved cooperatively by N GPUs (strong scaling).  `B` is the bench
+    module (workload, config, roofline, parity and clock helpers shared with the N = 1 line)."""
     import torch
     import torch.distributed as dist
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    pa = workload(args)
-    sc = ShardedCarry(pa, device=local, heap_words=1 << 24)
+    pa, gold = B.workload(args)
+    sc = ShardedCarry(pa, device=local, heap_words=args.heap_words)
     stream = torch.cuda.ExternalStream(sc.c.stream())
 
     def solve():
@@ -135,17 +136,17 @@ def bench(args, metric, unit, config, ClockSampler, workload):
 
     for _ in range(max(args.warmup, 3)):
         s = solve()
-    clocks = ClockSampler(local)
+    clocks = B.ClockSampler(local)
     if rank == 0:
         clocks.start()
     dist.barrier(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = s.kernel_launches
     e0.record(stream)
-    pivots = 0
+    pivots, loop_ms = 0, 0.0
     for _ in range(args.steps):
         s = solve()
-        pivots += s.pivots
+        pivots += s.pivots; loop_ms += s.loop_ms
     e1.record(stream)
     torch.cuda.synchronize(); dist.barrier()
     ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
@@ -153,6 +154,10 @@ def bench(args, metric, unit, config, ClockSampler, workload):
     ms = float(ms.item())
     launches = s.kernel_launches - launches0
     obj = sc.get_objective_function_value()
+    # parity on EVERY rank (the pivot log and the objective are replicated): the timed solve against the committed golden
+    par = B.parity_block(sc.log(), obj, gold)
+    flags = [None] * world
+    dist.all_gather_object(flags, (par["log_sha256"], par["objective"], par["identical_to_golden"]))
     # e2e: host buffers in, answer out, wall clock, max over ranks
     dist.barrier(); torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -168,15 +173,26 @@ def bench(args, metric, unit, config, ClockSampler, workload):
     if rank == 0:
         clk = clocks.stop()
         h2d = 8 * (pa.n + 1) + 20 * pa.nnz + 16 * pa.n + 16 * pa.m
-        line = {"metric": metric, "value": pivots / (ms * 1e-3), "unit": unit, "n_gpus": world, "steps": args.steps,
+        par["ranks_identical"] = bool(all(f[:2] == flags[0][:2] for f in flags))
+        par["ranks_identical_to_golden"] = [f[2] for f in flags]
+        roof = B.roofline_block(pa, s, loop_ms / args.steps, world)
+        roof["what"] += "  (rank 0's kernel; every rank runs the same loop on its row shard)"
+        cpu = {"kind": "port", "cores": 1, "unit": unit_of(B), "value": None,
+               "sample": "not re-timed at N > 1 (the CPU arm is timed at N = 1 and by --impl reference); cached full solve below"}
+        if gold and gold.get("oracle_seconds_to_optimal"):
+            cpu["time_to_optimal_s"] = gold["oracle_seconds_to_optimal"]
+            cpu["value"] = gold["pivots"] / gold["oracle_seconds_to_optimal"]
+            cpu["sample"] = "whole solve, " + gold["source"] + " -- run once in the build container, not on this box"
+        line = {"metric": B.METRIC, "value": pivots / (ms * 1e-3), "unit": B.UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None,
-                "dtype": "exact rational, int64/int64 tier (multi-limb escalation armed)", "data": "synthetic",
-                "config": config(args, world), "time_to_optimal_ms": ms / args.steps,
+                "dtype": "exact rational, int64/int64 tier (multi-limb escalation armed)", "data": "synthetic" if args.workload == "synth5a" else "netlib/miplib fixture",
+                "config": B.config(args, world, pa), "time_to_optimal_ms": ms / args.steps,
                 "pivots_per_solve": int(s.pivots), "objective": str(obj),
-                "e2e": {"value": pivots / e2e_s, "unit": unit, "h2d_bytes_per_step": h2d * world,
+                "e2e": {"value": pivots / e2e_s, "unit": B.UNIT, "h2d_bytes_per_step": h2d * world,
                         "d2h_bytes_per_step": 16 + 20 * pa.m, "ms_per_step": 1e3 * e2e_s / args.steps},
                 "gpu_launches": int(launches), "clocks": clk,
+                "roofline": roof, "parity": par, "cpu_baseline": cpu,
                 "transport": sc.transport,
                 "note": "ONE LP solved cooperatively (strong scaling): Carry rows sharded, cost row / reduced-cost row / basis "
                         "replicated; the persistent loop kernel runs on every rank and exchanges ratio-test candidates and the "
@@ -187,3 +203,7 @@ def bench(args, metric, unit, config, ClockSampler, workload):
         print(json.dumps(line), flush=True)
     sc.close()
     dist.destroy_process_group()
+
+
+def unit_of(B):
+    return B.UNIT

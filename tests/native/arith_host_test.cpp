@@ -10,11 +10,11 @@ using namespace relp;
 static std::vector<uint32_t> g_heap(1 << 24);
 static unsigned long long g_top = 16;
 static ScratchExt g_ext;
-static int g_err = 0;
+static int g_errs[2] = {0, 0};      // err word + the "long values exist" word behind it (Arena::err[1])
+#define g_err g_errs[0]
 static Arena arena() {
-    Arena a; a.top = &g_top; a.limit = g_heap.size(); a.err = &g_err;
-    g_ext.scr_top = &g_top; g_ext.scr_limit = g_heap.size(); g_ext.err = &g_err;     // scratch behind the values, same region
-    a.ext = &g_ext;
+    Arena a; a.top = &g_top; a.limit = g_heap.size(); a.err = g_errs; a.flag = g_errs + 1;
+    g_ext.scr_top = &g_top; g_ext.scr_limit = g_heap.size(); g_ext.err = g_errs;     // scratch behind the values, same region
     const uint64_t addr = (uint64_t)(uintptr_t)&g_ext;
     g_heap[2] = (uint32_t)addr; g_heap[3] = (uint32_t)(addr >> 32);                  // how big_cmp finds it (heap_scratch)
     return a;
