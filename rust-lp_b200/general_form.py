@@ -8,17 +8,32 @@ bounds to 0) -> make_b_non_negative (:558-590) -> make_minimization_problem (:59
 `MatrixData::new` (matrix_provider/matrix_data.rs:149-196; virtual slack columns and bound rows laid
 out as in :37-52, initial basis :432-452).
 
-NOT restated: the presolve rules (general_form/presolve/, 3.9 kLoC).  Presolve changes which rows and
-columns reach the simplex and therefore the pivot sequence, but not the optimum: objective values and
-feasibility are identical, which is what the golden tests check (tests/test_mps_golden.py).
+The presolve rules (general_form/presolve/) are restated in presolve.py and applied by `standardize(presolve=True)`
+exactly where the reference applies them (mod.rs:307-314: presolve, then transform_variables, make_b_non_negative,
+make_minimization_problem).  `presolve=False` keeps the un-presolved standard form that the round-1 fixtures
+(tests/golden/mps/, mps_prefix/) were generated with: same optimum, different rows / columns / pivot sequence.
 """
 from fractions import Fraction as Fr
 
+from . import presolve as _presolve
 from .synth import ProviderArrays
 
 
 class Infeasible(Exception):
     pass
+
+
+class Unbounded(Exception):
+    """`Err(LinearProgramType::Unbounded)`: a column that appears in no constraint can improve the objective for ever."""
+
+
+class SolvedByPresolve(Exception):
+    """`Err(LinearProgramType::FiniteOptimum(solution))` of `GeneralForm::presolve` (mod.rs:334-336): every variable was
+    eliminated with a value.  .objective / .solution are those of the ORIGINAL problem."""
+
+    def __init__(self, objective, solution):
+        super().__init__("linear program solved by presolve")
+        self.objective, self.solution = objective, solution
 
 
 class GeneralForm:
@@ -29,6 +44,7 @@ class GeneralForm:
         self.cols = [list(c[1]) for c in mps.columns]
         self.cost = [mps.cost.get(j, Fr(0)) for j in range(self.n_orig)]
         self.orig_cost = list(self.cost)
+        self.all_cost = list(self.cost)
         self.objective_constant = Fr(mps.objective_constant)
         self.fixed_cost = Fr(0)              # accumulated by the lower-bound shifts, minimisation form aside
         self.lower, self.upper = self._bounds(mps)
@@ -37,6 +53,10 @@ class GeneralForm:
         self.shift = [Fr(0)] * self.n_orig
         self.flipped = [False] * self.n_orig
         self.neg_part = {}           # original free variable -> index of its negative duplicate
+        # presolve bookkeeping (general_form/mod.rs `original_variables`, `from_active_to_original`)
+        self.all_names = list(self.names)
+        self.active_to_orig = list(range(self.n_orig))
+        self.removed = {}            # original index -> ("S", value) | ("F", constant, [(original index, coefficient)])
 
     # convert.rs:140-260
     @staticmethod
@@ -115,7 +135,59 @@ class GeneralForm:
         return types, b
 
     # ---- general_form/mod.rs:479-600 -----------------------------------------------------------
-    def standardize(self):
+    def presolve(self):
+        """`GeneralForm::presolve` (mod.rs:316-366): compute the changes (presolve.py), apply them to what remains
+        (:405-435), drop the removed rows and columns (:437-470), resolve removed variables whose dependencies are all
+        known (:728-790).  Raises Infeasible / Unbounded / SolvedByPresolve where the reference returns Err."""
+        try:
+            ch = _presolve.compute_presolve_changes(self)
+        except _presolve.PresolveInfeasible:
+            raise Infeasible("presolve: the problem is infeasible")
+        except _presolve.PresolveUnbounded:
+            raise Unbounded("presolve: the problem is unbounded")
+        for i, v in ch["b"].items():
+            self.b[i] = v
+        for i, t in ch["constraints"].items():
+            self.types[i] = t
+        self.fixed_cost += ch["fixed_cost"]
+        for (j, direction), v in ch["bounds"].items():
+            if direction == _presolve.LOWER:
+                self.lower[j] = v
+            else:
+                self.upper[j] = v
+        for j, sol in ch["removed_variables"]:
+            self.removed[self.active_to_orig[j]] = sol
+        gone_v = {j for j, _ in ch["removed_variables"]}
+        gone_c = set(ch["constraints_marked_removed"])
+        new_row, k = {}, 0
+        for i in range(len(self.b)):
+            if i not in gone_c:
+                new_row[i] = k
+                k += 1
+        keep = [j for j in range(len(self.cols)) if j not in gone_v]
+        self.cols = [[(new_row[i], v) for (i, v) in self.cols[j] if i in new_row] for j in keep]
+        for name in ("cost", "orig_cost", "lower", "upper", "names", "active_to_orig", "shift", "flipped"):
+            setattr(self, name, [getattr(self, name)[j] for j in keep])
+        self.n_orig = len(keep)
+        self.types = [t for i, t in enumerate(self.types) if i not in gone_c]
+        self.b = [v for i, v in enumerate(self.b) if i not in gone_c]
+        # compute_solution_where_possible (:728-790): a function of others whose others are all solved is solved
+        progress = True
+        while progress:
+            progress = False
+            for j, sol in list(self.removed.items()):
+                if sol[0] == "F" and all(self.removed.get(k, ("?",))[0] == "S" for k, _ in sol[2]):
+                    self.removed[j] = ("S", sol[1] - sum(c * self.removed[k][1] for k, c in sol[2]))
+                    progress = True
+        if not keep and all(s[0] == "S" for s in self.removed.values()):
+            values = [self.removed[j][1] for j in range(len(self.all_names))]
+            objective = sum(c * v for c, v in zip(self.all_cost, values)) + self.objective_constant
+            raise SolvedByPresolve(objective, dict(zip(self.all_names, values)))
+        return self
+
+    def standardize(self, presolve=True):
+        if presolve:
+            self.presolve()
         m = len(self.b)
         # split free variables (:522-556)
         n0 = len(self.cols)
@@ -211,6 +283,12 @@ class GeneralForm:
             "n_normal": len(self.cols),
             "objective_constant": str(self.objective_constant),
             "maximize": bool(self.maximize),
+            # presolve (general_form/mod.rs original_variables): what was eliminated and how to get it back
+            "all_names": list(self.all_names),
+            "all_cost": [str(c) for c in self.all_cost],
+            "active_to_orig": list(self.active_to_orig),
+            "removed": {str(j): ([s[0], str(s[1])] if s[0] == "S" else [s[0], str(s[1]), [[k, str(c)] for k, c in s[2]]])
+                        for j, s in self.removed.items()},
         }
 
     def reconstruct(self, bfs):
@@ -237,8 +315,22 @@ def reconstruct(state, bfs):
         if k is not None:                         # free variable: x = y_plus - y_minus
             val -= x.get(k, Fr(0))
         sol.append(val)
-    obj = sum(Fr(c) * v for c, v in zip(state["cost"], sol)) + Fr(state["objective_constant"])
-    return obj, dict(zip(state["names"], sol))
+    if not state.get("removed"):
+        obj = sum(Fr(c) * v for c, v in zip(state["cost"], sol)) + Fr(state["objective_constant"])
+        return obj, dict(zip(state["names"], sol))
+    # variables eliminated by presolve (compute_solution_value_with_bfs, mod.rs:884-925): fixed values, and functions
+    # `constant - sum coefficient * other` of other ORIGINAL variables (possibly eliminated themselves)
+    values = {o: v for o, v in zip(state["active_to_orig"], sol)}
+    removed = state["removed"]
+
+    def value_of(j):
+        if j not in values:
+            r = removed[str(j)]
+            values[j] = Fr(r[1]) if r[0] == "S" else Fr(r[1]) - sum(Fr(c) * value_of(k) for k, c in r[2])
+        return values[j]
+    full = [value_of(j) for j in range(len(state["all_names"]))]
+    obj = sum(Fr(c) * v for c, v in zip(state["all_cost"], full)) + Fr(state["objective_constant"])
+    return obj, dict(zip(state["all_names"], full))
 
 
 def minimisation_objective(state, objective):
@@ -262,8 +354,9 @@ def provider_arrays(m, cols, cost, rhs, piv, n_normal):
                           [p[0] for p in piv], [p[1] for p in piv], n_normal)
 
 
-def from_mps(mps):
-    """MPS -> (GeneralForm standardised, ProviderArrays)."""
+def from_mps(mps, presolve=False):
+    """MPS -> (GeneralForm standardised, ProviderArrays).  presolve=True is the reference's pipeline (mod.rs:259-314);
+    the default keeps the un-presolved form of the committed round-1 fixtures."""
     gf = GeneralForm(mps)
-    gf.standardize()
+    gf.standardize(presolve=presolve)
     return gf, gf.derive_matrix_data()

@@ -15,7 +15,7 @@ for e in EXPECTED:
     name = e["name"]
     if only and name not in only: continue
     pa = load(name)
-    c = capi.Carry(pa, heap_words=1 << 28)
+    c = capi.Carry(pa, heap_words=int(os.environ.get("RELP_HEAP_WORDS", str(1 << 28))))
     t0 = time.time()
     st, first = 0, True
     try:
