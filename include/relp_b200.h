@@ -149,6 +149,12 @@ int relp_load_matrix(relp_ctx*, int32_t m, int32_t n,
                      const int64_t* cost_num, const int64_t* cost_den,
                      const int64_t* rhs_num, const int64_t* rhs_den);
 
+/* Replace cost_value(j) of the loaded provider (same canonical-form rules).  Costs are read by phase two only, so this
+ * is refused (RELP_ERR_ARGUMENT) while a phase-two tableau is live.  For trait-level callers: RELP's
+ * InverseMaintener::create_for_partially_artificial never sees the provider, the real costs arrive with
+ * from_artificial / from_artificial_remove_rows (inverse_maintenance/mod.rs:120-151). */
+int relp_set_costs(relp_ctx*, int32_t n, const int64_t* cost_num, const int64_t* cost_den);
+
 /* ---- InverseMaintener constructors (inverse_maintenance/mod.rs:29-267) --------------------- */
 /* Partially::new + Carry::create_for_partially_artificial
  * (tableau/kind/artificial/partially.rs:125-205, carry/mod.rs:381-426).  (piv_rows[k], piv_cols[k])

@@ -22,7 +22,7 @@ FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
 # every symbol include/relp_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_debug_k1_dense", "relp_debug_k1_verify", "relp_debug_rat_op", "relp_comm_unique_id",
-    "relp_attach_comm", "relp_attach_comm_callbacks", "relp_peer_export", "relp_peer_attach", "relp_load_matrix", "relp_carry_create_partially_artificial",
+    "relp_attach_comm", "relp_attach_comm_callbacks", "relp_peer_export", "relp_peer_attach", "relp_load_matrix", "relp_set_costs", "relp_carry_create_partially_artificial",
     "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_carry_from_basis", "relp_price",
     "relp_generate_column", "relp_ratio_test", "relp_change_basis", "relp_generate_element",
     "relp_iterate", "relp_solve_relaxation", "relp_solve_continue", "relp_solve_to_handover",
@@ -87,6 +87,7 @@ def load_library(path=None):
     L.relp_peer_export.argtypes = [vp, i32, vp]
     L.relp_peer_attach.argtypes = [vp, vp]
     L.relp_load_matrix.argtypes = [vp, i32, i32] + [vp] * 8
+    L.relp_set_costs.argtypes = [vp, i32, vp, vp]
     L.relp_carry_create_partially_artificial.argtypes = [vp, i32, vp, vp]
     L.relp_carry_from_artificial.argtypes = [vp]
     L.relp_carry_from_artificial_remove_rows.argtypes = [vp, i32, vp]
@@ -268,6 +269,11 @@ class Carry:
         self._chk(self.L.relp_load_matrix(self.h, pa.m, pa.n, _p(pa.col_ptr), _p(pa.row_idx), _p(pa.val_num),
                                           _p(pa.val_den), _p(pa.cost_num), _p(pa.cost_den), _p(pa.rhs_num),
                                           _p(pa.rhs_den)))
+
+    def set_costs(self, cost_num, cost_den):
+        """replace cost_value(j) of the loaded provider (phase two reads them; refused while a phase-two tableau is live)"""
+        cn = np.ascontiguousarray(cost_num, dtype=np.int64); cd = np.ascontiguousarray(cost_den, dtype=np.int64)
+        self._chk(self.L.relp_set_costs(self.h, len(cn), _p(cn), _p(cd)))
 
     # ---- InverseMaintener constructors ---------------------------------------------------------
     def create_for_partially_artificial(self, piv_rows=None, piv_cols=None):

@@ -1143,6 +1143,26 @@ static int solve_continue(relp_ctx* c, int64_t max_pivots) {
 
 extern "C" {
 
+// Replace the cost vector of the loaded provider.  Costs are only read by phase two (pricing, hand-over, from_basis),
+// so this is legal whenever no phase-two tableau is live: the trait-level caller (integration/rust/relp-b200) learns the
+// real costs only in InverseMaintener::from_artificial (inverse_maintenance/mod.rs:120-133).
+int relp_set_costs(relp_ctx* c, int32_t n, const int64_t* cost_num, const int64_t* cost_den) {
+    if (!c || !c->loaded || !cost_num || !cost_den || n != c->n) { set_error("relp_set_costs: no matrix loaded, NULL argument or n differs from the loaded matrix"); return RELP_ERR_ARGUMENT; }
+    if (c->carry_ready && c->phase == 2) { set_error("relp_set_costs: a phase-two tableau is live (its cost row was computed from the old costs)"); return RELP_ERR_ARGUMENT; }
+    for (int j = 0; j < n; j++) {
+        const int64_t d = cost_den[j], v = cost_num[j];
+        if (v == INT64_MIN || d < 1 || (d != 1 && gcd64(abs64(v), (uint64_t)d) != 1)) {
+            set_error("relp_set_costs: cost " + std::to_string(j) + " is not canonical (den >= 1, lowest terms, num != INT64_MIN)"); return RELP_ERR_ARGUMENT;
+        }
+    }
+    CUDA_TRY(cudaSetDevice(c->device));
+    c->cn.assign(cost_num, cost_num + n); c->cd.assign(cost_den, cost_den + n);
+    CUDA_TRY(cudaMemcpyAsync(c->cn_d.p, c->cn.data(), (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(c->cd_d.p, c->cd.data(), (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return RELP_OK;
+}
+
 int relp_carry_create_partially_artificial(relp_ctx* c, int32_t n_piv, const int32_t* piv_rows, const int32_t* piv_cols) {
     if (!c) return RELP_ERR_ARGUMENT;
     c->stage = 0;

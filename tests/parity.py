@@ -224,3 +224,43 @@ def check_load_validation(pa, lib_path):
     c.load_matrix(pa)                        # and the context is still usable
     assert c.solve_relaxation() in (capi.OPTIMAL, capi.UNBOUNDED, capi.INFEASIBLE)
     c.close()
+
+
+def check_set_costs(pa, lib_path):
+    """relp_set_costs (the trait-level caller's route: tableau first, real costs at the phase hand-over): loading with
+    zero costs, running phase one, handing the real costs over and then from_artificial + phase two gives the pivot
+    log and answer of a load with the costs; non-canonical costs, a wrong length and a live phase-two tableau are refused."""
+    import copy
+
+    def run(loaded, late_costs):
+        c = capi.Carry(loaded, heap_words=1 << 22, lib_path=lib_path)
+        c.create_for_partially_artificial()
+        assert c.iterate(capi.FIRST_PROFITABLE_WITH_MEMORY) == capi.OPTIMAL          # phase one
+        assert c.get_objective_function_value() == 0 and all(j >= c.dims()[2] for j in c.basis_indices()), "pick a feasible full-rank LP"
+        if late_costs:
+            for bad_n, bad_d, what in ((pa.cost_num * 2, np.full_like(pa.cost_den, 2), "canonical"),
+                                       (pa.cost_num[:-1], pa.cost_den[:-1], "differs")):
+                try:
+                    c.set_costs(bad_n, bad_d)
+                except capi.RelpError as e:
+                    assert e.status == capi.ERR_ARGUMENT and what in str(e), str(e)
+                else:
+                    raise AssertionError("accepted " + what)
+            c.set_costs(pa.cost_num, pa.cost_den)
+        c.from_artificial()
+        st = c.iterate(capi.STEEPEST_DESCENT)
+        out = (st, c.log(), c.get_objective_function_value(), c.current_bfs(), c.carry())
+        if late_costs:
+            try:
+                c.set_costs(pa.cost_num, pa.cost_den)
+            except capi.RelpError as e:
+                assert "phase-two" in str(e)
+            else:
+                raise AssertionError("set_costs accepted with a phase-two tableau live")
+        c.close()
+        return out
+
+    blank = copy.deepcopy(pa)
+    blank.cost_num = np.zeros_like(pa.cost_num); blank.cost_den = np.ones_like(pa.cost_den)
+    assert np.any(pa.cost_num != 0)
+    assert run(blank, True) == run(pa, False)

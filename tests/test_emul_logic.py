@@ -164,3 +164,7 @@ def test_context_reuse_after_row_removal(lib):
 
 def test_load_matrix_validation(lib):
     parity.check_load_validation(pa_from_lp(feasible_lp(3, 3, 1, 3, 2, 10, frac=True)), lib)
+
+
+def test_set_costs_after_phase_one(lib):
+    parity.check_set_costs(pa_from_lp(feasible_lp(7, 6, 2, 4, 2, 12, frac=True)), lib)
