@@ -432,6 +432,40 @@ RELP_HD int mag_mod(uint32_t* u, int nu, const uint32_t* v, int nv, uint32_t* vn
     return mag_trim(u, nv);
 }
 
+// Inner loop of Lehmer's gcd (Knuth 4.5.2 L, steps L2-L4) on the 62-bit leading parts uh >= vh: cofactors with
+// |.| < 2^30 such that (A u + B v, C u + D v) continues the Euclidean sequence of the full numbers.  Knuth's test is
+// floor((uh + A) / (vh + C)) == floor((uh + B) / (vh + D)).  A 64-bit division is ~120 instructions on the GPU and the
+// loop used to do two per quotient, which made it 90 % of a 50-limb gcd: quotients 0..3 (two thirds of all, by the
+// Gauss-Kuzmin law) are now found by comparison, larger ones by ONE division, and the second quotient is never formed
+// -- q d2 <= n2 < (q + 1) d2 is checked by a multiplication.
+RELP_HD void lehmer_cofactors(int64_t uh, int64_t vh, int64_t& A, int64_t& B, int64_t& C, int64_t& D) {
+    for (;;) {
+        if (vh + C <= 0 || vh + D <= 0 || uh + A < 0 || uh + B < 0) break;
+        const uint64_t n1 = (uint64_t)(uh + A), d1 = (uint64_t)(vh + C), n2 = (uint64_t)(uh + B), d2 = (uint64_t)(vh + D);   // all < 2^62 + 2^30
+        uint64_t q, lo;
+        if (n1 < d1) { q = 0; lo = 0; }
+        else if (n1 - d1 < d1) { q = 1; lo = d2; }
+        else if (n1 - 2 * d1 < d1) { q = 2; lo = 2 * d2; }
+        else if (n1 - 3 * d1 < d1) { q = 3; lo = 3 * d2; }
+        else {
+            q = n1 / d1;
+            if (q > 0x7fffffffULL) break;
+#if defined(__CUDA_ARCH__)
+            if (__umul64hi(q, d2)) break;
+#else
+            if ((unsigned __int128)q * d2 >> 64) break;
+#endif
+            lo = q * d2;
+        }
+        if (lo > n2 || n2 - lo >= d2) break;                                   // the two quotients differ
+        const int64_t sq = (int64_t)q;
+        const int64_t nA = A - sq * C, nB = B - sq * D;
+        if (nA > 0x3fffffffLL || nA < -0x3fffffffLL || nB > 0x3fffffffLL || nB < -0x3fffffffLL) break;
+        const int64_t nh = uh - sq * vh;
+        A = C; C = nA; B = D; D = nB; uh = vh; vh = nh;
+    }
+}
+
 // GCD of two nonzero magnitudes (Lehmer, Knuth 4.5.2 L, with 62-bit leading parts and 31-bit cofactors);
 // destroys both buffers; *res points at the buffer (u or v) holding the result; returns its limb
 // count.  Each buffer needs one spare limb beyond max(nu, nv).  `tmp`: min(nu, nv) limbs.
@@ -448,19 +482,8 @@ RELP_HD int mag_gcd(uint32_t* u, int nu, uint32_t* v, int nv, uint32_t** res, ui
         if (nv == nu) { vw = ((uint64_t)v[top] << 32) | v[top - 1]; v3 = top >= 2 ? v[top - 2] : 0; }
         else if (nv == nu - 1) { vw = v[top - 1]; v3 = top >= 2 ? v[top - 2] : 0; }
         if (sft) { uw = (uw << sft) | (u3 >> (32 - sft)); vw = (vw << sft) | (v3 >> (32 - sft)); }
-        int64_t uh = (int64_t)(uw >> 2), vh = (int64_t)(vw >> 2);
         int64_t A = 1, B = 0, C = 0, D = 1;
-        if (nv >= nu - 1) {
-            for (;;) {
-                if (vh + C <= 0 || vh + D <= 0 || uh + A < 0 || uh + B < 0) break;
-                int64_t q = (uh + A) / (vh + C);
-                if (q > 0x7fffffffLL || q != (uh + B) / (vh + D)) break;
-                int64_t nA = A - q * C, nB = B - q * D;
-                if (nA > 0x3fffffffLL || nA < -0x3fffffffLL || nB > 0x3fffffffLL || nB < -0x3fffffffLL) break;
-                int64_t nh = uh - q * vh;
-                A = C; C = nA; B = D; D = nB; uh = vh; vh = nh;
-            }
-        }
+        if (nv >= nu - 1) lehmer_cofactors((int64_t)(uw >> 2), (int64_t)(vw >> 2), A, B, C, D);
         if (B == 0) {                                // no usable cofactors: one full remainder step
             int nr = mag_mod(u, nu, v, nv, tmp);
             uint32_t* t = u; u = v; v = t; nu = nv; nv = nr;

@@ -1584,8 +1584,11 @@ int relp_debug_rat_op(relp_ctx* c, int op, int32_t count, const int64_t* operand
     c->h_st->tr_top = base + limb_words;
     if (push_state(c)) return RELP_ERR_CUDA;
     CUDA_TRY(cudaMemcpyAsync(in.p, operands, (size_t)6 * count * 8, cudaMemcpyHostToDevice, c->stream));
+    cudaEventRecord(c->ev0, c->stream);
     LAUNCH(c, k_debug_rat_op, clampi(cdiv(count, 256), 1, c->sm_count * 4), 256, c->D, op, (int)count, in.p, base, s, on.p, od.p);
+    cudaEventRecord(c->ev1, c->stream);
     if (check_cuda(c)) return RELP_ERR_CUDA;
+    { float ms = 0; cudaEventSynchronize(c->ev1); cudaEventElapsedTime(&ms, c->ev0, c->ev1); c->loop_ms = ms; }     // relp_stats.loop_ms = this kernel (scripts/arith_time.py)
     return read_block_impl(c, on.p, od.p, 1, 1, count, 1, num, den, limbs, limb_cap, limb_used, true);
 }
 

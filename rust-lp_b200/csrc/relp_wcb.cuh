@@ -347,19 +347,8 @@ RELP_W int w_gcd(const G& g, uint32_t* u, int nu, uint32_t* v, int nv, uint32_t*
         if (nv == nu) { vw = ((uint64_t)v[top] << 32) | v[top - 1]; v3 = top >= 2 ? v[top - 2] : 0u; }
         else if (nv == nu - 1) { vw = v[top - 1]; v3 = top >= 2 ? v[top - 2] : 0u; }
         if (sft) { uw = (uw << sft) | (u3 >> (32 - sft)); vw = (vw << sft) | (v3 >> (32 - sft)); }
-        int64_t uh = (int64_t)(uw >> 2), vh = (int64_t)(vw >> 2);
         int64_t A = 1, B = 0, C = 0, D = 1;
-        if (nv >= nu - 1) {
-            for (;;) {
-                if (vh + C <= 0 || vh + D <= 0 || uh + A < 0 || uh + B < 0) break;
-                const int64_t q = (uh + A) / (vh + C);
-                if (q > 0x7fffffffLL || q != (uh + B) / (vh + D)) break;
-                const int64_t nA = A - q * C, nB = B - q * D;
-                if (nA > 0x3fffffffLL || nA < -0x3fffffffLL || nB > 0x3fffffffLL || nB < -0x3fffffffLL) break;
-                const int64_t nh = uh - q * vh;
-                A = C; C = nA; B = D; D = nB; uh = vh; vh = nh;
-            }
-        }
+        if (nv >= nu - 1) lehmer_cofactors((int64_t)(uw >> 2), (int64_t)(vw >> 2), A, B, C, D);     // every lane alike
         if (B == 0) {                                // no usable cofactors: one full remainder step
             const int nr = w_mod(g, u, nu, v, nv, t1, t2);
             uint32_t* t = u; u = v; v = t; nu = nv; nv = nr;
