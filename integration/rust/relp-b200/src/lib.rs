@@ -2,7 +2,8 @@
 //! updated by librelp_b200.so, plus `GpuRule<R>`: the three `PivotRule`s evaluated on the device.
 //!
 //! Every method of `InverseMaintener` (relp: src/algorithm/two_phase/tableau/inverse_maintenance/mod.rs:29-267),
-//! `ColumnComputationInfo` (:270-275) and `PivotRule` (strategy/pivot_rule.rs:21-33) is implemented; nothing is elided.
+//! `ColumnComputationInfo` (:270-275), `BasisInverse` (carry/mod.rs:68-157, on `GpuBasisInverse`) and `PivotRule`
+//! (strategy/pivot_rule.rs:21-33) is implemented; nothing is elided.
 //! NEVER COMPILED: there is no Rust toolchain where this was written.  The C ABI underneath is what is tested
 //! (tests/test_gpu_parity.py drives the same entry points in the same order through ctypes).
 //!
@@ -344,6 +345,84 @@ impl GpuCarry {
         }
         check(unsafe { sys::relp_set_costs(self.ctx, n as i32, cn.as_ptr(), cd.as_ptr()) });
     }
+}
+
+/// `BasisInverse` (carry/mod.rs:68-157) on its own, for callers that keep the reference's host-side `Carry<F, BI>` and
+/// only want `B^-1` on the device: a `GpuCarry` whose right-hand side is zero.  The nine methods map one to one.
+/// (Inside this crate `GpuCarry` replaces `Carry` AND its `BasisInverse`: `b`, `-pi` and the objective live on the
+/// device next to `B^-1`, which is what makes the fused loop possible.)
+pub struct GpuBasisInverse { inner: GpuCarry, nr_columns: usize }
+
+impl GpuBasisInverse {
+    /// load `columns` as the whole provider (costs 0, right-hand side 0)
+    fn with_columns<C: Column + OrderedColumn>(m: usize, columns: &[C]) -> GpuCarry where RationalBig: ops::Column<C::F> {
+        let mut im = GpuCarry::fresh(m);
+        let mut csc = Csc::new();
+        for column in columns { csc.push(column); }
+        let n = columns.len();
+        let (cn, cd, rn, rd) = (vec![0i64; n], vec![1i64; n], vec![0i64; m], vec![1i64; m]);
+        check(unsafe { sys::relp_load_matrix(im.ctx, m as i32, n as i32, csc.col_ptr.as_ptr(), csc.row_idx.as_ptr(), csc.vn.as_ptr(),
+            csc.vd.as_ptr(), cn.as_ptr(), cd.as_ptr(), rn.as_ptr(), rd.as_ptr()) });
+        im.matrix_loaded = true;
+        im
+    }
+}
+
+impl fmt::Display for GpuBasisInverse {
+    fn fmt(&self, f: &mut fmt::Formatter<'_>) -> fmt::Result {
+        for i in 0..self.inner.m { writeln!(f, "{:?}", self.basis_inverse_row(i))?; }
+        Ok(())
+    }
+}
+
+impl relp::algorithm::two_phase::tableau::inverse_maintenance::carry::BasisInverse for GpuBasisInverse {
+    type F = RationalBig;
+    type ColumnComputationInfo = GpuColumn;
+
+    /// basis_inverse_rows.rs:86-91: the identity = the fully artificial tableau of a provider with one (unit) column per row
+    fn identity(m: usize) -> Self {
+        let units: Vec<SparseVector<RationalBig, RationalBig>> = (0..m).map(|i| SparseVector::new(vec![(i, RationalBig::from(1))], m)).collect();
+        let mut inner = Self::with_columns(m, &units);
+        check(unsafe { sys::relp_carry_create_partially_artificial(inner.ctx, 0, std::ptr::null(), std::ptr::null()) });
+        inner.invalidate();
+        GpuBasisInverse { inner, nr_columns: m }
+    }
+
+    /// basis_inverse_rows.rs:93-128 (Gauss-Jordan over the given columns) = relp_carry_from_basis over columns 0..m
+    fn invert<C: Column + OrderedColumn>(columns: Vec<C>) -> Self where Self::F: ops::Column<C::F> {
+        let m = columns.len();
+        let inner = Self::with_columns(m, &columns);
+        let basis: Vec<i32> = (0..m as i32).collect();
+        check(unsafe { sys::relp_carry_from_basis(inner.ctx, basis.as_ptr()) });
+        GpuBasisInverse { inner, nr_columns: m }
+    }
+
+    /// basis_inverse_rows.rs:130-142 = K1 without the `b` and cost-row parts (both are zero here)
+    fn change_basis(&mut self, pivot_row_index: usize, column: GpuColumn) {
+        let _ = column;
+        let mut leaving = -1i32;
+        check(unsafe { sys::relp_change_basis(self.inner.ctx, pivot_row_index as i32, &mut leaving) });
+    }
+
+    fn generate_column<C: Column + OrderedColumn>(&self, original_column: C) -> GpuColumn where Self::F: ops::Column<C::F> {
+        self.inner.generate_column(original_column)
+    }
+
+    fn generate_element<C: Column + OrderedColumn>(&self, i: usize, original_column: C) -> Option<RationalBig> where Self::F: ops::Column<C::F> {
+        self.inner.generate_element(i, original_column)
+    }
+
+    /// basis_inverse_rows.rs:175-177: the explicit inverse never degrades
+    fn should_refactor(&self) -> bool { false }
+
+    /// basis_inverse_rows.rs:179-181: row `row` of `B^-1` = Carry block row `row`, columns 1..=m (column 0 is `b`)
+    fn basis_inverse_row(&self, row: usize) -> SparseVector<RationalBig, RationalBig> {
+        let m = self.inner.m;
+        let r = Rats::read(m, |n, d, l, cap, used| unsafe { sys::relp_read_block(self.inner.ctx, row as i32, 1, 1, m as i32, n, d, l, cap, used) });
+        SparseVector::new((0..m).filter(|&k| r.num[k] != 0 || r.den[k] == 0).map(|k| (k, r.get(k))).collect(), m)
+    }
+
+    fn m(&self) -> usize { let _ = self.nr_columns; self.inner.m }
 }
 
 thread_local! { static CURRENT_COLUMN: Cell<Option<usize>> = Cell::new(None); }

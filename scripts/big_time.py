@@ -46,7 +46,10 @@ for e in EXPECTED:
             obj_std = sum(v * Fr(int(pa.cost_num[j]), int(pa.cost_den[j])) for j, v in bfs)
             obj, _sol = general_form.reconstruct(state, bfs)
             s = c.stats()
-            res = dict(name=name, status="optimal", pivots=int(s.pivots), total_s=time.time() - t0, loop_ms=s.loop_ms,
+            sys.path.insert(0, os.path.join("tests", "golden"))
+            from make_prefix_golden import state_digests
+            dig = state_digests([(ord(x[0]), x[1], x[2]) for x in c.log()], c.basis_indices(), c.b(), c.get_objective_function_value())
+            res = dict(name=name, status="optimal", digests={k: dig[k] for k in ("log_sha256", "basis_sha256", "b_sha256")}, pivots=int(s.pivots), total_s=time.time() - t0, loop_ms=s.loop_ms,
                        escalated=int(s.escalated), max_limbs=int(s.max_limbs), objective=float(obj), objective_exact=str(obj),
                        reference=e["full_solve_reference"], abs_diff=abs(float(obj) - e["full_solve_reference"]),
                        exact_Ax_eq_b=bool(feasible), objective_equals_cx=bool(obj_std == c.get_objective_function_value()),

@@ -42,7 +42,7 @@ def test_rust_trait_shim_is_complete():
                    "from_artificial", "from_artificial_remove_rows", "change_basis", "cost_difference", "generate_column",
                    "generate_element", "after_basis_change", "current_bfs", "basis_column_index_for_row", "b",
                    "get_objective_function_value", "get_constraint_value", "column", "into_column", "new",
-                   "select_primal_pivot_column"):
+                   "select_primal_pivot_column", "identity", "invert", "should_refactor", "basis_inverse_row", "m"):
         assert re.search(r"\bfn %s\b[^;]*?\{" % method, src, re.S), method
     assert "unimplemented!" not in src and "todo!" not in src and "..." not in src.replace("0..", "")
 
