@@ -157,7 +157,7 @@ struct Dev {
 #endif
 #define RELP_MAXWARPS 32
 #ifndef RELP_COOP_FEW
-#define RELP_COOP_FEW 12              // stage_update_big with few queued elements: operations longer than this many limbs are shared by the warp
+#define RELP_COOP_FEW 32              // stage_update_big with few queued elements (<= 2 per warp): operations longer than this many limbs are shared by the warp (below ~1000 bits one thread is as fast, profiles/arith_time_r02.jsonl)
 #endif
 
 struct Grid { int tid, nth, bid, nb; };
@@ -1036,9 +1036,13 @@ __device__ __noinline__ void stage_update_big(const Dev& D, const Grid& g, const
 #else
     if (n == 0) return;
     const int lane = threadIdx.x & 31, nwarps = g.nth >> 5;
-    // few elements for the machine: a long operation done by one thread is what everybody waits for -- share them earlier
-    int thr = D.ext->coop_from < RELP_OPL ? D.ext->coop_from : RELP_OPL;
-    if (n <= 2 * nwarps && thr > RELP_COOP_FEW) thr = RELP_COOP_FEW;
+    // Measured (profiles/arith_time_r02.jsonl): a warp finishes ONE long operation sooner than a thread (1.2x at 1 600 bits,
+    // 4-6x beyond 2 000), but a GPU full of single threads finishes 12-60x more operations per second.  So whole warps
+    // share operations only when there are few elements for the machine (everybody would wait for one long chain);
+    // otherwise every element keeps its own thread, whatever its length (big_fma: per-thread buffers up to RELP_OPL limbs,
+    // the template routines on a group of one beyond).
+    int thr = 0x7fffffff;
+    if (n <= 2 * nwarps) thr = D.ext->coop_from < RELP_COOP_FEW ? D.ext->coop_from : RELP_COOP_FEW;
     const WarpGroup wg;
     for (int base = (g.tid >> 5) * 32; base < n; base += nwarps * 32) {       // the same trip count for the 32 lanes of a warp
         const int w = base + lane;
@@ -1052,7 +1056,7 @@ __device__ __noinline__ void stage_update_big(const Dev& D, const Grid& g, const
             e = (size_t)it.y * ld + it.x;
             x = ld_val(D.xn, D.xd, e); dv = ld_val(D.dn, D.dd, it.x); pv = ld_val(D.pn, D.pd, it.y);
             lng = imax3(ref_max_limbs(x, D.heap), ref_max_limbs(dv, D.heap), ref_max_limbs(pv, D.heap)) > thr;
-            if (!lng) out = big_fma_thread(x, dv, pv, -1, D.heap, ar);
+            if (!lng) out = big_fma(x, dv, pv, -1, D.heap, ar);
         }
         unsigned need = __ballot_sync(0xffffffffu, have && lng);
         while (need) {

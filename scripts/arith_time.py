@@ -1,6 +1,7 @@
 """Latency and throughput of the device rational arithmetic by operand size (GPU).
 
     python scripts/arith_time.py [out.jsonl]
+    python scripts/arith_time.py --one BITS OP COUNT      (one configuration, three launches: for ncu)
 
 Drives relp_debug_rat_op (the kernels' own front ends val_fma / val_div, one operation per thread, and op 3: one
 operation per warp through the cooperative tier) with random canonical operands of a given bit length and reports
@@ -25,14 +26,19 @@ def rnd(bits, rng):
 
 
 def main():
-    out = open(sys.argv[1], "w") if len(sys.argv) > 1 else None
+    one = None
+    if len(sys.argv) > 1 and sys.argv[1] == "--one":
+        one = (int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]))
+    out = open(sys.argv[1], "w") if len(sys.argv) > 1 and not one else None
     c = capi.Carry(synthetic_lp(30, 60, 5), heap_words=1 << 28)
     c.create_for_partially_artificial()
     rng = random.Random(7)
-    for bits in (40, 96, 128, 256, 512, 1024, 1600, 3200, 6400):
+    for bits in (40, 96, 128, 256, 512, 1024, 1600, 3200, 6400) if not one else (one[0],):
         for op, name in ((0, "fma, one thread"), (3, "fma, one warp"), (1, "div, one thread")):
-            for count in (1, 32768 if bits <= 1600 else 2048):
-                if op == 3 and count > 1:
+            if one and op != one[1]:
+                continue
+            for count in (1, 32768 if bits <= 1600 else 2048) if not one else (one[2],):
+                if op == 3 and count > 1 and not one:
                     count //= 8
                 base = [(rnd(bits, rng), rnd(bits, rng), rnd(bits, rng)) for _ in range(min(count, 64))]
                 xs = [base[k % len(base)][0] for k in range(count)]

@@ -17,4 +17,12 @@ timeout 300 python scripts/k1_dense.py 20000 8 | tail -1 > $O/k1_dense.json; cat
 S="python scripts/one_solve.py netlib_25FV47 4000 0"
 timeout 600 $S > $O/big_plain.log 2>&1 &&
 timeout 1500 ncu --set full --clock-control none --import-source on -k regex:k_update_big --launch-skip 3500 --launch-count 1 -o $O/update_big $S > $O/ncu_big.log 2>&1
+# the device arithmetic alone: instruction counts of ONE 128-bit and ONE 1600-bit x - a b (one thread), and of one done by a warp
+for cfg in "128 0 1" "1600 0 1" "1600 3 1" "1600 0 32768"; do
+  set -- $cfg
+  timeout 120 python scripts/arith_time.py --one $1 $2 $3 > $O/arith_one_$1_$2_$3.log 2>&1 &&
+  timeout 300 ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum,smsp__thread_inst_executed.sum,sm__inst_executed_pipe_alu.sum,sm__inst_executed_pipe_fma.sum,sm__inst_executed_pipe_xu.sum,sm__inst_executed_pipe_lsu.sum,sm__inst_executed_pipe_uniform.sum \
+      --clock-control none -k regex:k_debug_rat_op --csv --log-file $O/arith_ncu_$1_$2_$3.csv python scripts/arith_time.py --one $1 $2 $3 > /dev/null 2>&1
+done
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:k_debug_rat_op -c 1 -o $O/arith_128 python scripts/arith_time.py --one 128 0 1 > /dev/null 2>&1
 ls -la $O
