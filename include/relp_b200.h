@@ -155,6 +155,15 @@ int relp_load_matrix(relp_ctx*, int32_t m, int32_t n,
  * from_artificial / from_artificial_remove_rows (inverse_maintenance/mod.rs:120-151). */
 int relp_set_costs(relp_ctx*, int32_t n, const int64_t* cost_num, const int64_t* cost_den);
 
+/* Replace right_hand_side() by a rat array (the encoding every reader of this header returns): den > 0 is num/den as in
+ * relp_load_matrix; den == 0 means `num` is the word offset in `limbs` of a record [header | numerator limbs |
+ * denominator limbs] (little-endian 32-bit limbs, header = nn | nd << 14, sign bit clear: rhs >= 0).  A value that fits
+ * int64/int64 must be passed as such.  Records are trusted to be in lowest terms.  Why: the reference's right-hand side
+ * is a RationalBig (MatrixProvider::Rhs, matrix_provider/mod.rs:37-136 with tests/netlib/mod.rs:44-45) and its presolve
+ * substitutes solved variables into it -- netlib BORE3D reaches the simplex with 285-bit right-hand sides.  Call after
+ * relp_load_matrix (which takes placeholders, e.g. 0/1, for such rows) and before a Carry constructor. */
+int relp_set_rhs(relp_ctx*, int32_t m, const int64_t* rhs_num, const int64_t* rhs_den, const uint32_t* limbs, size_t limb_words);
+
 /* ---- InverseMaintener constructors (inverse_maintenance/mod.rs:29-267) --------------------- */
 /* Partially::new + Carry::create_for_partially_artificial
  * (tableau/kind/artificial/partially.rs:125-205, carry/mod.rs:381-426).  (piv_rows[k], piv_cols[k])

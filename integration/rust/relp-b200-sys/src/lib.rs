@@ -59,6 +59,8 @@ extern "C" {
                             rhs_num: *const i64, rhs_den: *const i64) -> c_int;
     /// replace cost_value(j) (read by phase two only; refused while a phase-two tableau is live)
     pub fn relp_set_costs(ctx: *mut relp_ctx, n: i32, cost_num: *const i64, cost_den: *const i64) -> c_int;
+    /// replace right_hand_side() by a rat array (den == 0: record in `limbs`): the reference's Rhs is a RationalBig
+    pub fn relp_set_rhs(ctx: *mut relp_ctx, m: i32, rhs_num: *const i64, rhs_den: *const i64, limbs: *const u32, limb_words: usize) -> c_int;
     /// InverseMaintener::create_for_partially_artificial (carry/mod.rs:381-426)
     pub fn relp_carry_create_partially_artificial(ctx: *mut relp_ctx, n_piv: i32, piv_rows: *const i32, piv_cols: *const i32) -> c_int;
     /// InverseMaintener::from_artificial (carry/mod.rs:484-510)

@@ -81,6 +81,8 @@ class COracle:
         self.h = L.orc_create(pa.m, pa.n, _p(pa.col_ptr), _p(pa.row_idx), _p(pa.val_num), _p(pa.val_den),
                               _p(pa.cost_num), _p(pa.cost_den), _p(pa.rhs_num), _p(pa.rhs_den),
                               len(pa.piv_rows), _p(pa.piv_rows), _p(pa.piv_cols))
+        for i, f in (getattr(pa, "rhs_exact", None) or {}).items():       # right-hand sides beyond int64/int64
+            L.orc_set_rhs(self.h, int(i), f"{f.numerator}/{f.denominator}".encode())
 
     def __del__(self):
         if getattr(self, "h", None):

@@ -22,7 +22,7 @@ FIRST_PROFITABLE, FIRST_PROFITABLE_WITH_MEMORY, STEEPEST_DESCENT = 0, 1, 2
 # every symbol include/relp_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "relp_create", "relp_destroy", "relp_last_error", "relp_abi_version", "relp_set_option", "relp_stream", "relp_debug_trace", "relp_debug_k1_dense", "relp_debug_k1_verify", "relp_debug_rat_op", "relp_comm_unique_id",
-    "relp_attach_comm", "relp_attach_comm_callbacks", "relp_peer_export", "relp_peer_attach", "relp_load_matrix", "relp_set_costs", "relp_carry_create_partially_artificial",
+    "relp_attach_comm", "relp_attach_comm_callbacks", "relp_peer_export", "relp_peer_attach", "relp_load_matrix", "relp_set_costs", "relp_set_rhs", "relp_carry_create_partially_artificial",
     "relp_carry_from_artificial", "relp_carry_from_artificial_remove_rows", "relp_carry_from_basis", "relp_price",
     "relp_generate_column", "relp_ratio_test", "relp_change_basis", "relp_generate_element",
     "relp_iterate", "relp_solve_relaxation", "relp_solve_continue", "relp_solve_to_handover",
@@ -88,6 +88,7 @@ def load_library(path=None):
     L.relp_peer_attach.argtypes = [vp, vp]
     L.relp_load_matrix.argtypes = [vp, i32, i32] + [vp] * 8
     L.relp_set_costs.argtypes = [vp, i32, vp, vp]
+    L.relp_set_rhs.argtypes = [vp, i32, vp, vp, vp, C.c_size_t]
     L.relp_carry_create_partially_artificial.argtypes = [vp, i32, vp, vp]
     L.relp_carry_from_artificial.argtypes = [vp]
     L.relp_carry_from_artificial_remove_rows.argtypes = [vp, i32, vp]
@@ -269,6 +270,26 @@ class Carry:
         self._chk(self.L.relp_load_matrix(self.h, pa.m, pa.n, _p(pa.col_ptr), _p(pa.row_idx), _p(pa.val_num),
                                           _p(pa.val_den), _p(pa.cost_num), _p(pa.cost_den), _p(pa.rhs_num),
                                           _p(pa.rhs_den)))
+        if getattr(pa, "rhs_exact", None):
+            self.set_rhs([pa.rhs_exact.get(i, Fr(int(pa.rhs_num[i]), int(pa.rhs_den[i]))) for i in range(pa.m)])
+
+    def set_rhs(self, rhs):
+        """replace the right-hand side by exact Fractions of any size (relp_set_rhs; the reference's Rhs is a RationalBig)"""
+        n = np.zeros(len(rhs), np.int64); d = np.ones(len(rhs), np.int64); limbs = []
+        for i, f in enumerate(rhs):
+            f = Fr(f)
+            if f.numerator <= 2 ** 63 - 1 and f.denominator <= 2 ** 63 - 1:
+                n[i], d[i] = f.numerator, f.denominator
+                continue
+            nl, dl, a, b = [], [], f.numerator, f.denominator
+            while a:
+                nl.append(a & 0xffffffff); a >>= 32
+            while b:
+                dl.append(b & 0xffffffff); b >>= 32
+            n[i], d[i] = len(limbs), 0
+            limbs.extend([len(nl) | len(dl) << 14] + nl + dl)
+        lin = np.array(limbs if limbs else [0], np.uint32)
+        self._chk(self.L.relp_set_rhs(self.h, len(rhs), _p(n), _p(d), _p(lin), len(limbs)))
 
     def set_costs(self, cost_num, cost_den):
         """replace cost_value(j) of the loaded provider (phase two reads them; refused while a phase-two tableau is live)"""

@@ -88,6 +88,7 @@ struct relp_ctx {
     int m = 0, n = 0;
     std::vector<long long> col_ptr; std::vector<int> row_idx;
     std::vector<int64_t> an, ad, cn, cd, rhsn, rhsd;
+    std::vector<uint32_t> rhs_limbs;     // relp_set_rhs: records of right-hand sides beyond int64/int64 (rhsd[i] == 0: rhsn[i] = word offset in here)
     // Row removal (from_artificial_remove_rows) filters the provider in place for phase two.  The provider the caller
     // loaded is kept here and put back by the next Carry constructor, so a context can be solved again without a reload.
     struct Provider { int m = 0; std::vector<long long> col_ptr; std::vector<int> row_idx; std::vector<int64_t> an, ad, rhsn, rhsd; } orig;
@@ -379,7 +380,7 @@ int relp_load_matrix(relp_ctx* c, int32_t m, int32_t n, const int64_t* col_ptr, 
     c->col_ptr.assign(col_ptr, col_ptr + n + 1);
     c->row_idx.clear(); c->an.clear(); c->ad.clear();     // fetched back from the device only if rows get removed
     c->cn.assign(cost_num, cost_num + n); c->cd.assign(cost_den, cost_den + n);
-    c->rhsn.assign(rhs_num, rhs_num + m); c->rhsd.assign(rhs_den, rhs_den + m);
+    c->rhsn.assign(rhs_num, rhs_num + m); c->rhsd.assign(rhs_den, rhs_den + m); c->rhs_limbs.clear();
     if (c->col_ptr_d.alloc(n + 1) || c->row_idx_d.alloc(nnz) || c->an_d.alloc(nnz) || c->ad_d.alloc(nnz) ||
         c->cn_d.alloc(n) || c->cd_d.alloc(n) || c->rhsn_d.alloc(m) || c->rhsd_d.alloc(m)) return RELP_ERR_CUDA;
     cudaStream_t s = c->stream;
@@ -444,6 +445,30 @@ static int restore_provider(relp_ctx* c) {
     CUDA_TRY(cudaStreamSynchronize(s));
     c->filtered = false;
     return build_sell(c, c->col_ptr.data());
+}
+
+// Right-hand sides beyond int64/int64 (relp_set_rhs): their limb records go to the head of the fresh persistent region
+// and the device copy of the right-hand side gets handles into it, so the kernels that build `b` and the phase-one
+// objective read them like any other value.  Called between init_heap_regions and push_state by every Carry constructor.
+static int stage_rhs(relp_ctx* c, DState* s) {
+    if (c->rhs_limbs.empty()) return 0;
+    bool any = false;
+    for (int i = 0; i < c->m; i++) any |= c->rhsd[i] == 0;
+    if (!any) return 0;
+    const unsigned long long base = s->pool_top;
+    if (base + c->rhs_limbs.size() + 16 > s->pool_limit) { set_error("right-hand side does not fit the limb heap: larger heap_words"); return RELP_ERR_HEAP_EXHAUSTED; }
+    std::vector<int64_t> hn(c->rhsn);
+    for (int i = 0; i < c->m; i++) if (c->rhsd[i] == 0) {
+        hn[i] = (int64_t)(base + (unsigned long long)c->rhsn[i]);
+        const uint32_t h = c->rhs_limbs[c->rhsn[i]];
+        if ((int)(h & 0x3fff) > RELP_LONG_TRIGGER || (int)((h >> 14) & 0x3fff) > RELP_LONG_TRIGGER) c->long_mode = true;
+    }
+    s->pool_top = base + c->rhs_limbs.size();
+    CUDA_TRY(cudaMemcpyAsync(c->heap.p + base, c->rhs_limbs.data(), c->rhs_limbs.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(c->rhsn_d.p, hn.data(), (size_t)c->m * 8, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(c->rhsd_d.p, c->rhsd.data(), (size_t)c->m * 8, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
 }
 
 static void shard_rows(relp_ctx* c, int m) {
@@ -804,6 +829,8 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     s->status = ST_RUNNING; s->last_selected = -1; s->iter = 0; s->iter_limit = ~0ull; s->tag = '1'; s->go = 1;
     s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap; s->k1_min = c->k1_min; s->k1_exit = c->k1_exit;
     init_heap_regions(c, s);
+    c->long_mode = false;
+    if (int rr = stage_rhs(c, s)) return rr;
     if (push_state(c)) return RELP_ERR_CUDA;
     if (publish_scratch_arena(c, s)) return RELP_ERR_CUDA;
     {   // row -> artificial column
@@ -822,7 +849,7 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     LAUNCH(c, k_build_zbits, grid_for(c, (m + 31) / 32), RELP_THREADS, c->D);
     if (check_cuda(c)) return RELP_ERR_CUDA;
     CUDA_TRY(cudaStreamSynchronize(c->stream));
-    c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0; c->long_mode = false;
+    c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0;
     return RELP_OK;
 }
 
@@ -994,6 +1021,8 @@ static int from_basis(relp_ctx* c, const int32_t* basis_in) {
     s->status = ST_RUNNING; s->last_selected = -1; s->iter = 0; s->iter_limit = ~0ull; s->tag = 'b'; s->go = 1;
     s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap; s->k1_min = c->k1_min; s->k1_exit = c->k1_exit;
     init_heap_regions(c, s);
+    c->long_mode = false;
+    if (int rr = stage_rhs(c, s)) return rr;
     if (push_state(c)) return RELP_ERR_CUDA;
     if (publish_scratch_arena(c, s)) return RELP_ERR_CUDA;
     wire_dev(c);
@@ -1029,7 +1058,7 @@ static int from_basis(relp_ctx* c, const int32_t* basis_in) {
     LAUNCH(c, k_gather_planes, c->sm_count * 8, RELP_THREADS, c->xn.p, c->xd.p, c->ld, nxn.p, nxd.p, c->ld, m, m + 1, where.p, kc.p);
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     c->xn.swap(nxn); c->xd.swap(nxd);
-    c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0; c->long_mode = false; c->phase = 1;   // handover_common expects phase-1 numbering + nr_art (0)
+    c->carry_ready = true; c->rows_removed.clear(); c->loop_ms = 0; c->phase = 1;   // handover_common expects phase-1 numbering + nr_art (0)
     std::vector<int> basis(basis_in, basis_in + m);
     rc = handover_common(c, basis, true);
     if (rc) return rc;
@@ -1160,6 +1189,42 @@ int relp_set_costs(relp_ctx* c, int32_t n, const int64_t* cost_num, const int64_
     CUDA_TRY(cudaMemcpyAsync(c->cn_d.p, c->cn.data(), (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(cudaMemcpyAsync(c->cd_d.p, c->cd.data(), (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return RELP_OK;
+}
+
+// Replace the right-hand side by a rat array: entries with den > 0 are int64/int64 as in relp_load_matrix, entries with
+// den == 0 are records [header | numerator limbs | denominator limbs] at word offset `num` of `limbs`.  The reference's
+// right-hand side is a RationalBig (tests/netlib/mod.rs:44-45: GeneralForm<RationalBig>), and presolve substitutes
+// solved variables into it: netlib BORE3D reaches the simplex with 285-bit right-hand sides.
+int relp_set_rhs(relp_ctx* c, int32_t m, const int64_t* rhs_num, const int64_t* rhs_den, const uint32_t* limbs, size_t limb_words) {
+    if (!c || !c->loaded || !rhs_num || !rhs_den || m != c->m || (limb_words && !limbs)) { set_error("relp_set_rhs: no matrix loaded, NULL argument or m differs from the loaded matrix"); return RELP_ERR_ARGUMENT; }
+    if (c->filtered && restore_provider(c)) return RELP_ERR_CUDA;
+    for (int i = 0; i < m; i++) {
+        const int64_t d = rhs_den[i], v = rhs_num[i];
+        std::string bad;
+        if (d > 0) {
+            if (v < 0) bad = "rhs < 0";
+            else if (d != 1 && gcd64((uint64_t)v, (uint64_t)d) != 1) bad = "not in lowest terms";
+        } else if (d < 0) bad = "denominator < 0";
+        else {
+            if (v < 0 || (size_t)v >= limb_words) bad = "record offset outside limbs";
+            else {
+                const uint32_t h = limbs[v]; const size_t nn = h & 0x3fff, nd = (h >> 14) & 0x3fff;
+                if (h >> 31) bad = "rhs < 0";
+                else if (nn == 0 || nd == 0 || (size_t)v + 1 + nn + nd > limb_words) bad = "record runs past limbs";
+                else if (limbs[v + nn] == 0 || limbs[v + nn + nd] == 0) bad = "leading zero limb";
+                else if (nn <= 2 && nd <= 2 && (nn < 2 || limbs[v + 2] < 0x80000000u) && (nd < 2 || limbs[v + nn + 2] < 0x80000000u)) bad = "fits int64/int64: must be passed as such (one representation per value)";
+            }
+        }
+        if (!bad.empty()) { set_error("relp_set_rhs: row " + std::to_string(i) + ": " + bad); return RELP_ERR_ARGUMENT; }
+    }
+    CUDA_TRY(cudaSetDevice(c->device));
+    c->rhsn.assign(rhs_num, rhs_num + m); c->rhsd.assign(rhs_den, rhs_den + m);
+    c->rhs_limbs.assign(limbs, limbs + limb_words);
+    CUDA_TRY(cudaMemcpyAsync(c->rhsn_d.p, c->rhsn.data(), (size_t)m * 8, cudaMemcpyHostToDevice, c->stream));     // int64 entries; handles are staged per Carry (stage_rhs)
+    CUDA_TRY(cudaMemcpyAsync(c->rhsd_d.p, c->rhsd.data(), (size_t)m * 8, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    c->carry_ready = false;
     return RELP_OK;
 }
 

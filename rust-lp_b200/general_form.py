@@ -349,9 +349,14 @@ def provider_arrays(m, cols, cost, rhs, piv, n_normal):
     for arr in (vn, vd):
         if any(abs(x) > lim for x in arr):
             raise OverflowError("matrix value does not fit Rational64")
-    return ProviderArrays(m, len(cols), col_ptr, rows, vn, vd, [c.numerator for c in cost], [c.denominator for c in cost],
-                          [x.numerator for x in rhs], [x.denominator for x in rhs],
-                          [p[0] for p in piv], [p[1] for p in piv], n_normal)
+    # the right-hand side alone may leave int64: presolve substitutes solved variables into it (BORE3D: 285 bits); the
+    # reference's Rhs is a RationalBig.  Such rows travel separately (ProviderArrays.rhs_exact -> relp_set_rhs).
+    big = {i: x for i, x in enumerate(rhs) if abs(x.numerator) > lim or x.denominator > lim}
+    pa = ProviderArrays(m, len(cols), col_ptr, rows, vn, vd, [c.numerator for c in cost], [c.denominator for c in cost],
+                        [0 if i in big else x.numerator for i, x in enumerate(rhs)], [1 if i in big else x.denominator for i, x in enumerate(rhs)],
+                        [p[0] for p in piv], [p[1] for p in piv], n_normal)
+    pa.rhs_exact = big
+    return pa
 
 
 def from_mps(mps, presolve=False):

@@ -52,6 +52,7 @@ class ProviderArrays:
         self.piv_rows = np.ascontiguousarray(piv_rows, dtype=np.int32)
         self.piv_cols = np.ascontiguousarray(piv_cols, dtype=np.int32)
         self.n_normal = int(n_normal)
+        self.rhs_exact = {}      # row -> Fraction for right-hand sides beyond int64/int64 (rhs_num/rhs_den hold 0/1 there): relp_set_rhs
 
     @property
     def nnz(self):

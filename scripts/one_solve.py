@@ -3,8 +3,13 @@ usage: python scripts/one_solve.py netlib_SHARE1B [max_pivots (-1)] [persistent 
 import sys, time
 sys.path.insert(0, '.'); sys.path.insert(0, 'tests')
 from rust_lp_b200 import capi
-from test_mps_golden import load_fixture
-pa, _ = load_fixture(sys.argv[1])
+import os
+from test_mps_golden import load_fixture, GOLD
+if os.path.exists(os.path.join(GOLD, "mps", sys.argv[1] + ".npz")):
+    pa, _ = load_fixture(sys.argv[1])
+else:                                   # BASELINE configs[2..3]: tests/golden/mps_prefix
+    from test_mps_prefix import load
+    pa = load(sys.argv[1])
 budget = int(sys.argv[2]) if len(sys.argv) > 2 else -1
 c = capi.Carry(pa, heap_words=int(sys.argv[4]) if len(sys.argv) > 4 else 1 << 26)
 if len(sys.argv) > 3:

@@ -7,7 +7,12 @@ R = sys.argv[1] if len(sys.argv) > 1 else "r01"
 
 
 def raw(rep):
-    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    """`rep` is X.ncu-rep; round 2 exports X_raw.csv on the GPU box (scripts/round_ncu.sh) because the reports are too big to bring back"""
+    exported = rep.replace(".ncu-rep", "_raw.csv")
+    if os.path.exists(exported):
+        out = open(exported).read()
+    else:
+        out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     return dict(zip(rows[0], rows[2])), dict(zip(rows[0], rows[1]))
 
@@ -38,6 +43,8 @@ def kernel_summary(rep, extra):
          "lsu_pipe_pct_of_peak_active": num(d, "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active"),
          "registers_per_thread": num(d, "launch__registers_per_thread"),
          "warps_active_pct": num(d, "sm__warps_active.avg.pct_of_peak_sustained_active"),
+         "xu_pipe_pct_of_peak_active": num(d, "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"),
+         "threads_per_warp_instruction": num(d, "smsp__thread_inst_executed_per_inst_executed.ratio"),
          "l2_hit_rate_pct": num(d, "lts__t_sector_hit_rate.pct")}
     s.update(extra)
     return s
@@ -75,8 +82,16 @@ k1n = kernel_summary(os.path.join(G, "k1_dense.ncu-rep"), {
     "note": "one full-size rank-1 update of the Carry block: T = 19999 rows x S = 20001 columns, int64/int64 tier, integers",
     "cuda_event_timing_without_ncu": k1})
 json.dump(k1n, open(os.path.join(P, f"k1_dense_{R}.json"), "w"), indent=1)
-bench["roofline"]["traffic"] = loop["dram_bytes_per_launch"]
-json.dump(bench, open(os.path.join(P, f"bench_{R}.json"), "w"))
+if os.path.exists(os.path.join(G, "update_big_raw.csv")):
+    ub = kernel_summary(os.path.join(G, "update_big.ncu-rep"), {
+        "kernel": "k_update_big (stage_update_big: the queued multi-limb elements of one pivot)",
+        "command": "ncu --set full --clock-control none --import-source on -k regex:k_update_big --launch-skip 3500 --launch-count 1 "
+                   "python scripts/one_solve.py netlib_25FV47 4000 0",
+        "note": "one launch about 3 500 pivots into phase one of netlib 25FV47 (staged driver: one launch per stage)",
+        "measured_integer_peaks": "profiles/k1_dense_rational_r01.json (scripts/micro/int_peak.cu: IMAD 18.0, IADD3 18.3, LOP3 12.3 T thread-ops/s)"})
+    if ub["warp_instructions"] and ub["threads_per_warp_instruction"]:
+        ub["thread_instructions_per_s_under_ncu"] = ub["warp_instructions"] * ub["threads_per_warp_instruction"] / (ub["gpu_time_ms_under_ncu"] * 1e-3)
+    json.dump(ub, open(os.path.join(P, f"update_big_{R}.json"), "w"), indent=1)
 if os.path.exists(os.path.join(G, "k1_frac.ncu-rep")):      # the same update on general rationals (integer-pipe bound) + measured integer peaks
     kf = kernel_summary(os.path.join(G, "k1_frac.ncu-rep"), {
         "kernel": "k_update on general rationals",

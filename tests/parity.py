@@ -264,3 +264,34 @@ def check_set_costs(pa, lib_path):
     blank.cost_num = np.zeros_like(pa.cost_num); blank.cost_den = np.ones_like(pa.cost_den)
     assert np.any(pa.cost_num != 0)
     assert run(blank, True) == run(pa, False)
+
+
+def check_big_rhs(pa, lib_path):
+    """relp_set_rhs: right-hand sides beyond int64/int64 (the reference's Rhs is a RationalBig; presolve produces them).
+    Whole solves with every row scaled by a 130-bit factor, and with only some rows big, against the oracle; bad records
+    are refused."""
+    import copy
+    scale = Fr(10 ** 40 + 1, 3 ** 5)
+    for rows in (range(pa.m), range(0, pa.m, 2)):
+        q = copy.deepcopy(pa)
+        q.rhs_exact = {i: Fr(int(pa.rhs_num[i]), int(pa.rhs_den[i])) * scale for i in rows if pa.rhs_num[i] != 0}
+        for i in q.rhs_exact:
+            q.rhs_num[i], q.rhs_den[i] = 0, 1
+        s, o = check_full_solve(q, lib_path, heap_words=1 << 22)
+        assert s.escalated > 0 and o.max_bits() > 100
+    c = capi.Carry(pa, heap_words=1 << 20, lib_path=lib_path)
+    m = pa.m
+    n = np.zeros(m, np.int64); d = np.ones(m, np.int64)
+
+    def refused(limbs, what, n0=0, d0=0):
+        n[0], d[0] = n0, d0
+        lin = np.array(limbs, np.uint32)
+        st = c.L.relp_set_rhs(c.h, m, n.ctypes.data_as(capi.C.c_void_p), d.ctypes.data_as(capi.C.c_void_p), lin.ctypes.data_as(capi.C.c_void_p), len(limbs))
+        assert st == capi.ERR_ARGUMENT and what in c.L.relp_last_error().decode(), c.L.relp_last_error()
+    refused([3 | 1 << 14 | 0x80000000, 1, 2, 3, 1], "rhs < 0")
+    refused([3 | 1 << 14, 1, 2, 3, 1], "outside", n0=7)
+    refused([3 | 1 << 14, 1, 2, 3], "past")
+    refused([3 | 1 << 14, 1, 2, 0, 1], "leading zero")
+    refused([1 | 1 << 14, 5, 1], "fits int64")
+    refused([0], "denominator < 0", n0=1, d0=-2)
+    c.close()
