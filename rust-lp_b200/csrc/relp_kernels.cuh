@@ -1037,38 +1037,34 @@ __device__ __noinline__ void stage_update_big(const Dev& D, const Grid& g, const
     if (n == 0) return;
     const int lane = threadIdx.x & 31, nwarps = g.nth >> 5;
     // Measured (profiles/arith_time_r02.jsonl): a warp finishes ONE long operation sooner than a thread (1.2x at 1 600 bits,
-    // 4-6x beyond 2 000), but a GPU full of single threads finishes 12-60x more operations per second.  So whole warps
-    // share operations only when there are few elements for the machine (everybody would wait for one long chain);
-    // otherwise every element keeps its own thread, whatever its length (big_fma: per-thread buffers up to RELP_OPL limbs,
-    // the template routines on a group of one beyond).
-    int thr = 0x7fffffff;
-    if (n <= 2 * nwarps) thr = D.ext->coop_from < RELP_COOP_FEW ? D.ext->coop_from : RELP_COOP_FEW;
+    // 4-6x beyond 2 000), but a GPU full of single threads finishes 12-60x more operations per second.
+    if (n > 2 * nwarps) {
+        // throughput regime: every element keeps its own thread, whatever its length (big_fma: per-thread buffers up to
+        // RELP_OPL limbs, the template routines on a group of one beyond)
+        for (int w = g.tid; w < n; w += g.nth) {
+            const int2 it = D.worklist[w];
+            const size_t e = (size_t)it.y * ld + it.x;
+            const Val x = ld_val(D.xn, D.xd, e);
+            const Val out = big_fma(x, ld_val(D.dn, D.dd, it.x), ld_val(D.pn, D.pd, it.y), -1, D.heap, ar);
+            st_val(D.xn, D.xd, e, out);
+            if ((x.n != 0) != (out.n != 0)) pattern_set(D, I, it.x, it.y, out.n != 0);
+        }
+        return;
+    }
+    // latency regime (few elements for the machine: everybody would wait for the longest chain): ONE ELEMENT PER WARP, the
+    // whole warp reads the same element; a long one is computed by its 32 lanes together, a short one by lane 0
+    const int thr = D.ext->coop_from < RELP_COOP_FEW ? D.ext->coop_from : RELP_COOP_FEW;
     const WarpGroup wg;
-    for (int base = (g.tid >> 5) * 32; base < n; base += nwarps * 32) {       // the same trip count for the 32 lanes of a warp
-        const int w = base + lane;
-        const bool have = w < n;
-        int2 it = make_int2(0, 0);
-        size_t e = 0;
-        Val x = val_zero(), dv = val_zero(), pv = val_zero(), out = val_zero();
-        bool lng = false;
-        if (have) {
-            it = D.worklist[w];
-            e = (size_t)it.y * ld + it.x;
-            x = ld_val(D.xn, D.xd, e); dv = ld_val(D.dn, D.dd, it.x); pv = ld_val(D.pn, D.pd, it.y);
-            lng = imax3(ref_max_limbs(x, D.heap), ref_max_limbs(dv, D.heap), ref_max_limbs(pv, D.heap)) > thr;
-            if (!lng) out = big_fma(x, dv, pv, -1, D.heap, ar);
-        }
-        unsigned need = __ballot_sync(0xffffffffu, have && lng);
-        while (need) {
-            const int r = ctz32(need); need &= need - 1;
-            Val X, A, B;
-            X.n = __shfl_sync(0xffffffffu, x.n, r); X.d = __shfl_sync(0xffffffffu, x.d, r);
-            A.n = __shfl_sync(0xffffffffu, dv.n, r); A.d = __shfl_sync(0xffffffffu, dv.d, r);
-            B.n = __shfl_sync(0xffffffffu, pv.n, r); B.d = __shfl_sync(0xffffffffu, pv.d, r);
-            const Val o = wcb_fma(wg, X, A, B, -1, D.heap, ar);
-            if (lane == r) out = o;
-        }
-        if (have) {
+    for (int w = g.tid >> 5; w < n; w += nwarps) {
+        const int2 it = D.worklist[w];
+        const size_t e = (size_t)it.y * ld + it.x;
+        const Val x = ld_val(D.xn, D.xd, e), dv = ld_val(D.dn, D.dd, it.x), pv = ld_val(D.pn, D.pd, it.y);
+        const bool lng = imax3(ref_max_limbs(x, D.heap), ref_max_limbs(dv, D.heap), ref_max_limbs(pv, D.heap)) > thr;      // warp-uniform
+        Val out = val_zero();
+        if (lng) out = wcb_fma(wg, x, dv, pv, -1, D.heap, ar);
+        else if (lane == 0) out = big_fma(x, dv, pv, -1, D.heap, ar);
+        __syncwarp();
+        if (lane == 0) {
             st_val(D.xn, D.xd, e, out);
             if ((x.n != 0) != (out.n != 0)) pattern_set(D, I, it.x, it.y, out.n != 0);
         }
