@@ -55,6 +55,36 @@ fn to_pair(big: &RationalBig) -> (i64, i64) {
 }
 fn zero() -> RationalBig { RationalBig(BigRational::zero()) }
 
+/// A right-hand side as the rat array of `relp_set_rhs`: values that fit int64/int64 as such, the others as limb records
+/// `[nn | nd << 14, numerator limbs, denominator limbs]` (the reference's `Rhs` is a `RationalBig`; presolve makes big ones).
+fn rhs_rat_array(values: &[RationalBig]) -> (Vec<i64>, Vec<i64>, Vec<u32>) {
+    use num::ToPrimitive;
+    let (mut num, mut den, mut limbs) = (Vec::with_capacity(values.len()), Vec::with_capacity(values.len()), Vec::new());
+    for v in values {
+        match (v.0.numer().to_i64(), v.0.denom().to_i64()) {
+            (Some(n), Some(d)) => { num.push(n); den.push(d); }
+            _ => {
+                assert!(v.0.numer().sign() != num::bigint::Sign::Minus, "right-hand side must be >= 0");
+                let (n, d) = (v.0.numer().magnitude().to_u32_digits(), v.0.denom().magnitude().to_u32_digits());
+                num.push(limbs.len() as i64); den.push(0);
+                limbs.push(n.len() as u32 | (d.len() as u32) << 14);
+                limbs.extend(n); limbs.extend(d);
+            }
+        }
+    }
+    (num, den, limbs)
+}
+
+/// placeholders for `relp_load_matrix` (0/1 where the value travels as a limb record) + the `relp_set_rhs` call if needed
+fn upload_rhs(ctx: *mut sys::relp_ctx, values: &[RationalBig], load: impl FnOnce(&[i64], &[i64])) {
+    let (num, den, limbs) = rhs_rat_array(values);
+    let (pn, pd): (Vec<i64>, Vec<i64>) = num.iter().zip(&den).map(|(&n, &d)| if d == 0 { (0, 1) } else { (n, d) }).unzip();
+    load(&pn, &pd);
+    if !limbs.is_empty() {
+        check(unsafe { sys::relp_set_rhs(ctx, values.len() as i32, num.as_ptr(), den.as_ptr(), limbs.as_ptr(), limbs.len()) });
+    }
+}
+
 /// rat array entry -> `RationalBig` (values arrive canonical: `new_raw` is right)
 fn from_rat(num: i64, den: i64, limbs: &[u32]) -> RationalBig {
     RationalBig(sys::rat_to_big(num, den, limbs))
@@ -110,7 +140,7 @@ pub struct GpuCarry {
     /// column uploaded by the last `generate_column` (tableau index), so that `change_basis` pivots on it
     generated: Cell<Option<usize>>,
 }
-struct Pending { rhs: Vec<(i64, i64)>, piv_rows: Vec<i32>, piv_cols: Vec<i32> }
+struct Pending { rhs: Vec<RationalBig>, piv_rows: Vec<i32>, piv_cols: Vec<i32> }
 
 impl GpuCarry {
     fn fresh(m: usize) -> Self {
@@ -133,9 +163,9 @@ impl GpuCarry {
             csc.push(&kind.original_column(j));
             cn.push(0); cd.push(1);        // phase-one costs are the kind's (0 for provider columns); real costs arrive in from_artificial
         }
-        let (rn, rd): (Vec<i64>, Vec<i64>) = p.rhs.iter().cloned().unzip();
-        check(unsafe { sys::relp_load_matrix(self.ctx, self.m as i32, (kind.nr_columns() - nr_art) as i32, csc.col_ptr.as_ptr(),
-            csc.row_idx.as_ptr(), csc.vn.as_ptr(), csc.vd.as_ptr(), cn.as_ptr(), cd.as_ptr(), rn.as_ptr(), rd.as_ptr()) });
+        let (ctx, m, n) = (self.ctx, self.m as i32, (kind.nr_columns() - nr_art) as i32);
+        upload_rhs(ctx, &p.rhs, |rn, rd| { check(unsafe { sys::relp_load_matrix(ctx, m, n, csc.col_ptr.as_ptr(),
+            csc.row_idx.as_ptr(), csc.vn.as_ptr(), csc.vd.as_ptr(), cn.as_ptr(), cd.as_ptr(), rn.as_ptr(), rd.as_ptr()) }); });
         check(unsafe { sys::relp_carry_create_partially_artificial(self.ctx, p.piv_rows.len() as i32, p.piv_rows.as_ptr(), p.piv_cols.as_ptr()) });
         self.matrix_loaded = true;
     }
@@ -151,9 +181,10 @@ impl GpuCarry {
             cn.push(a); cd.push(b);
         }
         let rhs = provider.right_hand_side();
-        let (rn, rd): (Vec<i64>, Vec<i64>) = (0..m).map(|i| to_pair(&RationalBig::from(rhs[i].clone()))).unzip();
-        check(unsafe { sys::relp_load_matrix(self.ctx, m as i32, n as i32, csc.col_ptr.as_ptr(), csc.row_idx.as_ptr(), csc.vn.as_ptr(),
-            csc.vd.as_ptr(), cn.as_ptr(), cd.as_ptr(), rn.as_ptr(), rd.as_ptr()) });
+        let values: Vec<RationalBig> = (0..m).map(|i| RationalBig::from(rhs[i].clone())).collect();
+        let ctx = self.ctx;
+        upload_rhs(ctx, &values, |rn, rd| { check(unsafe { sys::relp_load_matrix(ctx, m as i32, n as i32, csc.col_ptr.as_ptr(), csc.row_idx.as_ptr(),
+            csc.vn.as_ptr(), csc.vd.as_ptr(), cn.as_ptr(), cd.as_ptr(), rn.as_ptr(), rd.as_ptr()) }); });
         self.m = m;
         self.matrix_loaded = true;
     }
@@ -199,7 +230,7 @@ impl InverseMaintener for GpuCarry {
     ) -> Self where Self::F: ops::Rhs<G> {
         let m = artificial.len() + basis.len();
         let mut im = Self::fresh(m);
-        let rhs = (0..m).map(|i| to_pair(&RationalBig::from(b[i].clone()))).collect();
+        let rhs = (0..m).map(|i| RationalBig::from(b[i].clone())).collect();
         im.pending = Some(Pending {
             rhs,
             piv_rows: basis.iter().map(|&(row, _)| row as i32).collect(),
