@@ -38,7 +38,7 @@ enum relp_status {
     RELP_INFEASIBLE = 3,      /* phase 1 ended with objective != 0 (phase_one.rs:146-148)           */
     RELP_ERR_CUDA = -1,
     RELP_ERR_ZERO_PIVOT = -2, /* "Pivot value can't be zero" (carry/mod.rs:291-292)                 */
-    RELP_ERR_LIMB_CAPACITY = -3,  /* a numerator/denominator exceeded RELP_OPL 32-bit limbs         */
+    RELP_ERR_LIMB_CAPACITY = -3,  /* a numerator/denominator exceeded 16 383 limbs (512 Kbit, the record header's length field), or a multi-limb value would have to cross GPUs */
     RELP_ERR_HEAP_EXHAUSTED = -4, /* limb heap full: recreate the context with a larger heap        */
     RELP_ERR_ARGUMENT = -5,
     RELP_ERR_PHASE1_UNBOUNDED = -6, /* "Artificial cost can not be unbounded" (phase_one.rs:143)     */
@@ -92,7 +92,11 @@ int relp_abi_version(void);
  * (default) lets CTA 0 of the persistent kernel do small pivots alone, 0 always uses the whole grid;
  * "k1_exit" / "k1_min" = number of Carry elements (T x S) from which the persistent loop hands a dense
  * update to the staged update kernel / from which that kernel tiles the update (set before the Carry
- * is created; tests lower them so that small problems take the large-problem paths). */
+ * is created; tests lower them so that small problems take the large-problem paths).
+ * Multi-limb tier (tests): "coop_from" = limbs from which an operation leaves the fixed-size per-thread routines for
+ * the arbitrary-length ones (default 64, the per-thread buffers' size); "long_mode" = 1 runs the copy of the loop that
+ * contains that tier from the first pivot instead of handing over when a value beyond 12 limbs is stored;
+ * "wslab_words" / "tslab_words" = scratch words per resident warp / per thread for long operations. */
 int relp_set_option(relp_ctx*, const char* name, int64_t value);
 /* the cudaStream_t all work of this context is enqueued on (for CUDA-event timing by the caller) */
 void* relp_stream(relp_ctx*);

@@ -64,6 +64,10 @@ struct ScratchExt {
     int coop_from = RELP_OPL;    // operands longer than this many limbs leave the per-thread routines for the cooperative ones
     unsigned long long heap_words = 0;   // size of the limb heap (sanity checks of handles in the cooperative entry points)
     int dbg = 0;                 // first failed sanity check (0 = none): see w_check
+    // one slab per THREAD (indexed by the global thread id, no lock) for long operations done by a single thread: without
+    // it their temporaries come from the transient region, which is only recycled at the end of an iteration -- 674 000
+    // queued elements of 70 limbs exhausted a 4 GiB region (netlib 25FV47, phase two).  Allocated when a solve turns long.
+    uint32_t* tslab = nullptr; unsigned tslab_words = 0; unsigned tslots = 0;
 };
 // The limb heap's first words are never a value (offset 0 is not a handle): words 2..3 hold the address of the
 // ScratchExt of the heap's owner (null = none).  The slow paths find it there, so that the Arena every stage carries
@@ -790,6 +794,10 @@ template <class G> RELP_HD void wop_begin(const G& g, WOp<G>& op, uint32_t* heap
         if (g.rank() == 0) got = atomicCAS(&x->wlock[slot], 0, 1) == 0;
         got = g.shfl(got, 0);
         if (got) { op.sc.slab = x->wslab + (size_t)slot * x->wslab_words; op.sc.cap = x->wslab_words; op.slot = slot; op.locked = true; }
+    }
+    if (g.size() == 1 && x && x->tslab) {                         // one thread: its own slab
+        const unsigned long long gt = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+        if (gt < x->tslots) { op.sc.slab = x->tslab + (size_t)gt * x->tslab_words; op.sc.cap = x->tslab_words; }
     }
 #endif
     (void)g;

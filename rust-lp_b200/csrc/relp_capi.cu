@@ -112,6 +112,8 @@ struct relp_ctx {
     DBuf<unsigned char> xbuf; void* peer_base[RELP_MAX_WORLD] = {}; bool peer_mode = false; int peer_max_m = 0;
     // cooperative multi-limb tier: scratch slabs (one per resident warp slot), their locks, and the Arena that big_cmp finds through the heap
     DBuf<uint32_t> wslab; DBuf<int> wlock; DBuf<ScratchExt> scr_ext; unsigned wslab_words = 2048; int coop_from = RELP_OPL;
+    bool force_long = false;   // option "long_mode": run the full copy of the loop (and its scratch) from the first pivot (tests)
+    DBuf<uint32_t> tslab; unsigned tslab_words = 8192;     // per-thread scratch of long one-thread operations (ScratchExt::tslab), allocated when a solve turns long
     unsigned long long epoch = 0;
     int k1_bench_frac = 0;          // option "k1_bench_frac": relp_debug_k1_dense fills the block with general rationals
     long long k1_exit = 8 << 20;    // option "k1_exit": T x S from which the persistent loop hands a dense update to k_update
@@ -564,12 +566,25 @@ static int publish_scratch_arena(relp_ctx* c, const DState* s) {
     a.wslab = c->wslab.p; a.wslab_words = c->wslab_words; a.wlock = c->wlock.p; a.wslots = c->wslab.p ? c->sm_count * 64 : 0;
     a.scr_top = &c->st.p->tr_top; a.scr_limit = s->tr_limit; a.err = &c->st.p->err; a.flag = &c->st.p->long_seen; a.coop_from = c->coop_from;
     a.heap_words = c->heap_words;
+#ifndef RELP_EMUL
+    if (c->long_mode && !c->tslab.p && c->tslab.alloc((size_t)c->sm_count * 1024u * c->tslab_words)) cudaGetLastError();   // no memory for it: the transient region serves instead
+#endif
+    a.tslab = c->tslab.p; a.tslab_words = c->tslab.p ? c->tslab_words : 0; a.tslots = c->tslab.p ? (unsigned)c->sm_count * 1024u : 0;
     CUDA_TRY(cudaMemcpyAsync(c->scr_ext.p, &a, sizeof(a), cudaMemcpyHostToDevice, c->stream));
     const uint64_t addr = (uint64_t)(uintptr_t)c->scr_ext.p;
     uint32_t words[4] = { 0u, 0u, (uint32_t)addr, (uint32_t)(addr >> 32) };
     CUDA_TRY(cudaMemcpyAsync(c->heap.p, words, sizeof(words), cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     return 0;
+}
+
+// A solve has produced long values: give every resident thread its own scratch slab (sm_count x 1024 threads x 32 KB =
+// 4.6 GiB on a B200 -- only solves that need it pay for it) and tell the device.  If the memory is not there the long
+// one-thread operations keep taking their temporaries from the transient region.
+static int ensure_tslab(relp_ctx* c) {
+    if (c->tslab.p || !c->scr_ext.p) return 0;
+    if (sync_state(c)) return RELP_ERR_CUDA;
+    return publish_scratch_arena(c, c->h_st);       // allocates the slabs: long_mode is set
 }
 
 static void init_heap_regions(relp_ctx* c, DState* s) {
@@ -778,6 +793,7 @@ static int run_loop(relp_ctx* c, int rule, int64_t max_iters, int tag) {
         if (s->err) { result = err_status(s); break; }
         if (s->want_long) {      // a long value has been stored: from here on the copy of the loop with the arbitrary-length tier
             c->long_mode = true;
+            if (ensure_tslab(c)) return RELP_ERR_CUDA;
             LAUNCH(c, k_clear_want_long, 1, 1, c->st.p);
             continue;
         }
@@ -829,7 +845,7 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     s->status = ST_RUNNING; s->last_selected = -1; s->iter = 0; s->iter_limit = ~0ull; s->tag = '1'; s->go = 1;
     s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap; s->k1_min = c->k1_min; s->k1_exit = c->k1_exit;
     init_heap_regions(c, s);
-    c->long_mode = false;
+    c->long_mode = c->force_long;
     if (int rr = stage_rhs(c, s)) return rr;
     if (push_state(c)) return RELP_ERR_CUDA;
     if (publish_scratch_arena(c, s)) return RELP_ERR_CUDA;
@@ -1021,7 +1037,7 @@ static int from_basis(relp_ctx* c, const int32_t* basis_in) {
     s->status = ST_RUNNING; s->last_selected = -1; s->iter = 0; s->iter_limit = ~0ull; s->tag = 'b'; s->go = 1;
     s->rc = make_small(0, 1); s->rc_valid = 0; s->wl_cap = (int)c->wl_cap; s->k1_min = c->k1_min; s->k1_exit = c->k1_exit;
     init_heap_regions(c, s);
-    c->long_mode = false;
+    c->long_mode = c->force_long;
     if (int rr = stage_rhs(c, s)) return rr;
     if (push_state(c)) return RELP_ERR_CUDA;
     if (publish_scratch_arena(c, s)) return RELP_ERR_CUDA;
@@ -1430,6 +1446,8 @@ int relp_set_option(relp_ctx* c, const char* name, int64_t value) {
     if (!strcmp(name, "k1_exit")) { c->k1_exit = value; return RELP_OK; }
     if (!strcmp(name, "k1_bench_frac")) { c->k1_bench_frac = value != 0; return RELP_OK; }     // takes effect when the Carry is next created
     if (!strcmp(name, "coop_from")) { c->coop_from = (int)std::max<int64_t>(1, std::min<int64_t>(value, RELP_OPL)); if (c->carry_ready && c->scr_ext.p) { if (sync_state(c) || publish_scratch_arena(c, c->h_st)) return RELP_ERR_CUDA; } return RELP_OK; }   // limbs from which operations are cooperative
+    if (!strcmp(name, "long_mode")) { c->force_long = value != 0; return RELP_OK; }       // takes effect when the Carry is next created
+    if (!strcmp(name, "tslab_words")) { c->tslab_words = (unsigned)std::max<int64_t>(64, value); c->tslab.release(); return RELP_OK; }
     if (!strcmp(name, "wslab_words")) { c->wslab_words = (unsigned)std::max<int64_t>(64, value); c->wslab.release(); return RELP_OK; }   // takes effect when the Carry is next created
     if (!strcmp(name, "coop_blocks")) { c->coop_blocks = (int)value; return RELP_OK; }   // debug: CTAs of the persistent kernel
     if (!strcmp(name, "trace")) {      // debug: per-CTA barrier arrival times of the last iteration

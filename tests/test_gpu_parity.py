@@ -186,12 +186,14 @@ def test_dense_update_ring_at_scale(m, frac):
     c.close()
 
 
-@pytest.mark.parametrize("persistent", [True, False])
-def test_cooperative_multi_limb_tier_in_solves(persistent):
+@pytest.mark.parametrize("persistent,long_mode", [(True, 1), (True, 0), (False, 0)])
+def test_cooperative_multi_limb_tier_in_solves(persistent, long_mode):
     """option coop_from = 2: every operation on values beyond two limbs takes the arbitrary-length routines of
     relp_wcb.cuh instead of the fixed-size per-thread ones -- whole warps in the Carry update's multi-limb stage, one
-    lane elsewhere -- same pivots, same Carry as the oracle"""
-    opts = {"coop_from": 2}
+    lane (with its per-thread scratch slab once the solve is in long mode) elsewhere -- same pivots, same Carry as the
+    oracle.  long_mode = 1 runs the full copy of the persistent loop from the first pivot (the fast copy has no such tier
+    and hands over only when a value beyond 12 limbs is stored)."""
+    opts = {"coop_from": 2, "long_mode": long_mode}
     s, o = parity.check_full_solve(pa_from_lp(feasible_lp(0, 10, 2, 10, 6, 40, frac=True, maxval=9, density=0.4)), LIB,
                                    expect_escalation=True, options=opts, persistent=persistent, heap_words=1 << 25)
     assert o.max_bits() > 128
