@@ -902,7 +902,7 @@ static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbe
     if (sync_state(c)) return RELP_ERR_CUDA;
     DState* s = c->h_st;
     s->phase = 2; s->ncols = n; shard_cols(c, s); s->last_selected = -1; s->status = ST_RUNNING;
-    s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld;
+    s->m = m; s->mloc = c->mloc; s->row_lo = c->row_lo; s->ld = c->ld; s->wl_cap = (int)c->wl_cap;
     s->tr_top = s->tr_base; s->T = 0; s->S = 0; s->wl_count = 0; s->W = 0; s->rc_valid = 0;
     if (push_state(c)) return RELP_ERR_CUDA;
     c->phase = 2;
@@ -944,7 +944,6 @@ static int from_artificial(relp_ctx* c) {
 
 static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* rows) {
     if (!c->carry_ready || c->phase != 1) { set_error("no artificial tableau"); return RELP_ERR_ARGUMENT; }
-    if (c->world > 1) { set_error("row removal is single-GPU only"); return RELP_ERR_COMM; }
     CUDA_TRY(cudaSetDevice(c->device));
     int m = c->m, n = c->n;
     std::vector<int> basis;
@@ -958,12 +957,54 @@ static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* r
     keep_col[0] = 0; for (int k = 0; k < m2; k++) keep_col[1 + k] = 1 + keep[k];
     int ld2 = std::max(32, (m2 + 31) / 32 * 32);
     DBuf<int64_t> nxn, nxd;
-    if (nxn.alloc((size_t)(m2 + 1) * ld2) || nxd.alloc((size_t)(m2 + 1) * ld2)) return RELP_ERR_CUDA;
     int* kr = c->scratch_i.p; int* kc = c->scratch_i.p + (m + 2);
-    if (m2) CUDA_TRY(cudaMemcpyAsync(kr, keep.data(), keep.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(cudaMemcpyAsync(kc, keep_col.data(), keep_col.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
-    LAUNCH(c, k_gather_planes, c->sm_count * 8, RELP_THREADS, c->xn.p, c->xd.p, c->ld, nxn.p, nxd.p, ld2, m2, m2 + 1, kr, kc);
-    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    if (c->world == 1) {
+        if (nxn.alloc((size_t)(m2 + 1) * ld2) || nxd.alloc((size_t)(m2 + 1) * ld2)) return RELP_ERR_CUDA;
+        if (m2) CUDA_TRY(cudaMemcpyAsync(kr, keep.data(), keep.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        LAUNCH(c, k_gather_planes, c->sm_count * 8, RELP_THREADS, c->xn.p, c->xd.p, c->ld, nxn.p, nxd.p, ld2, m2, m2 + 1, kr, kc);
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+    } else {
+        // Several GPUs: the block is re-sharded (m2 rows over the same ranks).  Every rank compacts the kept rows of its
+        // shard (kept columns only), the compacted shards are all-gathered, and every rank picks the rows of its NEW
+        // shard out of them.  Row removal happens once per solve on rank-deficient problems; the gathered copy is the
+        // size of the whole Carry block (16 (m2 + 1) m2 bytes).  Values must be in the int64 tier to cross GPUs.
+        if (!c->comm && !c->cb_allgather) { set_error("row removal on several GPUs needs a communicator (relp_attach_comm)"); return RELP_ERR_COMM; }
+        const int per_old = (m + c->world - 1) / c->world, per_new = (m2 + c->world - 1) / c->world;
+        std::vector<int> first_kept(c->world + 1, 0);          // first_kept[r] = number of kept rows owned by ranks < r (old sharding)
+        for (int i : keep) first_kept[std::min(i / per_old, c->world - 1) + 1]++;
+        int maxk = 1;
+        for (int r = 0; r < c->world; r++) { maxk = std::max(maxk, first_kept[r + 1]); first_kept[r + 1] += first_kept[r]; }
+        const size_t shard_words = (size_t)(m2 + 1) * maxk;
+        if ((size_t)c->world * shard_words > (size_t)INT_MAX) { set_error("row removal on several GPUs: the block is too large for the gathered copy"); return RELP_ERR_ARGUMENT; }
+        DBuf<int64_t> sendn, sendd, alln, alld; DBuf<int> rl;
+        if (sendn.alloc(shard_words) || sendd.alloc(shard_words) || alln.alloc(c->world * shard_words) || alld.alloc(c->world * shard_words) ||
+            rl.alloc((size_t)std::max(maxk, std::max(per_new, 1)))) return RELP_ERR_CUDA;
+        std::vector<int> local;                                 // kept rows of this rank, as local row indices
+        for (int g = first_kept[c->rank]; g < first_kept[c->rank + 1]; g++) local.push_back(keep[g] - c->row_lo);
+        if (!local.empty()) CUDA_TRY(cudaMemcpyAsync(rl.p, local.data(), local.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        LAUNCH(c, k_gather_planes, c->sm_count * 8, RELP_THREADS, c->xn.p, c->xd.p, c->ld, sendn.p, sendd.p, maxk, (int)local.size(), m2 + 1, rl.p, kc);
+        LAUNCH(c, k_flag_multi_limb, c->sm_count * 4, RELP_THREADS, c->st.p, sendd.p, (long long)shard_words);
+        if (comm_allgather(c, sendn.p, alln.p, shard_words * 8) || comm_allgather(c, sendd.p, alld.p, shard_words * 8)) return RELP_ERR_COMM;
+        // new shard of this rank: new global row g -> (old rank, position among that rank's kept rows)
+        const int lo2 = std::min(m2, c->rank * per_new), mloc2 = std::max(0, std::min(m2, lo2 + per_new) - lo2);
+        ld2 = std::max(32, (mloc2 + 31) / 32 * 32);
+        if (nxn.alloc((size_t)(m2 + 1) * ld2) || nxd.alloc((size_t)(m2 + 1) * ld2)) return RELP_ERR_CUDA;
+        std::vector<int> src(std::max(mloc2, 1), 0), ident(m2 + 1);
+        for (int li = 0; li < mloc2; li++) {
+            const int g = lo2 + li;
+            int r = 0; while (g >= first_kept[r + 1]) r++;
+            src[li] = (int)((size_t)r * shard_words + (size_t)(g - first_kept[r]));
+        }
+        for (int k = 0; k <= m2; k++) ident[k] = k;
+        CUDA_TRY(cudaStreamSynchronize(c->stream));            // rl and kc are read by the launches above
+        CUDA_TRY(cudaMemcpyAsync(rl.p, src.data(), src.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(cudaMemcpyAsync(kc, ident.data(), ident.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        LAUNCH(c, k_gather_planes, c->sm_count * 8, RELP_THREADS, alln.p, alld.p, maxk, nxn.p, nxd.p, ld2, mloc2, m2 + 1, rl.p, kc);
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        if (sync_state(c)) return RELP_ERR_CUDA;
+        if (c->h_st->err) return err_status(c->h_st);
+    }
     c->xn.swap(nxn); c->xd.swap(nxd);      // (with the capacity: alloc_carry trusts it when the context is reused)
     // provider without the removed rows (filter/generic_wrapper.rs:224-300)
     if (c->row_idx.empty() && c->col_ptr[n] > 0) {
@@ -1000,7 +1041,16 @@ static int from_artificial_remove_rows(relp_ctx* c, int n_rows, const int32_t* r
         CUDA_TRY(cudaMemcpyAsync(c->rhsd_d.p, c->rhsd.data(), (size_t)m2 * 8, cudaMemcpyHostToDevice, c->stream));
     }
     CUDA_TRY(cudaStreamSynchronize(c->stream));
-    c->m = m2; shard_rows(c, m2); c->ld = ld2;
+    c->m = m2; shard_rows(c, m2); c->ld = ld2;      // (several GPUs: ld2 was computed from this rank's new shard)
+    if (c->world > 1) {
+        // re-sharding can GROW a rank's shard (m = 9 on 4 ranks: 3,3,3,0 -> m2 = 8: 2,2,2,2): the per-shard buffers are
+        // grow-only, their contents are scratch or rebuilt by the hand-over (pattern bitmaps)
+        if (c->tlist.alloc(c->mloc + 1) || c->cost_rows.alloc(c->mloc + 1) || c->dn.alloc(c->ld + 32) || c->dd.alloc(c->ld + 32) ||
+            c->colbits.alloc((size_t)(m2 + 1) * (c->ld / 32) + 2) || c->rowbits.alloc((size_t)c->ld * ((m2 + 32) / 32) + 4) ||
+            c->colsum.alloc((size_t)(m2 + 1) * ((c->ld / 32 + 31) / 32) + 2)) return RELP_ERR_CUDA;
+        c->wl_cap = std::max(c->wl_cap, std::min<size_t>((size_t)(m2 + 1) * std::max(c->mloc, 1), (size_t)1 << 24));
+        if (c->worklist.alloc(c->wl_cap)) return RELP_ERR_CUDA;
+    }
     int rc = build_sell(c, c->col_ptr.data());
     if (rc) return rc;
     basis = b2;
@@ -1095,6 +1145,15 @@ static int remove_artificial_basis_variables(relp_ctx* c) {
     c->rows_removed.clear();
     if (arts.empty()) return RELP_OK;
     int* d_best = c->scratch_i.p;
+    // Several GPUs: the clean-up pivots go through the stage-per-launch driver with the attached communicator (a handful
+    // of pivots per solve).  With the peer transport the pivot row lives in the exchange buffers: point the stages at the
+    // context's own buffers for the duration.
+    struct Unpeer {
+        relp_ctx* c; bool was;
+        explicit Unpeer(relp_ctx* c_) : c(c_), was(c_->peer_mode) { if (was) { c->peer_mode = false; wire_dev(c); } }
+        ~Unpeer() { if (was) { c->peer_mode = true; wire_dev(c); } }
+    } unpeer(c);
+    if (c->world > 1 && !c->comm && !c->cb_allreduce) { set_error("artificial clean-up on several GPUs needs a communicator (relp_attach_comm)"); return RELP_ERR_COMM; }
     for (int a : arts) {
         int pivot_row = c->art_rows_h[a];
         int best = INT_MAX;
@@ -1103,7 +1162,17 @@ static int remove_artificial_basis_variables(relp_ctx* c) {
         LAUNCH(c, k_cleanup_select, grid_for(c, c->n), RELP_THREADS, c->D, pivot_row, d_best);
         CUDA_TRY(cudaMemcpyAsync(&best, d_best, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
         CUDA_TRY(cudaStreamSynchronize(c->stream));
-        if (c->world > 1) { set_error("artificial clean-up is single-GPU only"); return RELP_ERR_COMM; }
+        if (c->world > 1) {
+            // only the owner of the pivot row can test B^-1[row] . a_j: everybody else contributes 0 to a sum
+            const bool owner = pivot_row >= c->row_lo && pivot_row < c->row_lo + c->mloc;
+            int64_t v = owner ? (int64_t)best : 0;
+            int64_t* d_v = c->tmpn.p;
+            CUDA_TRY(cudaMemcpyAsync(d_v, &v, 8, cudaMemcpyHostToDevice, c->stream));
+            if (comm_allreduce_i64(c, d_v, 1)) return RELP_ERR_COMM;
+            CUDA_TRY(cudaMemcpyAsync(&v, d_v, 8, cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(cudaStreamSynchronize(c->stream));
+            best = (int)v;
+        }
         // the reference pushes `artificial` (phase_one.rs:251); equal to pivot_row whenever the reference survives (else it removes the wrong row and underflows at carry/mod.rs:665)
         if (best == INT_MAX) { c->rows_removed.push_back(pivot_row); continue; }
         LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'z', 1, 1);

@@ -1969,6 +1969,11 @@ __global__ void k_gather_planes(const int64_t* sn, const int64_t* sd, int sld,
         tn[e] = n; td[e] = d;
     }
 }
+// values that would have to cross GPUs must be in the int64 tier: a denominator 0 is a rank-local heap handle
+__global__ void k_flag_multi_limb(DState* st, const int64_t* d, long long count) {
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < count; e += (long long)gridDim.x * blockDim.x)
+        if (d[e] == 0) { atomicOr(&st->err, ERR_PEER_BIG); return; }
+}
 __global__ void k_gather_vec(const int64_t* sn, const int64_t* sd, int64_t* tn, int64_t* td, int count, const int* keep) {
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
         tn[k] = sn[keep[k]]; td[k] = sd[keep[k]];

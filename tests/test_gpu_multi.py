@@ -39,6 +39,33 @@ WORKER = textwrap.dedent('''
             st2 = sc.solve_relaxation()          # a second solve in the same context (new epoch of the exchange ring)
             assert st2 == st and sc.get_objective_function_value() == o.objective()
             sc.close(); del o
+    # rank-deficient LPs on several GPUs (round 2): artificial clean-up pivots through the staged driver, row removal with
+    # re-sharding of the Carry block, then phase two in the persistent peer loop / the NCCL stages; miplib 50v-10
+    # (BASELINE configs[3], one redundant row) is the full-size case
+    from helpers import feasible_lp, pa_from_lp
+    import test_mps_golden as G
+    deficient = [pa_from_lp(feasible_lp(s, a, b, c, d, e, frac=False, dup_rows=k))
+                 for (s, a, b, c, d, e, k) in ((9, 4, 1, 4, 2, 16, 2), (4, 5, 1, 3, 1, 14, 3), (6, 3, 0, 5, 1, 12, 1))]
+    deficient.append(G.load_fixture("miplib_50v-10")[0])
+    for transport in ("peer", "nccl"):
+        removed = 0
+        for pa in deficient:
+            o = coracle.COracle(pa); st_o = o.solve(1, 2)
+            sc = multi.ShardedCarry(pa, device=local, heap_words=1 << 22, transport=transport)
+            try:
+                st = sc.solve_relaxation()
+            except capi.RelpError as e:
+                assert e.status == capi.ERR_LIMB_CAPACITY, (transport, e)       # a multi-limb value would have to cross GPUs
+                sc.close(); continue
+            assert st == parity.STATUS[st_o], (transport, st, st_o)
+            assert [x[:4] for x in sc.log()] == [x[:4] for x in parity.oracle_log(o)], transport
+            assert len(sc.c.rows_removed()) == pa.m - o.m
+            removed += len(sc.c.rows_removed())
+            if st_o == coracle.OPTIMAL:
+                assert sc.get_objective_function_value() == o.objective()
+                assert sc.current_bfs() == o.current_bfs()
+            sc.close(); del o
+        assert removed > 0, transport
     # values that leave the int64 tier cannot cross GPUs: every rank must stop with an error (or every rank must
     # finish with the oracle's answer if no such value had to cross) -- promptly, never a hang and never a mix
     import time
