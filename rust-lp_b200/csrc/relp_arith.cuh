@@ -774,11 +774,14 @@ struct WarpGroup {      // all 32 lanes of a warp, converged by the caller (one-
 
 
 
+#if defined(RELP_WCB_TEST_SLAB) && !defined(__CUDA_ARCH__)
+extern uint32_t* relp_test_slab; extern unsigned relp_test_slab_words;
+#endif
 template <class G> struct WOp {          // scratch of one cooperative operation
     WScratch<G> sc; int slot; bool locked; const ScratchExt* ext;
 };
 template <class G> RELP_HD void wop_begin(const G& g, WOp<G>& op, uint32_t* heap, const Arena& ar) {
-    op.sc.slab = nullptr; op.sc.cap = 0; op.sc.used = 0; op.sc.heap = heap; op.slot = -1; op.locked = false;
+    op.sc.slab = nullptr; op.sc.cap = 0; op.sc.used = 0; op.sc.heap = heap; op.slot = -1; op.locked = false; op.sc.spills = 0;
     op.sc.fallback = ar;
     op.sc.fallback.flag = nullptr;
     const ScratchExt* x = heap_scratch(heap);
@@ -799,6 +802,9 @@ template <class G> RELP_HD void wop_begin(const G& g, WOp<G>& op, uint32_t* heap
         const unsigned long long gt = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
         if (gt < x->tslots) { op.sc.slab = x->tslab + (size_t)gt * x->tslab_words; op.sc.cap = x->tslab_words; }
     }
+#endif
+#if defined(RELP_WCB_TEST_SLAB) && !defined(__CUDA_ARCH__)
+    if (relp_test_slab_words) { op.sc.slab = relp_test_slab; op.sc.cap = relp_test_slab_words; }     // host tests of the slab's stack discipline
 #endif
     (void)g;
 }
@@ -851,22 +857,30 @@ RELP_W int w_gcd_of(const G& g, WScratch<G>& sc, const uint32_t* p, int np, cons
     *gp = nullptr;
     if ((np == 1 && p[0] == 1) || (nq == 1 && q[0] == 1)) return 1;
     const int cap = (np > nq ? np : nq) + 3;
+    const unsigned mk = sc.mark(), sp = sc.spills;
     uint32_t* u = sc.take(g, cap); uint32_t* v = sc.take(g, cap);
     uint32_t* t1 = sc.take(g, cap); uint32_t* t2 = sc.take(g, cap); uint32_t* t3 = sc.take(g, cap);
     if (!u || !v || !t1 || !t2 || !t3) return -1;
     w_copy(g, u, p, np); w_copy(g, v, q, nq);
     const int ng = w_gcd(g, u, np, v, nq, t1, t2, t3, gp);
     if (ng == 1 && (*gp)[0] == 1) *gp = nullptr;
+    if (sc.releasable(sp)) {          // keep the result at the bottom of what was taken, give the other four buffers back
+        g.sync();                     // (every lane is done reading them: what is given back is overwritten by the next take)
+        if (*gp && *gp != u) { w_copy(g, u, *gp, ng); *gp = u; }
+        sc.release_to(mk + (*gp ? (unsigned)ng : 0u));
+    }
     return ng;
 }
 // p / d exactly into fresh scratch (p stays intact); d == nullptr means 1: the operand itself is returned
 RELP_W const uint32_t* w_quot(const G& g, WScratch<G>& sc, const uint32_t* p, int np, const uint32_t* d, int nd, int* nout) {
     if (!d) { *nout = np; return p; }
+    const unsigned mk = sc.mark(), sp = sc.spills;
     uint32_t* out = sc.take(g, np + 1); uint32_t* cp = sc.take(g, np + 1);
     uint32_t* dt = sc.take(g, nd + 1); uint32_t* pt = sc.take(g, nd + 2);
     if (!out || !cp || !dt || !pt) { *nout = -1; return nullptr; }
     w_copy(g, cp, p, np);
     *nout = w_divexact(g, out, cp, np, d, nd, dt, pt);
+    if (sc.releasable(sp)) { g.sync(); sc.release_to(mk + (unsigned)(*nout > 0 ? *nout : 1)); }      // the quotient stays, its temporaries go (once every lane is done with them)
     return out;
 }
 

@@ -42,6 +42,12 @@ struct SoloGroup {
 template <class G> struct WScratch {
     uint32_t* slab; unsigned cap, used;
     uint32_t* heap; Arena fallback;
+    unsigned spills = 0;          // takes served by the fallback arena (those cannot be given back before the iteration ends)
+    // Stack discipline for the slab: a routine notes mark() on entry, takes its temporaries, and gives everything behind
+    // its result back with release_to() -- possible only if nothing was spilled in between.
+    RELP_HD unsigned mark() const { return used; }
+    RELP_HD bool releasable(unsigned spills_at_mark) const { return slab != nullptr && spills == spills_at_mark; }
+    RELP_HD void release_to(unsigned new_used) { used = new_used; }
     RELP_HD uint32_t* take(const G& g, int words) {
         unsigned w = (unsigned)(words < 1 ? 1 : words);
 #if defined(RELP_WCB_TEST_MALLOC) && !defined(__CUDA_ARCH__)
@@ -52,6 +58,7 @@ template <class G> struct WScratch {
         return (uint32_t*)(uintptr_t)q;
 #endif
         if (slab && used + w <= cap) { uint32_t* p = slab + used; used += w; return p; }
+        spills++;
         if (!fallback.top) return nullptr;
         long long off = 0;
         if (g.rank() == 0) off = arena_alloc(fallback, w);

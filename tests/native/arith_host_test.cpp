@@ -1,11 +1,14 @@
 // TEST INFRASTRUCTURE: host build (g++) of the product's __host__ __device__ arithmetic
 // (rust-lp_b200/csrc/relp_arith.cuh) so that tests/test_arith_host.py can check it against
 // Python's fractions.Fraction without a GPU.  Not part of the product library.
+#define RELP_WCB_TEST_SLAB 1
 #include "relp_arith.cuh"
 #include <vector>
 #include <algorithm>
 #include <cstring>
 using namespace relp;
+namespace relp { uint32_t* relp_test_slab = nullptr; unsigned relp_test_slab_words = 0; }
+static std::vector<uint32_t> g_slab;
 
 static std::vector<uint32_t> g_heap(1 << 24);
 static unsigned long long g_top = 16;
@@ -21,6 +24,8 @@ static Arena arena() {
 }
 
 extern "C" {
+// scratch slab of the cooperative operations (0 words = none: everything from the arena); a small one makes them spill midway
+void t_set_slab(int words) { g_slab.assign((size_t)(words > 0 ? words : 1), 0xdeadbeefu); relp::relp_test_slab = g_slab.data(); relp::relp_test_slab_words = (unsigned)(words > 0 ? words : 0); }
 void t_reset() { g_top = 16; g_err = 0; }
 int t_err() { return g_err; }
 int t_opl() { return RELP_OPL; }

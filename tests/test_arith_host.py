@@ -280,3 +280,32 @@ def test_wcb_rationals(L, S, bits, seed):
         assert L.t_w_cmp(S, vx, va) == (x > a) - (x < a)
         assert L.t_w_cmp(S, vx, vx) == 0
         assert L.t_err() == 0
+
+
+@pytest.mark.parametrize("slab_words", [100000, 700, 150])
+def test_wcb_scratch_slab_stack_discipline(L, slab_words):
+    """the cooperative operations take their temporaries from a slab and give them back as soon as a partial result is
+    final (gcd: four of five buffers, exact quotient: three of four); a slab that is too small makes them spill into the
+    arena midway, after which nothing is given back -- results must be the same in every case"""
+    rnd = random.Random(slab_words)
+    out = (C.c_int64 * 2)()
+    L.t_set_slab(slab_words)
+    try:
+        for it in range(60):
+            if it % 10 == 0:
+                L.t_reset()
+            bits = rnd.choice([70, 200, 500, 1500])
+            x, a, b = (Fr(rnd.getrandbits(bits) * rnd.choice([1, -1]), rnd.getrandbits(bits) + 1) for _ in range(3))
+            if it % 3 == 0:
+                x = x * Fr(a.denominator * 6, 35)         # shared factors: the gcds are not 1
+            vx, va, vb = mk(L, x), mk(L, a), mk(L, b)
+            for S in (1, 5, 32):
+                L.t_w_fma(S, vx, va, vb, -1, out)
+                assert rd(L, out) == x - a * b
+                if b != 0:
+                    L.t_w_div(S, vx, vb, out)
+                    assert rd(L, out) == x / b
+                assert L.t_w_cmp(S, vx, va) == (x > a) - (x < a)
+            assert L.t_err() == 0
+    finally:
+        L.t_set_slab(0)
