@@ -34,6 +34,7 @@ def lib():
         L.orc_create.restype = C.c_void_p
         L.orc_create.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 8 + [C.c_int, C.c_void_p, C.c_void_p]
         L.orc_destroy.argtypes = [C.c_void_p]
+        L.orc_set_cleanup_any.argtypes = [C.c_void_p, C.c_int]
         for f in ("orc_set_cost", "orc_set_rhs"):
             getattr(L, f).argtypes = [C.c_void_p, C.c_int, C.c_char_p]
         L.orc_set_value.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p]
@@ -88,6 +89,10 @@ class COracle:
         if getattr(self, "h", None):
             lib().orc_destroy(self.h)
             self.h = None
+
+    def set_cleanup_any(self, on=True):
+        """clean-up pivots on any nonzero element of the artificial's row (default: the reference's zero-cost columns only)"""
+        lib().orc_set_cleanup_any(self.h, 1 if on else 0)
 
     def begin(self, rule1=1, rule2=2):
         lib().orc_begin(self.h, rule1, rule2)

@@ -235,6 +235,7 @@ struct Solver {
     }
 
     // phase_one.rs:223-260
+    bool cleanup_any = false;      // test/diagnostic switch: pivot on any nonzero element of the row (see relp_set_option "cleanup_any")
     void remove_artificial_basis_variables() {
         rows_removed.clear();
         std::vector<int> arts;   // snapshot, ascending (phase_one.rs:230-232)
@@ -245,7 +246,7 @@ struct Solver {
             for (int j = nr_art; j < nr_columns(); j++) {
                 if (in_basis[j]) continue;
                 Rat rc = relative_cost(j);
-                if (!rc.is_zero()) continue;
+                if (!cleanup_any && !rc.is_zero()) continue;       // the reference tries zero-cost columns only (phase_one.rs:243)
                 if (!generate_element(pivot_row, original_column(j)).is_zero()) { found = j; cost = rc; break; }
             }
             if (found >= 0) {
@@ -409,6 +410,7 @@ void* orc_create(int m, int n, const int64_t* col_ptr, const int32_t* row_idx,
     return s;
 }
 void orc_destroy(void* h) { delete (Solver*)h; }
+void orc_set_cleanup_any(void* h, int v) { ((Solver*)h)->cleanup_any = v != 0; }
 
 // Overwrite one matrix value / cost / rhs with an arbitrary-precision rational (decimal string).
 void orc_set_value(void* h, int j, int k, const char* v) { ((Solver*)h)->lp.cols[j][k].second = Rat::from_string(v); }

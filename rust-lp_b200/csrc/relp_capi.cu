@@ -112,6 +112,7 @@ struct relp_ctx {
     DBuf<unsigned char> xbuf; void* peer_base[RELP_MAX_WORLD] = {}; bool peer_mode = false; int peer_max_m = 0;
     // cooperative multi-limb tier: scratch slabs (one per resident warp slot), their locks, and the Arena that big_cmp finds through the heap
     DBuf<uint32_t> wslab; DBuf<int> wlock; DBuf<ScratchExt> scr_ext; unsigned wslab_words = 2048; int coop_from = RELP_OPL;
+    bool cleanup_any = false;  // option "cleanup_any": the artificial clean-up may pivot on ANY nonzero element of the row, not only in zero-cost columns
     bool force_long = false;   // option "long_mode": run the full copy of the loop (and its scratch) from the first pivot (tests)
     DBuf<uint32_t> tslab; unsigned tslab_words = 8192;     // per-thread scratch of long one-thread operations (ScratchExt::tslab), allocated when a solve turns long
     unsigned long long epoch = 0;
@@ -1159,7 +1160,7 @@ static int remove_artificial_basis_variables(relp_ctx* c) {
         int best = INT_MAX;
         CUDA_TRY(cudaMemcpyAsync(d_best, &best, sizeof(int), cudaMemcpyHostToDevice, c->stream));
         LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'z', 1, 1);
-        LAUNCH(c, k_cleanup_select, grid_for(c, c->n), RELP_THREADS, c->D, pivot_row, d_best);
+        LAUNCH(c, k_cleanup_select, grid_for(c, c->n), RELP_THREADS, c->D, pivot_row, d_best, c->cleanup_any ? 1 : 0);
         CUDA_TRY(cudaMemcpyAsync(&best, d_best, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
         CUDA_TRY(cudaStreamSynchronize(c->stream));
         if (c->world > 1) {
@@ -1515,6 +1516,7 @@ int relp_set_option(relp_ctx* c, const char* name, int64_t value) {
     if (!strcmp(name, "k1_exit")) { c->k1_exit = value; return RELP_OK; }
     if (!strcmp(name, "k1_bench_frac")) { c->k1_bench_frac = value != 0; return RELP_OK; }     // takes effect when the Carry is next created
     if (!strcmp(name, "coop_from")) { c->coop_from = (int)std::max<int64_t>(1, std::min<int64_t>(value, RELP_OPL)); if (c->carry_ready && c->scr_ext.p) { if (sync_state(c) || publish_scratch_arena(c, c->h_st)) return RELP_ERR_CUDA; } return RELP_OK; }   // limbs from which operations are cooperative
+    if (!strcmp(name, "cleanup_any")) { c->cleanup_any = value != 0; return RELP_OK; }
     if (!strcmp(name, "long_mode")) { c->force_long = value != 0; return RELP_OK; }       // takes effect when the Carry is next created
     if (!strcmp(name, "tslab_words")) { c->tslab_words = (unsigned)std::max<int64_t>(64, value); c->tslab.release(); return RELP_OK; }
     if (!strcmp(name, "wslab_words")) { c->wslab_words = (unsigned)std::max<int64_t>(64, value); c->wslab.release(); return RELP_OK; }   // takes effect when the Carry is next created

@@ -1889,7 +1889,9 @@ __global__ void k_recompute_cost_row(Dev D, const int* cost_rows, int n_cost_row
 
 // Artificial clean-up search (phase_one.rs:236-243): first non-artificial non-basic column with
 // relative cost exactly zero and a nonzero element in `pivot_row` of B^-1 A.
-__global__ void k_cleanup_select(Dev D, int pivot_row, int* best_j) {
+// `any_cost` = 0: the reference's rule (phase_one.rs:239-249: only columns whose relative cost is zero are tried);
+// 1: any non-basic column with a nonzero element in the row (the pivot is at zero level either way)
+__global__ void k_cleanup_select(Dev D, int pivot_row, int* best_j, int any_cost) {
     DState* st = D.st;
     if (st->err) return;
     Arena ar = transient(D);
@@ -1898,8 +1900,10 @@ __global__ void k_cleanup_select(Dev D, int pivot_row, int* best_j) {
     const size_t ld = st->ld;
     for (int j = st->nr_art + blockIdx.x * blockDim.x + threadIdx.x; j < st->ncols; j += gridDim.x * blockDim.x) {
         if (D.in_basis[j]) continue;
-        Val rc = price_column_csc(D, st, j, ar);
-        if (rc.n != 0) continue;
+        if (!any_cost) {
+            Val rc = price_column_csc(D, st, j, ar);
+            if (rc.n != 0) continue;
+        }
         if (!owner) continue;
         int jj = j - st->nr_art;
         Val acc = val_zero();

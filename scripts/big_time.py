@@ -16,6 +16,8 @@ for e in EXPECTED:
     if only and name not in only: continue
     pa = load(name)
     c = capi.Carry(pa, heap_words=int(os.environ.get("RELP_HEAP_WORDS", str(1 << 28))))
+    if os.environ.get("RELP_CLEANUP_ANY") == "1":      # artificial clean-up pivots on any nonzero element (default: the reference's zero-cost columns only)
+        c.set_option("cleanup_any", 1)
     t0 = time.time()
     st, first = 0, True
     try:
@@ -53,7 +55,9 @@ for e in EXPECTED:
                        escalated=int(s.escalated), max_limbs=int(s.max_limbs), objective=float(obj), objective_exact=str(obj),
                        reference=e["full_solve_reference"], abs_diff=abs(float(obj) - e["full_solve_reference"]),
                        exact_Ax_eq_b=bool(feasible), objective_equals_cx=bool(obj_std == c.get_objective_function_value()),
-                       rows_removed=len(c.rows_removed()))
+                       rows_removed=len(c.rows_removed()), cleanup_any=os.environ.get("RELP_CLEANUP_ANY") == "1",
+                       violated_rows=[i for i in range(pa.m) if ax[i] != Fr(int(pa.rhs_num[i]), int(pa.rhs_den[i]))][:50],
+                       removed_rows=[int(i) for i in c.rows_removed()])
             print(json.dumps(res), flush=True)
             with open(os.path.join("gpurun_out", "big_result_" + name + ".json"), "w") as fh:
                 json.dump(res, fh, indent=1)

@@ -295,3 +295,23 @@ def check_big_rhs(pa, lib_path):
     refused([1 | 1 << 14, 5, 1], "fits int64")
     refused([0], "denominator < 0", n0=1, d0=-2)
     c.close()
+
+
+def check_cleanup_any(lib_path):
+    """The artificial clean-up.  Reference rule (phase_one.rs:239-249): only columns with relative cost zero are tried, and a
+    row whose artificial cannot be pivoted out that way is REMOVED -- also when the row is not redundant (here: row 0,
+    -x1 - x2 = 0, fixes x1 = x2 = 0; after phase one its only nonzero elements sit in columns with positive relative cost).
+    The default mirrors the reference (objective -5 of the relaxed problem); option cleanup_any = 1 pivots on any nonzero
+    element of the row and reaches the true optimum 0.  Product and oracle agree under both settings."""
+    from rust_lp_b200.synth import ProviderArrays
+    #            x1        x2      slack
+    pa = ProviderArrays(2, 3, [0, 2, 3, 4], [0, 1, 0, 1], [-1, 1, -1, 1], [1, 1, 1, 1], [-1, 0, 0], [1, 1, 1], [0, 5], [1, 1], [1], [2], 2)
+    for any_cost, want in ((0, Fr(-5)), (1, Fr(0))):
+        o = coracle.COracle(pa); o.set_cleanup_any(bool(any_cost))
+        assert o.solve(1, 2) == coracle.OPTIMAL and o.objective() == want, (any_cost, o.objective())
+        c = capi.Carry(pa, heap_words=1 << 20, lib_path=lib_path)
+        c.set_option("cleanup_any", any_cost)
+        assert c.solve_relaxation() == capi.OPTIMAL
+        assert c.get_objective_function_value() == want and c.log() == oracle_log(o) and c.current_bfs() == o.current_bfs()
+        assert len(c.rows_removed()) == (0 if any_cost else 1)
+        c.close()

@@ -170,5 +170,9 @@ def test_set_costs_after_phase_one(lib):
     parity.check_set_costs(pa_from_lp(feasible_lp(7, 6, 2, 4, 2, 12, frac=True)), lib)
 
 
+def test_artificial_cleanup_rule(lib):
+    parity.check_cleanup_any(lib)
+
+
 def test_right_hand_side_beyond_int64(lib):
     parity.check_big_rhs(pa_from_lp(feasible_lp(11, 6, 2, 5, 3, 14, frac=True)), lib)

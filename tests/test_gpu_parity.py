@@ -167,6 +167,10 @@ def test_set_costs_after_phase_one():
     parity.check_set_costs(pa_from_lp(feasible_lp(7, 6, 2, 4, 2, 12, frac=True)), LIB)
 
 
+def test_artificial_cleanup_rule():
+    parity.check_cleanup_any(LIB)
+
+
 def test_right_hand_side_beyond_int64():
     parity.check_big_rhs(pa_from_lp(feasible_lp(11, 6, 2, 5, 3, 14, frac=True)), LIB)
 
