@@ -96,7 +96,10 @@ int relp_abi_version(void);
  * Multi-limb tier (tests): "coop_from" = limbs from which an operation leaves the fixed-size per-thread routines for
  * the arbitrary-length ones (default 64, the per-thread buffers' size); "long_mode" = 1 runs the copy of the loop that
  * contains that tier from the first pivot instead of handing over when a value beyond 12 limbs is stored;
- * "wslab_words" / "tslab_words" = scratch words per resident warp / per thread for long operations. */
+ * "wslab_words" / "tslab_words" = scratch words per resident warp / per thread for long operations.
+ * "cleanup_any" = 1: the artificial clean-up (phase_one.rs:223-260) pivots on ANY nonzero element of the row that holds a
+ * zero-level artificial column and removes a row only when it is entirely zero; default 0 = the reference's rule
+ * (zero-cost columns only, the artificial's original row), which also removes rows that are not redundant -- DESIGN.md 6. */
 int relp_set_option(relp_ctx*, const char* name, int64_t value);
 /* the cudaStream_t all work of this context is enqueued on (for CUDA-event timing by the caller) */
 void* relp_stream(relp_ctx*);

@@ -241,7 +241,9 @@ struct Solver {
         std::vector<int> arts;   // snapshot, ascending (phase_one.rs:230-232)
         for (int a = 0; a < nr_art; a++) if (in_basis[a]) arts.push_back(a);
         for (int a : arts) {
-            int pivot_row = column_to_row[a];
+            int pivot_row = column_to_row[a];       // the reference: the row the artificial STARTED on (partially.rs:98-102)
+            if (cleanup_any)                        // the row that holds it NOW (it may have left and re-entered on another row)
+                for (int i = 0; i < c.m(); i++) if (c.basis_indices[i] == a) pivot_row = i;
             int found = -1; Rat cost;
             for (int j = nr_art; j < nr_columns(); j++) {
                 if (in_basis[j]) continue;
@@ -252,7 +254,8 @@ struct Solver {
             if (found >= 0) {
                 SparseVec col = generate_column(found);
                 bring_into_basis(found, pivot_row, col, cost, 'z');
-            } else rows_removed.push_back(pivot_row);
+            } else if (pivot_row == column_to_row[a]) rows_removed.push_back(pivot_row);
+            // (cleanup_any, artificial on a foreign row whose real part is all zero: it stays, the hand-over reports it)
             // the reference pushes `artificial` (phase_one.rs:251); equal to pivot_row whenever the reference survives (else it removes the wrong row and underflows at carry/mod.rs:665)
         }
     }

@@ -1155,8 +1155,12 @@ static int remove_artificial_basis_variables(relp_ctx* c) {
         ~Unpeer() { if (was) { c->peer_mode = true; wire_dev(c); } }
     } unpeer(c);
     if (c->world > 1 && !c->comm && !c->cb_allreduce) { set_error("artificial clean-up on several GPUs needs a communicator (relp_attach_comm)"); return RELP_ERR_COMM; }
+    std::vector<int> row_now(c->nr_art, -1);
+    for (int i = 0; i < (int)basis.size(); i++) if (basis[i] < c->nr_art) row_now[basis[i]] = i;     // (clean-up pivots only replace the artificial itself)
     for (int a : arts) {
-        int pivot_row = c->art_rows_h[a];
+        // the reference: the row the artificial STARTED on (partially.rs:98-102); cleanup_any: the row that holds it NOW
+        // (an artificial that left the basis and re-entered on another row is otherwise pivoted on the wrong row and stays)
+        int pivot_row = c->cleanup_any ? row_now[a] : c->art_rows_h[a];
         int best = INT_MAX;
         CUDA_TRY(cudaMemcpyAsync(d_best, &best, sizeof(int), cudaMemcpyHostToDevice, c->stream));
         LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'z', 1, 1);
@@ -1175,7 +1179,10 @@ static int remove_artificial_basis_variables(relp_ctx* c) {
             best = (int)v;
         }
         // the reference pushes `artificial` (phase_one.rs:251); equal to pivot_row whenever the reference survives (else it removes the wrong row and underflows at carry/mod.rs:665)
-        if (best == INT_MAX) { c->rows_removed.push_back(pivot_row); continue; }
+        if (best == INT_MAX) {
+            if (pivot_row == c->art_rows_h[a]) c->rows_removed.push_back(pivot_row);
+            continue;       // (cleanup_any, on a foreign row whose real part is all zero: it stays, the hand-over reports RELP_ERR_ARTIFICIAL_BASIC)
+        }
         LAUNCH(c, k_set_control, 1, 1, c->st.p, ~0ull, (int)'z', 1, 1);
         enqueue_begin(c);
         LAUNCH(c, k_set_pivot, 1, 1, c->st.p, best, pivot_row, 1);
