@@ -870,16 +870,35 @@ static int create_partially_artificial(relp_ctx* c, int n_piv, const int32_t* pi
     return RELP_OK;
 }
 
-// exact sum of the per-rank partial cost rows (multi-GPU hand-over): int64 tier only
+// Multi-GPU hand-over: the per-rank partial cost rows cross GPUs in a fixed-width format of four int64 per entry --
+// |numerator| low and high 64 bits, denominator (< 2^63), sign -- because a rank's PARTIAL sum leaves int64 well before the
+// total does (miplib 50v-10: values of 63 bits).  A partial beyond 128/63 bits sets ERR_PEER_BIG.
+__global__ void k_pack_partials(Dev D, const int64_t* pn, const int64_t* pd, int count, int64_t* out) {
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
+        Val v = make_small(pn[k], pd[k]);
+        Ref r; ref_load(r, v, D.heap);
+        int64_t* o = out + 4 * (size_t)k;
+        if (r.nn > 4 || r.nd > 2 || (r.nd == 2 && (r.den[1] >> 31))) { o[0] = o[1] = 0; o[2] = 1; o[3] = 2; atomicOr(&D.st->err, ERR_PEER_BIG); continue; }
+        uint64_t lo = 0, hi = 0, den = 0;
+        for (int q = 0; q < r.nn; q++) { if (q < 2) lo |= (uint64_t)r.num[q] << (32 * q); else hi |= (uint64_t)r.num[q] << (32 * (q - 2)); }
+        for (int q = 0; q < r.nd; q++) den |= (uint64_t)r.den[q] << (32 * q);
+        o[0] = (int64_t)lo; o[1] = (int64_t)hi; o[2] = (int64_t)den; o[3] = r.sign;
+    }
+}
+// exact sum of the packed partials of all ranks
 __global__ void k_sum_partials(Dev D, const int64_t* allp, int world, int count, int64_t* outn, int64_t* outd) {
-    Arena ar = persistent(D);
+    Arena ar = persistent(D), tr = transient(D);
     Val one = make_small(1, 1);
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
         Val acc = val_zero();
         for (int r = 0; r < world; r++) {
-            const int64_t* base = allp + (size_t)r * 2 * count;
-            Val v = make_small(base[k], base[count + k]);
-            if (v.d <= 0) { atomicOr(&D.st->err, ERR_LIMB_CAPACITY); continue; }
+            const int64_t* e = allp + ((size_t)r * count + k) * 4;
+            if (e[3] == 0) continue;
+            if (e[3] == 2) { atomicOr(&D.st->err, ERR_PEER_BIG); continue; }
+            const uint64_t lo = (uint64_t)e[0], hi = (uint64_t)e[1], den = (uint64_t)e[2];
+            uint32_t num[4] = { (uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32) };
+            uint32_t dn[2] = { (uint32_t)den, (uint32_t)(den >> 32) };
+            Val v = store_val((int)e[3], num, mag_trim(num, 4), dn, mag_trim(dn, 2), D.heap, tr);      // already in lowest terms
             acc = val_fma(acc, v, one, 1, D.heap, ar);
         }
         outn[k] = acc.n; outd[k] = acc.d;
@@ -915,9 +934,11 @@ static int handover_common(relp_ctx* c, std::vector<int>& basis /* tableau numbe
         // each rank sums over its rows into pn|pd, the partials are all-gathered and added exactly
         int cnt = m + 1;
         DBuf<int64_t>& all = c->hand_all;
-        if (all.alloc((size_t)c->world * 2 * cnt)) return RELP_ERR_CUDA;
+        DBuf<int64_t> packed;
+        if (all.alloc((size_t)c->world * 4 * cnt) || packed.alloc(4 * (size_t)cnt)) return RELP_ERR_CUDA;
         LAUNCH(c, k_recompute_cost_row, grid_for(c, cnt, 2), RELP_THREADS, c->D, c->cost_rows.p, (int)cost_rows.size(), c->pnd.p, c->pnd.p + cnt);      // (not D.pn: with the peer transport that lives in the exchange buffer)
-        if (comm_allgather(c, c->pnd.p, all.p, 2 * (size_t)cnt * 8)) return RELP_ERR_COMM;
+        LAUNCH(c, k_pack_partials, grid_for(c, cnt, 2), RELP_THREADS, c->D, c->pnd.p, c->pnd.p + cnt, cnt, packed.p);
+        if (comm_allgather(c, packed.p, all.p, 4 * (size_t)cnt * 8)) return RELP_ERR_COMM;
         LAUNCH(c, k_sum_partials, grid_for(c, cnt, 2), RELP_THREADS, c->D, all.p, c->world, cnt, c->zn.p, c->zd.p);
         CUDA_TRY(cudaStreamSynchronize(c->stream));
     }

@@ -27,15 +27,18 @@ WORKER = textwrap.dedent('''
     # rank-deficient LPs: artificial clean-up pivots and row removal with re-sharding across the ranks (round 2)
     deficient = [pa_from_lp(feasible_lp(s, a, b, c, d, e, frac=False, dup_rows=k))
                  for (s, a, b, c, d, e, k) in ((9, 4, 1, 4, 2, 16, 2), (2, 3, 1, 3, 2, 10, 1), (4, 5, 1, 3, 1, 14, 3), (6, 3, 0, 5, 1, 12, 1), (8, 2, 1, 4, 0, 11, 2))]
+    # hand-over with partial cost-row sums beyond int64 (they cross ranks as 128/63-bit records): costs scaled by 2^48
+    import copy
+    wide = copy.deepcopy(cases[1]); wide.cost_num = wide.cost_num * (1 << 48)       # objective and partial sums of 66 bits; reduced costs stay below 2^56
     removed_somewhere = 0
-    for pa in cases + deficient:
+    for pa in cases + deficient + [wide]:
         o = coracle.COracle(pa); st_o = o.solve(1, 2)
         sc = multi.ShardedCarry(pa, device=0, heap_words=1 << 22, lib_path=lib, transport="callbacks")
         try:
             st = sc.solve_relaxation()
         except capi.RelpError as e:
             # the one documented restriction of the sharded path: a multi-limb value that would have to cross ranks
-            assert e.status == capi.ERR_LIMB_CAPACITY, e
+            assert e.status == capi.ERR_LIMB_CAPACITY and pa is not wide, e
             print("rank", dist.get_rank(), "restriction:", e); sc.close(); continue
         assert st == parity.STATUS[st_o], (st, st_o)
         removed_somewhere += len(sc.c.rows_removed())
