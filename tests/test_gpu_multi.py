@@ -55,7 +55,8 @@ WORKER = textwrap.dedent('''
             try:
                 st = sc.solve_relaxation()
             except capi.RelpError as e:
-                assert e.status == capi.ERR_LIMB_CAPACITY, (transport, e)       # a multi-limb value would have to cross GPUs
+                # a multi-limb value would have to cross GPUs: accepted for the random LPs, not for 50v-10 (peer transport)
+                assert e.status == capi.ERR_LIMB_CAPACITY and not (pa is deficient[-1] and transport == "peer"), (transport, e)
                 sc.close(); continue
             assert st == parity.STATUS[st_o], (transport, st, st_o)
             assert [x[:4] for x in sc.log()] == [x[:4] for x in parity.oracle_log(o)], transport
