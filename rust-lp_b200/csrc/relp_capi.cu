@@ -16,6 +16,7 @@
 #include <string>
 #include <vector>
 #include <dlfcn.h>
+#include <thread>
 
 using namespace relp;
 
@@ -401,18 +402,31 @@ int relp_load_matrix(relp_ctx* c, int32_t m, int32_t n, const int64_t* col_ptr, 
     // out-of-range row index addresses outside the Carry planes, and the right-hand side must be >= 0
     // (matrix_data.rs:359-371).  Nothing is usable until `loaded` is set, which happens only when all of it holds.
     std::string bad;
-    auto check_rats = [&](const int64_t* num, const int64_t* den, long long count, const char* what) {
-        for (long long t = 0; t < count && bad.empty(); t++) {
-            const int64_t d = den[t], v = num[t];
-            if (v == INT64_MIN) { bad = std::string(what) + ": numerator INT64_MIN at " + std::to_string(t); return; }
-            if (d == 1) continue;
-            if (d < 1) { bad = std::string(what) + ": denominator < 1 at " + std::to_string(t); return; }
-            if (gcd64(abs64(v), (uint64_t)d) != 1) bad = std::string(what) + ": not in lowest terms at " + std::to_string(t);
-        }
+    auto rat_fault = [](int64_t v, int64_t d) -> const char* {      // nullptr = canonical
+        if (v == INT64_MIN) return "numerator INT64_MIN";
+        if (d == 1) return nullptr;
+        if (d < 1) return "denominator < 1";
+        return gcd64(abs64(v), (uint64_t)d) != 1 ? "not in lowest terms" : nullptr;
     };
-    for (long long t = 0; t < nnz && bad.empty(); t++)
-        if ((unsigned)row_idx[t] >= (unsigned)m) bad = "row_idx out of range at entry " + std::to_string(t);
-    check_rats(val_num, val_den, nnz, "val");
+    auto check_rats = [&](const int64_t* num, const int64_t* den, long long count, const char* what) {
+        for (long long t = 0; t < count && bad.empty(); t++)
+            if (const char* f = rat_fault(num[t], den[t])) bad = std::string(what) + ": " + f + " at " + std::to_string(t);
+    };
+    {   // the nnz entries: 80 MB of host reads, spread over a few threads so that they finish under the copies
+        const int nthr = (int)std::max<long long>(1, std::min<long long>({8, (long long)std::thread::hardware_concurrency(), nnz / 65536 + 1}));
+        std::vector<long long> bad_row(nthr, -1), bad_val(nthr, -1);
+        auto scan = [&](int w) {
+            const long long lo = nnz * w / nthr, hi = nnz * (w + 1) / nthr;
+            for (long long t = lo; t < hi; t++) if ((unsigned)row_idx[t] >= (unsigned)m) { bad_row[w] = t; break; }
+            for (long long t = lo; t < hi; t++) if (val_num[t] == INT64_MIN || (val_den[t] != 1 && rat_fault(val_num[t], val_den[t]))) { bad_val[w] = t; break; }
+        };
+        std::vector<std::thread> pool;
+        for (int w = 1; w < nthr; w++) pool.emplace_back(scan, w);
+        scan(0);
+        for (auto& th : pool) th.join();
+        for (int w = 0; w < nthr && bad.empty(); w++) if (bad_row[w] >= 0) bad = "row_idx out of range at entry " + std::to_string(bad_row[w]);
+        for (int w = 0; w < nthr && bad.empty(); w++) if (bad_val[w] >= 0) bad = std::string("val: ") + rat_fault(val_num[bad_val[w]], val_den[bad_val[w]]) + " at " + std::to_string(bad_val[w]);
+    }
     check_rats(cost_num, cost_den, n, "cost");
     check_rats(rhs_num, rhs_den, m, "rhs");
     for (int i = 0; i < m && bad.empty(); i++) if (rhs_num[i] < 0) bad = "rhs < 0 in row " + std::to_string(i);
