@@ -47,9 +47,13 @@ def load_npz(path):
     import numpy as np
     from rust_lp_b200.synth import ProviderArrays
     z = np.load(path)
-    return ProviderArrays(int(z["m"]), int(z["n"]), z["col_ptr"].tolist(), z["row_idx"].tolist(), z["val_num"].tolist(),
-                          z["val_den"].tolist(), z["cost_num"].tolist(), z["cost_den"].tolist(), z["rhs_num"].tolist(),
-                          z["rhs_den"].tolist(), z["piv_rows"].tolist(), z["piv_cols"].tolist(), int(z["n_normal"]))
+    pa = ProviderArrays(int(z["m"]), int(z["n"]), z["col_ptr"].tolist(), z["row_idx"].tolist(), z["val_num"].tolist(),
+                        z["val_den"].tolist(), z["cost_num"].tolist(), z["cost_den"].tolist(), z["rhs_num"].tolist(),
+                        z["rhs_den"].tolist(), z["piv_rows"].tolist(), z["piv_cols"].tolist(), int(z["n_normal"]))
+    if "rhs_exact" in z.files:          # right-hand sides beyond int64/int64 (relp_set_rhs)
+        from fractions import Fraction
+        pa.rhs_exact = {int(i): Fraction(int(v[0]), int(v[1])) for i, v in json.loads(bytes(z["rhs_exact"]).decode()).items()}
+    return pa
 
 
 def workload(args):
@@ -77,7 +81,18 @@ def workload(args):
                             "source": "tests/golden/mps_expected.json (oracle full solve; objective pinned against the reference's "
                                       "test value " + str(e["source"]) + "; no presolve)", "max_bits": e["max_bits"]}
             return load_npz(f), gold
-    raise SystemExit(f"unknown workload {args.workload!r}: synth5a or a fixture name under tests/golden/mps*/")
+    if args.workload.startswith("presolved:"):       # the reference's own pipeline (presolve first): tests/golden/mps_presolved/
+        name = args.workload.split(":", 1)[1]
+        f = os.path.join(GOLD, "mps_presolved", name + ".npz")
+        if os.path.exists(f):
+            e = {x["name"]: x for x in json.load(open(os.path.join(GOLD, "mps_presolved_expected.json")))}.get(name)
+            gold = None
+            if e and e.get("status") == "optimal":
+                gold = {"pivots": e["pivots"], "log_sha256": e["log_sha256"], "objective_of_standard_form": None,
+                        "source": "tests/golden/mps_presolved_expected.json (oracle full solve of the presolved standard form; objective pinned "
+                                  "against the reference's test value " + str(e["source"]) + ")", "max_bits": e["max_bits"]}
+            return load_npz(f), gold
+    raise SystemExit(f"unknown workload {args.workload!r}: synth5a, a fixture name under tests/golden/mps*/, or presolved:<fixture>")
 
 
 def config(args, n_gpus, pa):
@@ -85,7 +100,7 @@ def config(args, n_gpus, pa):
         what = (f"synthetic sparse LP 5a ({args.variant}): m={args.m} n={args.n} nnz/col={args.nnz_col} (+{args.m} slack columns), "
                 "exact solve to optimality, FirstProfitableWithMemory/SteepestDescent")
     else:
-        what = (f"{args.workload} (committed MPS fixture, standard form without presolve): m={pa.m} n={pa.n} nnz={pa.nnz}, exact solve to "
+        what = (f"{args.workload} (committed MPS fixture, standard form {'through the reference\'s presolve' if args.workload.startswith('presolved:') else 'without presolve'}): m={pa.m} n={pa.n} nnz={pa.nnz}, exact solve to "
                 "optimality, FirstProfitableWithMemory/SteepestDescent")
     return {"workload": what, "m": pa.m, "n": pa.n, "nnz": pa.nnz, "seed": 20260101 if args.workload == "synth5a" else None,
             "parallelism": "1 GPU" if n_gpus == 1 else f"ONE LP, Carry rows sharded over {n_gpus} GPUs (strong scaling)",
